@@ -1,0 +1,222 @@
+// Dense pass: FP32 chi2 + prior constant for every (star, model), reduced to one
+// minimum per (star, group of BF_GROUP models).
+//
+// Replaces the per-star full-grid sweep of the reference
+// (beast/fitting/fit_metrics/likelihood.py:24-55, 109-167 and beast/fitting/fit.py:657-668):
+//   acc(s, m) = sum_b ( f_sb * r_mb - a_mb )^2 + c2_m   =  -2 ( lnP(s, m) - c_off )
+// with r = 1/sigma, a = (sed+bias)/sigma, c2 = -2 (-lnQ + ln w - c_off).
+//
+// Mapping: each thread keeps 2*NPAIR stars in registers as packed f32x2 pairs
+// (FFMA2: one instruction = 2 star x 1 model FMAs); a thread block owns BF_STAR_BLOCK
+// stars.  Grid tiles (BF_TILE_MODELS models x (2*nb+1) rows, 13 KB at 6 bands) are staged
+// into shared memory by 1-D bulk async copies (TMA, UBLKCP) through a 4-stage
+// mbarrier ring, and every value read from a tile is a warp-wide broadcast that is
+// reused by all 1024 stars of the block.  Per (star, model): 2*nb FFMA2 halves
+// (= 2*nb FP32 FMA) + 1/2 FMNMX3; no exp, no divergent code.
+//
+// This pass is a *filter*: the exact FP64 pass (exact.cu) re-evaluates every model of
+// every selected group, so FP32 rounding here only has to stay inside the selection
+// margin ("margins").
+
+#include "common.cuh"
+
+namespace bf {
+
+constexpr int kDenseThreads = 128;
+constexpr int kDenseStages = 4;
+constexpr int kDensePrefetch = 2;  // tiles in flight ahead of the consumer
+constexpr int kNPair = BF_STAR_BLOCK / kDenseThreads / 2;  // star pairs per thread (4)
+
+template <int NB>
+struct DenseSmem {
+  static constexpr int kRows = 2 * NB + 1;
+  static constexpr uint32_t kTileBytes = kRows * BF_TILE_MODELS * sizeof(float);
+  static constexpr uint32_t kBytes = kDenseStages * kTileBytes + 2 * kDenseStages * sizeof(uint64_t);
+};
+
+template <int NB>
+__global__ void __launch_bounds__(kDenseThreads, 3)
+dense_chi2_kernel(const float* __restrict__ tiles, int64_t n_tiles, int tiles_per_item,
+                  const float* __restrict__ flux, int64_t ld_star, float* __restrict__ gmin,
+                  unsigned int* __restrict__ starmin) {
+  constexpr int TM = BF_TILE_MODELS;
+  constexpr int ROWS = 2 * NB + 1;
+  constexpr uint32_t TILE_BYTES = DenseSmem<NB>::kTileBytes;
+  constexpr int GROUPS_PER_TILE = TM / BF_GROUP;
+
+  extern __shared__ __align__(128) unsigned char smem_raw[];
+  float* stage_buf = reinterpret_cast<float*>(smem_raw);
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem_raw + kDenseStages * TILE_BYTES);
+  uint64_t* empty_bar = full_bar + kDenseStages;
+
+  const int tid = threadIdx.x;
+  const int64_t star0 = static_cast<int64_t>(blockIdx.y) * BF_STAR_BLOCK;
+  const int64_t t_begin = static_cast<int64_t>(blockIdx.x) * tiles_per_item;
+  const int nt = static_cast<int>(min(static_cast<int64_t>(tiles_per_item), n_tiles - t_begin));
+
+  if (tid == 0) {
+#pragma unroll
+    for (int s = 0; s < kDenseStages; ++s) {
+      mbar_init(&full_bar[s], 1);
+      mbar_init(&empty_bar[s], kDenseThreads / 32);
+    }
+    mbar_fence_init();
+  }
+  __syncthreads();
+
+  const float* tile_src = tiles + t_begin * static_cast<int64_t>(ROWS * TM);
+  if (tid == 0) {
+#pragma unroll
+    for (int j = 0; j < kDensePrefetch; ++j) {
+      if (j < nt) {
+        mbar_expect_tx(&full_bar[j], TILE_BYTES);
+        tma_load_1d(stage_buf + j * (ROWS * TM), tile_src + static_cast<int64_t>(j) * (ROWS * TM),
+                    TILE_BYTES, &full_bar[j]);
+      }
+    }
+  }
+
+  // this thread's stars: star0 + q*128 + tid, q = 0..2*NPAIR-1; pair p = (q=2p, q=2p+1)
+  f32x2 f[kNPair][NB];
+#pragma unroll
+  for (int p = 0; p < kNPair; ++p) {
+#pragma unroll
+    for (int b = 0; b < NB; ++b) {
+      const float* fb = flux + static_cast<int64_t>(b) * ld_star + star0 + tid;
+      f[p][b] = pack2(fb[(2 * p) * kDenseThreads], fb[(2 * p + 1) * kDenseThreads]);
+    }
+  }
+
+  const float kInf = __int_as_float(0x7f800000);
+  float rmin[2 * kNPair], smin[2 * kNPair];
+#pragma unroll
+  for (int q = 0; q < 2 * kNPair; ++q) {
+    rmin[q] = kInf;
+    smin[q] = kInf;
+  }
+
+  for (int i = 0; i < nt; ++i) {
+    const int stage = i % kDenseStages;
+    // producer side (one thread): refill the stage that was consumed two iterations ago
+    if (tid == 0) {
+      const int j = i + kDensePrefetch;
+      if (j < nt) {
+        const int js = j % kDenseStages;
+        const int use = j / kDenseStages;
+        if (use > 0) mbar_wait(&empty_bar[js], (use - 1) & 1);
+        mbar_expect_tx(&full_bar[js], TILE_BYTES);
+        tma_load_1d(stage_buf + js * (ROWS * TM), tile_src + static_cast<int64_t>(j) * (ROWS * TM),
+                    TILE_BYTES, &full_bar[js]);
+      }
+    }
+    mbar_wait(&full_bar[stage], (i / kDenseStages) & 1);
+
+    const float* sb = stage_buf + stage * (ROWS * TM);
+#pragma unroll 1
+    for (int g = 0; g < GROUPS_PER_TILE; ++g) {
+#pragma unroll 2
+      for (int m = g * BF_GROUP; m < (g + 1) * BF_GROUP; m += 2) {
+        float2 r[NB], na[NB];
+#pragma unroll
+        for (int b = 0; b < NB; ++b) {
+          r[b] = *reinterpret_cast<const float2*>(sb + b * TM + m);
+          na[b] = *reinterpret_cast<const float2*>(sb + (NB + b) * TM + m);
+        }
+        const float2 c2 = *reinterpret_cast<const float2*>(sb + 2 * NB * TM + m);
+#pragma unroll
+        for (int p = 0; p < kNPair; ++p) {
+          f32x2 acc0 = pack2(c2.x, c2.x);
+          f32x2 acc1 = pack2(c2.y, c2.y);
+#pragma unroll
+          for (int b = 0; b < NB; ++b) {
+            const f32x2 t0 = fma2(f[p][b], pack2(r[b].x, r[b].x), pack2(na[b].x, na[b].x));
+            const f32x2 t1 = fma2(f[p][b], pack2(r[b].y, r[b].y), pack2(na[b].y, na[b].y));
+            acc0 = fma2(t0, t0, acc0);
+            acc1 = fma2(t1, t1, acc1);
+          }
+          float a0l, a0h, a1l, a1h;
+          unpack2(acc0, a0l, a0h);
+          unpack2(acc1, a1l, a1h);
+          rmin[2 * p] = min3(rmin[2 * p], a0l, a1l);
+          rmin[2 * p + 1] = min3(rmin[2 * p + 1], a0h, a1h);
+        }
+      }
+      const int64_t gidx = (t_begin + i) * GROUPS_PER_TILE + g;
+      float* gp = gmin + gidx * ld_star + star0 + tid;
+#pragma unroll
+      for (int q = 0; q < 2 * kNPair; ++q) {
+        gp[q * kDenseThreads] = rmin[q];
+        smin[q] = fminf(smin[q], rmin[q]);
+        rmin[q] = kInf;
+      }
+    }
+    __syncwarp();
+    if ((tid & 31) == 0) mbar_arrive(&empty_bar[stage]);
+  }
+
+  // acc >= 0 always (chi2 >= 0, c2 >= 0), so the IEEE bit pattern orders like the value
+#pragma unroll
+  for (int q = 0; q < 2 * kNPair; ++q) {
+    if (smin[q] < kInf) atomicMin(starmin + star0 + q * kDenseThreads + tid, __float_as_uint(smin[q]));
+  }
+}
+
+template <int NB>
+static int launch_dense(int64_t n_tiles, const float* tiles, int64_t ld_star, const float* flux,
+                        float* gmin, float* starmin, int tiles_per_item, cudaStream_t st) {
+  auto kern = dense_chi2_kernel<NB>;
+  static bool configured[64] = {};
+  int dev = 0;
+  BF_CUDA_TRY(cudaGetDevice(&dev));
+  if (dev < 64 && !configured[dev]) {
+    BF_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                     DenseSmem<NB>::kBytes));
+    configured[dev] = true;
+  }
+  const int64_t n_items = (n_tiles + tiles_per_item - 1) / tiles_per_item;
+  dim3 grid(static_cast<unsigned>(n_items), static_cast<unsigned>(ld_star / BF_STAR_BLOCK));
+  kern<<<grid, kDenseThreads, DenseSmem<NB>::kBytes, st>>>(
+      tiles, n_tiles, tiles_per_item, flux, ld_star, gmin, reinterpret_cast<unsigned int*>(starmin));
+  BF_CHECK_LAUNCH("dense_chi2_kernel");
+  return BF_OK;
+}
+
+}  // namespace bf
+
+extern "C" int bf_dense_tiles_per_item(int64_t n_tiles, int64_t n_stars, int sm_count) {
+  if (n_tiles <= 0 || n_stars <= 0 || sm_count <= 0) return 1;
+  const int64_t star_blocks = (n_stars + BF_STAR_BLOCK - 1) / BF_STAR_BLOCK;
+  // aim for ~12 waves of 3 resident blocks per SM, at least 4 tiles per item
+  const int64_t want_items = 12LL * 3 * sm_count;
+  int64_t slices = (want_items + star_blocks - 1) / star_blocks;
+  if (slices < 1) slices = 1;
+  int64_t tpi = (n_tiles + slices - 1) / slices;
+  if (tpi < 4) tpi = 4;
+  if (tpi > n_tiles) tpi = n_tiles;
+  return static_cast<int>(tpi);
+}
+
+extern "C" int bf_dense_chi2(int nb, int64_t n_tiles, const float* tiles, int64_t n_stars,
+                             int64_t ld_star, const float* flux, float* gmin, float* starmin,
+                             int tiles_per_item, void* stream) {
+  using namespace bf;
+  BF_REQUIRE(nb >= 1 && nb <= BF_MAX_BANDS, "bf_dense_chi2: nb=%d out of range", nb);
+  BF_REQUIRE(n_tiles > 0 && n_stars > 0, "bf_dense_chi2: empty problem");
+  BF_REQUIRE(ld_star >= n_stars && ld_star % BF_STAR_BLOCK == 0,
+             "bf_dense_chi2: ld_star must be a multiple of %d and >= n_stars", BF_STAR_BLOCK);
+  BF_REQUIRE(tiles_per_item > 0, "bf_dense_chi2: tiles_per_item must be positive");
+  BF_REQUIRE(tiles && flux && gmin && starmin, "bf_dense_chi2: null pointer");
+  BF_REQUIRE(ld_star / BF_STAR_BLOCK <= 65535, "bf_dense_chi2: too many stars per call");
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  switch (nb) {
+#define BF_CASE(N) \
+  case N:          \
+    return launch_dense<N>(n_tiles, tiles, ld_star, flux, gmin, starmin, tiles_per_item, st);
+    BF_CASE(1) BF_CASE(2) BF_CASE(3) BF_CASE(4) BF_CASE(5) BF_CASE(6) BF_CASE(7) BF_CASE(8)
+    BF_CASE(9) BF_CASE(10) BF_CASE(11) BF_CASE(12)
+#undef BF_CASE
+    default:
+      set_error("bf_dense_chi2: nb=%d not instantiated (1..12)", nb);
+      return BF_ERR_UNSUPPORTED;
+  }
+}

@@ -1,0 +1,199 @@
+/*
+ * beast_b200 -- C ABI of the B200-native BEAST fitting hot path.
+ *
+ * This is the drop-in boundary: a plain C interface (pointers + sizes, no torch
+ * types) over hand-written sm_100a kernels.  Every entry point is asynchronous
+ * on the CUDA stream it is given (pass the raw cudaStream_t as void*; NULL = the
+ * legacy default stream), takes caller-owned DEVICE pointers unless a parameter
+ * says "host", allocates nothing, and returns 0 on success or a negative
+ * bf_status code; bf_last_error() returns a message for the calling thread.
+ *
+ * The reference has no FFI of its own (it is pure NumPy); each entry point
+ * cites the reference code (relative to beast/) whose per-star work it
+ * replaces.  The Python side (beast_b200/fit.py) keeps the reference's
+ * summary_table_memory / Q_all_memory signatures and calls these through ctypes.
+ *
+ * Index spaces
+ *   "model j"  : row of the weight>0 filtered grid (fit.py:402, g0_indxs), padded
+ *                up to a multiple of BF_TILE_MODELS with never-selected rows.
+ *   "group"    : BF_GROUP consecutive models; the dense pass reports one minimum
+ *                per (star, group).
+ *   "chunk"    : 8 consecutive models; the unit of the per-parameter tables.
+ */
+#ifndef BEAST_B200_H
+#define BEAST_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define BF_TILE_MODELS 256 /* models per TMA-staged shared-memory tile            */
+#define BF_GROUP 64        /* models per group minimum                            */
+#define BF_CHUNK 8         /* models per parameter-table chunk                    */
+#define BF_STAR_BLOCK 1024 /* stars per thread block of the dense pass            */
+#define BF_MAX_BANDS 16
+#define BF_MAX_PARAMS 128
+#define BF_SELECT_SPLIT 16 /* model-axis splits of the group-selection pass       */
+
+typedef enum {
+  BF_OK = 0,
+  BF_ERR_INVALID = -1,   /* bad argument                                        */
+  BF_ERR_CUDA = -2,      /* a CUDA runtime call failed; see bf_last_error()     */
+  BF_ERR_UNSUPPORTED = -3,
+  BF_ERR_TOO_LARGE = -4
+} bf_status;
+
+const char* bf_last_error(void);
+int bf_version(void);
+
+/* SM count, shared memory per block (opt-in) and SM clock (kHz) of `device`. */
+int bf_device_info(int device, int* sm_count, int* smem_optin_bytes, int* clock_khz);
+
+/* ---------------------------------------------------------------------------
+ * Dense pass -- replaces the per-star N_logLikelihood_NM / N_chi2_NM sweep over
+ * all models (fitting/fit_metrics/likelihood.py:24-55, 109-167; fit.py:657-668).
+ *
+ * tiles : [n_tiles][2*nb+1][BF_TILE_MODELS] float.  Row b (<nb) = r_b = s_b/sigma_b,
+ *         row nb+b = -a_b = -(sed_b+bias_b)/sigma_b, row 2nb = c2 = -2*(c - c_off)
+ *         with c = -lnQ + ln w (star-independent part of lnP).  Padding models
+ *         carry c2 = 3e38.  (s_b = per-band scale so that values are O(1).)
+ * flux  : [nb][ld_star] float, observed flux / s_b, star-fastest.
+ * gmin  : out [n_tiles*BF_TILE_MODELS/BF_GROUP][ld_star] float,
+ *         min over the group of  acc = chi2 + c2  (= -2 (lnP - c_off)) in FP32.
+ * starmin : in/out [ld_star] float, atomically lowered to min over all models
+ *         (caller initialises to +inf bits / 0x7f800000).
+ * ld_star must be a multiple of BF_STAR_BLOCK and >= n_stars.
+ * ------------------------------------------------------------------------- */
+int bf_dense_chi2(int nb, int64_t n_tiles, const float* tiles, int64_t n_stars,
+                  int64_t ld_star, const float* flux, float* gmin, float* starmin,
+                  int tiles_per_item, void* stream);
+
+/* Suggested tiles_per_item for a device with `sm_count` SMs. */
+int bf_dense_tiles_per_item(int64_t n_tiles, int64_t n_stars, int sm_count);
+
+/* ---------------------------------------------------------------------------
+ * Group selection -- the conservative superset of fit.py:670
+ *   indx = where(lnp - max(lnp) > threshold)
+ * at group granularity: group g is kept for star s when
+ *   gmin[g][s] < starmin[s] + tau        (tau = -2*threshold + FP32 margin).
+ * counts : out [n_stars][BF_SELECT_SPLIT] uint32 (bf_select_count)
+ * offsets: in  [n_stars*BF_SELECT_SPLIT + 1] uint32 exclusive scan of counts
+ * list   : out group ids, ascending per star (bf_select_fill)
+ * ------------------------------------------------------------------------- */
+int bf_select_count(int64_t n_groups, int64_t n_stars, int64_t ld_star, const float* gmin,
+                    const float* starmin, float tau, uint32_t* counts, void* stream);
+int bf_select_fill(int64_t n_groups, int64_t n_stars, int64_t ld_star, const float* gmin,
+                   const float* starmin, float tau, const uint32_t* offsets, uint32_t* list,
+                   void* stream);
+
+/* Exclusive prefix sum of n uint32 (out[n] = total).  scratch: >= bf_scan_scratch_elems(n)
+ * uint32.  Plumbing for the variable-length per-star lists. */
+int64_t bf_scan_scratch_elems(int64_t n);
+int bf_exclusive_scan_u32(int64_t n, const uint32_t* in, uint32_t* out, uint32_t* scratch,
+                          void* stream);
+
+/* ---------------------------------------------------------------------------
+ * Exact (FP64) grid, band-major, ld_model = padded model count:
+ *   msb  [nb][ld_model]  seds+bias            (fit.py:463)
+ *   ivar [nb][ld_model]  1/error^2            (fit.py:444)
+ *   lnq  [ld_model]      n/2 ln 2pi - 1/2 sum ln ivar   (likelihood.py:149-159)
+ *   lnw  [ld_model]      ln weight [- ln sum weight]    (fit.py:411-415)
+ * lnP = (-lnq - 0.5*chi2) + lnw, evaluated in the reference's operation order.
+ * ------------------------------------------------------------------------- */
+typedef struct {
+  int nb;
+  int64_t n_models; /* real (unpadded) filtered models */
+  int64_t ld_model;
+  const double* msb;
+  const double* ivar;
+  const double* lnq;
+  const double* lnw;
+} bf_exact_grid;
+
+/* Exact per-star maximum of lnP and its first index (fit.py:670, 684, 719, 727):
+ * evaluates only groups with gmin < starmin + tau_tight.
+ * flux64 [n_stars][nb] double.  pmax [n_stars] double, pmax_j [n_stars] int64 (filtered index,
+ * -1 when the star has no finite lnP). */
+int bf_exact_max(const bf_exact_grid* grid, int64_t n_stars, int64_t ld_star,
+                 const double* flux64, const float* gmin, const float* starmin, float tau_tight,
+                 const uint32_t* offsets, const uint32_t* list, double* pmax, int64_t* pmax_j,
+                 void* stream);
+
+/* ---------------------------------------------------------------------------
+ * Per-parameter tables for the marginal PDFs / expectations, chunk-major:
+ *   bin_tab [ld_model/8][n_q][8] uint8   0-based pdf1d bin of each model
+ *                                        (np.digitize result, pdf1d.py:90)
+ *   q_tab   [ld_model/8][n_q][8] double  parameter value of each model (fit.py:733-737)
+ *   bin_off [n_q+1] int32                start of parameter k's bins in a star's pdf row
+ *   bin_val [bin_off[n_q]] double        bin centres (pdf1d.bin_vals)
+ * ------------------------------------------------------------------------- */
+typedef struct {
+  int n_q;
+  int total_bins;
+  const uint8_t* bin_tab;
+  const double* q_tab;
+  const int32_t* bin_off;
+  const double* bin_val;
+} bf_param_tables;
+
+typedef struct {
+  double* total_log_norm; /* [n_stars]            fit.py:716                       */
+  double* chi2min;        /* [n_stars]            fit.py:725                       */
+  int64_t* chi2min_j;     /* [n_stars] filtered   fit.py:726                       */
+  uint32_t* n_sparse;     /* [n_stars]  size of the sparse set                     */
+  double* exp_vals;       /* [n_stars][n_q]       fit.py:743, common.py:126-167    */
+  double* pdf1d;          /* [n_stars][total_bins] fit.py:746-748, pdf1d.py:119-148*/
+  double* per_vals;       /* [n_stars][n_q][3]    fit.py:749-755, common.py:48-123 */
+  uint32_t* member_mask;  /* [n_list][BF_GROUP/32] membership bits per listed group */
+  uint32_t* member_prefix;/* [n_list] members of the star before this group        */
+} bf_star_outputs;
+
+/* Sparse pass: exact sparse set, weights, normalisation, chi2min, expectations, 1D PDFs
+ * and p16/p50/p84 (fit.py:670-755).  percentiles [3] host doubles in percent. */
+int bf_exact_accumulate(const bf_exact_grid* grid, const bf_param_tables* params,
+                        int64_t n_stars, const double* flux64, const double* pmax,
+                        double threshold, const uint32_t* offsets, const uint32_t* list,
+                        const double* percentiles_host, const bf_star_outputs* out, void* stream);
+
+/* Sparse lnP record (fit.py:693-709): for star s, entries [rec_off[s], rec_off[s+1]) of
+ * `ranks` hold 0-based positions inside the star's ascending sparse set; outputs the filtered
+ * model index, lnP and chi2 of each (float32 like the reference stores them). */
+int bf_sparse_gather(const bf_exact_grid* grid, int64_t n_stars, const double* flux64,
+                     const uint32_t* offsets, const uint32_t* list, const uint32_t* member_mask,
+                     const uint32_t* member_prefix, const int64_t* rec_off, const uint32_t* ranks,
+                     int64_t* out_j, float* out_lnp, float* out_chi2, void* stream);
+
+/* ---------------------------------------------------------------------------
+ * 2D PDFs (fitting/pdf2d.py:122-148, fit.py:758-762).
+ *   pair_bin [n_pairs][ld_model] int32  flattened (b1*nb2+b2) bin, -1 = outside
+ *   pair_off [n_pairs+1] int64          start of pair p inside a star's pdf2d row
+ *   pdf2d    [n_stars][pair_off[n_pairs]] double, must be zero on entry
+ * ------------------------------------------------------------------------- */
+int bf_pdf2d_accumulate(const bf_exact_grid* grid, int n_pairs, const int32_t* pair_bin,
+                        const int64_t* pair_off, int64_t n_stars, const double* flux64,
+                        const double* pmax, const double* total_log_norm, double threshold,
+                        const uint32_t* offsets, const uint32_t* list, double* pdf2d,
+                        void* stream);
+
+/* ---------------------------------------------------------------------------
+ * Subgrid merge (tools/subgridding_tools.py:392-527), device part.  Each rank holds the
+ * results of its own subgrid for the same stars; after the caller all-gathers
+ * total_log_norm / Pmax into [n_sub][n_stars] arrays these kernels produce the merged rows.
+ * ------------------------------------------------------------------------- */
+/* weight_g = exp(tln_g - max_g tln_g); merged_tln = ln sum_g weight_g + max (:394-406, 513) */
+int bf_merge_weights(int n_sub, int64_t n_stars, const double* tln_all, double* weight_all,
+                     double* merged_tln, void* stream);
+/* in place: rows[s][:] *= weight[s]   (the scaling that feeds the cross-rank sum, :421-426) */
+int bf_scale_rows(int64_t n_stars, int64_t row_len, const double* weight, double* rows,
+                  void* stream);
+/* after the cross-rank sum: normalise each parameter's pdf to unit sum where positive
+ * (:428-434) and recompute the percentiles from the merged pdf (:472-491). */
+int bf_merge_finalize(const bf_param_tables* params, int64_t n_stars, double* pdf1d,
+                      const double* percentiles_host, double* per_vals, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* BEAST_B200_H */
