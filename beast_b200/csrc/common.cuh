@@ -109,6 +109,15 @@ __device__ __forceinline__ float min3(float a, float b, float c) {
   return d;
 }
 
+// Selection threshold on the FP32 accumulator scale: x = starmin + tau widened by the
+// worst-case FP32 rounding error of acc for models with chi2 <= x,
+//   |acc32 - acc| <= err_a * sqrt(x) + err_b * x      (derivation: DESIGN.md, "margins").
+__device__ __forceinline__ float select_threshold(float starmin, float tau, float err_a,
+                                                  float err_b) {
+  const float x = starmin + tau;
+  return x + 2.0f * (err_a * sqrtf(fmaxf(x, 0.0f)) + err_b * x) + 1e-6f;
+}
+
 __device__ __forceinline__ int lane_id() { return threadIdx.x & 31; }
 
 }  // namespace bf

@@ -1,0 +1,25 @@
+// Exact FP64 likelihood of one model, shared by the exact-pass kernels.
+#pragma once
+
+#include "common.cuh"
+
+namespace bf {
+
+constexpr int kWordsPerGroup = BF_GROUP / 32;
+
+// exact lnP / chi2 of model j for the star whose flux sits in shared memory
+__device__ __forceinline__ void exact_lnp(const bf_exact_grid& g, const double* sflux, int64_t j,
+                                          double& lnp, double& chi2) {
+  double acc = 0.0;
+  for (int b = 0; b < g.nb; ++b) {
+    const double d = __dsub_rn(sflux[b], g.msb[static_cast<int64_t>(b) * g.ld_model + j]);
+    const double dd = __dmul_rn(d, d);
+    acc = __dadd_rn(acc, __dmul_rn(dd, g.ivar[static_cast<int64_t>(b) * g.ld_model + j]));
+  }
+  chi2 = acc;
+  lnp = __dadd_rn(__dsub_rn(-g.lnq[j], __dmul_rn(0.5, acc)), g.lnw[j]);
+}
+
+__device__ __forceinline__ bool is_finite(double x) { return fabs(x) <= 1.7976931348623157e308; }
+
+}  // namespace bf

@@ -17,7 +17,8 @@ constexpr int kSelThreads = 128;
 template <bool FILL>
 __global__ void __launch_bounds__(kSelThreads)
 select_kernel(int64_t n_groups, int64_t n_stars, int64_t ld_star, const float* __restrict__ gmin,
-              const float* __restrict__ starmin, float tau, uint32_t* __restrict__ counts,
+              const float* __restrict__ starmin, float tau, float err_a, float err_b,
+              uint32_t* __restrict__ counts,
               const uint32_t* __restrict__ offsets, uint32_t* __restrict__ list) {
   const int64_t s = static_cast<int64_t>(blockIdx.x) * kSelThreads + threadIdx.x;
   if (s >= n_stars) return;
@@ -25,7 +26,7 @@ select_kernel(int64_t n_groups, int64_t n_stars, int64_t ld_star, const float* _
   const int64_t per = (n_groups + BF_SELECT_SPLIT - 1) / BF_SELECT_SPLIT;
   const int64_t g0 = c * per;
   const int64_t g1 = min(n_groups, g0 + per);
-  const float thr = starmin[s] + tau;
+  const float thr = select_threshold(starmin[s], tau, err_a, err_b);
   const float* p = gmin + s;
   uint32_t n = 0;
   uint32_t pos = FILL ? offsets[s * BF_SELECT_SPLIT + c] : 0u;
@@ -151,26 +152,27 @@ static int run_scan(int64_t n, const uint32_t* in, uint32_t* out, uint32_t* scra
 
 extern "C" int bf_select_count(int64_t n_groups, int64_t n_stars, int64_t ld_star,
                                const float* gmin, const float* starmin, float tau,
-                               uint32_t* counts, void* stream) {
+                               float err_a, float err_b, uint32_t* counts, void* stream) {
   using namespace bf;
   BF_REQUIRE(n_groups > 0 && n_stars > 0 && ld_star >= n_stars, "bf_select_count: bad sizes");
   BF_REQUIRE(gmin && starmin && counts, "bf_select_count: null pointer");
   dim3 grid(static_cast<unsigned>((n_stars + kSelThreads - 1) / kSelThreads), BF_SELECT_SPLIT);
   select_kernel<false><<<grid, kSelThreads, 0, static_cast<cudaStream_t>(stream)>>>(
-      n_groups, n_stars, ld_star, gmin, starmin, tau, counts, nullptr, nullptr);
+      n_groups, n_stars, ld_star, gmin, starmin, tau, err_a, err_b, counts, nullptr, nullptr);
   BF_CHECK_LAUNCH("select_kernel<count>");
   return BF_OK;
 }
 
 extern "C" int bf_select_fill(int64_t n_groups, int64_t n_stars, int64_t ld_star,
                               const float* gmin, const float* starmin, float tau,
-                              const uint32_t* offsets, uint32_t* list, void* stream) {
+                              float err_a, float err_b, const uint32_t* offsets,
+                              uint32_t* list, void* stream) {
   using namespace bf;
   BF_REQUIRE(n_groups > 0 && n_stars > 0 && ld_star >= n_stars, "bf_select_fill: bad sizes");
   BF_REQUIRE(gmin && starmin && offsets && list, "bf_select_fill: null pointer");
   dim3 grid(static_cast<unsigned>((n_stars + kSelThreads - 1) / kSelThreads), BF_SELECT_SPLIT);
   select_kernel<true><<<grid, kSelThreads, 0, static_cast<cudaStream_t>(stream)>>>(
-      n_groups, n_stars, ld_star, gmin, starmin, tau, nullptr, offsets, list);
+      n_groups, n_stars, ld_star, gmin, starmin, tau, err_a, err_b, nullptr, offsets, list);
   BF_CHECK_LAUNCH("select_kernel<fill>");
   return BF_OK;
 }

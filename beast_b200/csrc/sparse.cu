@@ -1,0 +1,137 @@
+// Sparse lnP records and 2D PDFs: both walk the membership bits the sparse pass left
+// behind (member_mask / member_prefix) and re-evaluate the exact lnP of the members.
+//
+//   bf_sparse_gather    -> the (idx, lnp, chi2) triples the reference appends to
+//                          save_lnp_vals (beast/fitting/fit.py:693-709)
+//   bf_pdf2d_accumulate -> pdf2d.gen2d for every parameter pair
+//                          (beast/fitting/pdf2d.py:122-148, fit.py:758-762)
+
+#include "exact.cuh"
+
+namespace bf {
+
+constexpr int kGatherThreads = 128;
+
+__global__ void __launch_bounds__(kGatherThreads)
+sparse_gather_kernel(bf_exact_grid grid, const double* __restrict__ flux64,
+                     const uint32_t* __restrict__ offsets, const uint32_t* __restrict__ list,
+                     const uint32_t* __restrict__ member_mask,
+                     const uint32_t* __restrict__ member_prefix,
+                     const int64_t* __restrict__ rec_off, const uint32_t* __restrict__ ranks,
+                     int64_t* __restrict__ out_j, float* __restrict__ out_lnp,
+                     float* __restrict__ out_chi2) {
+  __shared__ double sflux[BF_MAX_BANDS];
+  const int64_t s = blockIdx.x;
+  if (threadIdx.x < grid.nb) sflux[threadIdx.x] = flux64[s * grid.nb + threadIdx.x];
+  __syncthreads();
+  const uint32_t e0 = offsets[s * BF_SELECT_SPLIT];
+  const uint32_t e1 = offsets[(s + 1) * BF_SELECT_SPLIT];
+  const int64_t r0 = rec_off[s], r1 = rec_off[s + 1];
+  for (int64_t r = r0 + threadIdx.x; r < r1; r += kGatherThreads) {
+    const uint32_t rank = ranks ? ranks[r] : static_cast<uint32_t>(r - r0);
+    // last entry whose exclusive prefix is <= rank
+    uint32_t lo = e0, hi = e1;  // invariant: prefix[lo] <= rank, answer in [lo, hi)
+    while (hi - lo > 1) {
+      const uint32_t mid = lo + (hi - lo) / 2;
+      if (member_prefix[mid] <= rank) lo = mid; else hi = mid;
+    }
+    uint32_t local = rank - member_prefix[lo];
+    int64_t j = -1;
+#pragma unroll
+    for (int h = 0; h < kWordsPerGroup; ++h) {
+      const uint32_t word = member_mask[static_cast<size_t>(lo) * kWordsPerGroup + h];
+      const uint32_t c = __popc(word);
+      if (j < 0) {
+        if (local < c) {
+          const int bit = __fns(word, 0, static_cast<int>(local) + 1);
+          j = static_cast<int64_t>(list[lo]) * BF_GROUP + h * 32 + bit;
+        } else {
+          local -= c;
+        }
+      }
+    }
+    double lnp = 0.0, chi2 = 0.0;
+    if (j >= 0) exact_lnp(grid, sflux, j, lnp, chi2);
+    out_j[r] = j;
+    out_lnp[r] = static_cast<float>(lnp);
+    out_chi2[r] = static_cast<float>(chi2);
+  }
+}
+
+// one warp per listed group; weights are already normalised: exp(lnp - total_log_norm)
+constexpr int kPdf2dWarps = 8;
+
+__global__ void __launch_bounds__(kPdf2dWarps * 32)
+pdf2d_kernel(bf_exact_grid grid, int n_pairs, const int32_t* __restrict__ pair_bin,
+             const int64_t* __restrict__ pair_off, const double* __restrict__ flux64,
+             const double* __restrict__ pmax, const double* __restrict__ tln, double threshold,
+             const uint32_t* __restrict__ offsets, const uint32_t* __restrict__ list,
+             double* __restrict__ pdf2d) {
+  __shared__ double sflux[BF_MAX_BANDS];
+  const int64_t s = blockIdx.x;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  if (threadIdx.x < grid.nb) sflux[threadIdx.x] = flux64[s * grid.nb + threadIdx.x];
+  __syncthreads();
+  const double M = pmax[s];
+  const double norm = tln[s];
+  const uint32_t e0 = offsets[s * BF_SELECT_SPLIT];
+  const uint32_t e1 = offsets[(s + 1) * BF_SELECT_SPLIT];
+  const int64_t row_len = pair_off[n_pairs];
+  double* row = pdf2d + s * row_len;
+  for (uint32_t e = e0 + warp; e < e1; e += kPdf2dWarps) {
+    const uint32_t g = list[e];
+#pragma unroll
+    for (int h = 0; h < kWordsPerGroup; ++h) {
+      const int64_t j = static_cast<int64_t>(g) * BF_GROUP + h * 32 + lane;
+      if (j >= grid.n_models) continue;
+      double lnp, chi2;
+      exact_lnp(grid, sflux, j, lnp, chi2);
+      if (!((lnp - M) > threshold)) continue;
+      const double w = exp(lnp - norm);
+      for (int p = 0; p < n_pairs; ++p) {
+        const int32_t b = pair_bin[static_cast<int64_t>(p) * grid.ld_model + j];
+        if (b >= 0) atomicAdd(row + pair_off[p] + b, w);
+      }
+    }
+  }
+}
+
+}  // namespace bf
+
+extern "C" int bf_sparse_gather(const bf_exact_grid* grid, int64_t n_stars, const double* flux64,
+                                const uint32_t* offsets, const uint32_t* list,
+                                const uint32_t* member_mask, const uint32_t* member_prefix,
+                                const int64_t* rec_off, const uint32_t* ranks, int64_t* out_j,
+                                float* out_lnp, float* out_chi2, void* stream) {
+  using namespace bf;
+  BF_REQUIRE(grid && grid->nb >= 1 && grid->nb <= BF_MAX_BANDS, "bf_sparse_gather: bad grid");
+  BF_REQUIRE(n_stars > 0 && n_stars < (1LL << 31), "bf_sparse_gather: bad n_stars");
+  BF_REQUIRE(flux64 && offsets && list && member_mask && member_prefix && rec_off && out_j &&
+                 out_lnp && out_chi2,
+             "bf_sparse_gather: null pointer");
+  sparse_gather_kernel<<<static_cast<unsigned>(n_stars), kGatherThreads, 0,
+                         static_cast<cudaStream_t>(stream)>>>(
+      *grid, flux64, offsets, list, member_mask, member_prefix, rec_off, ranks, out_j, out_lnp,
+      out_chi2);
+  BF_CHECK_LAUNCH("sparse_gather_kernel");
+  return BF_OK;
+}
+
+extern "C" int bf_pdf2d_accumulate(const bf_exact_grid* grid, int n_pairs, const int32_t* pair_bin,
+                                   const int64_t* pair_off, int64_t n_stars, const double* flux64,
+                                   const double* pmax, const double* total_log_norm,
+                                   double threshold, const uint32_t* offsets, const uint32_t* list,
+                                   double* pdf2d, void* stream) {
+  using namespace bf;
+  BF_REQUIRE(grid && grid->nb >= 1 && grid->nb <= BF_MAX_BANDS, "bf_pdf2d_accumulate: bad grid");
+  BF_REQUIRE(n_pairs >= 1, "bf_pdf2d_accumulate: n_pairs must be >= 1");
+  BF_REQUIRE(n_stars > 0 && n_stars < (1LL << 31), "bf_pdf2d_accumulate: bad n_stars");
+  BF_REQUIRE(pair_bin && pair_off && flux64 && pmax && total_log_norm && offsets && list && pdf2d,
+             "bf_pdf2d_accumulate: null pointer");
+  pdf2d_kernel<<<static_cast<unsigned>(n_stars), kPdf2dWarps * 32, 0,
+                 static_cast<cudaStream_t>(stream)>>>(
+      *grid, n_pairs, pair_bin, pair_off, flux64, pmax, total_log_norm, threshold, offsets, list,
+      pdf2d);
+  BF_CHECK_LAUNCH("pdf2d_kernel");
+  return BF_OK;
+}

@@ -1,0 +1,284 @@
+"""
+Device-side driver of the fitting hot path: owns the resident grid (torch tensors as
+plain device buffers) and runs the kernel pipeline of ``include/beast_b200.h`` on
+batches of stars.
+
+    dense FP32 sweep  ->  group selection  ->  exact FP64 max  ->  exact sparse pass
+    (bf_dense_chi2)      (bf_select_*)        (bf_exact_max)      (bf_exact_accumulate)
+                                                         [-> bf_pdf2d_accumulate, bf_sparse_gather]
+
+This is the star loop of the reference (``beast/fitting/fit.py:637-762``) for a whole
+batch at once.  PyTorch is used for allocation, streams and host<->device copies only.
+"""
+
+from __future__ import annotations
+
+import ctypes as C
+
+import numpy as np
+
+from . import _cabi
+from ._cabi import GROUP, SELECT_SPLIT, STAR_BLOCK, ExactGrid, ParamTables, StarOutputs
+
+_INF_BITS = 0x7F800000
+
+
+def _torch():
+    import torch
+
+    return torch
+
+
+def _ptr(t):
+    return C.c_void_p(t.data_ptr()) if t is not None else C.c_void_p(0)
+
+
+class FitResult:
+    """Per-star outputs of one ``FitEngine.fit`` call (host NumPy arrays).
+
+    Index arrays are in *filtered* model space (``j``); ``FitSetup.g0_indxs[j]`` maps to
+    full-grid indices as the reference reports them (fit.py:719-728)."""
+
+    def __init__(self, ns, nq, total_bins, pair_len=0):
+        self.Pmax = np.zeros(ns)
+        self.Pmax_j = np.full(ns, -1, dtype=np.int64)
+        self.total_log_norm = np.zeros(ns)
+        self.chi2min = np.zeros(ns)
+        self.chi2min_j = np.full(ns, -1, dtype=np.int64)
+        self.n_sparse = np.zeros(ns, dtype=np.int64)
+        self.n_groups_selected = np.zeros(ns, dtype=np.int64)
+        self.exp_vals = np.zeros((ns, nq))
+        self.per_vals = np.zeros((ns, nq, 3))
+        self.pdf1d = np.zeros((ns, total_bins))
+        self.pdf2d = np.zeros((ns, pair_len)) if pair_len else None
+        self.sparse_off = None  # int64 [ns+1]
+        self.sparse_j = None  # int64 filtered indices
+        self.sparse_lnp = None  # float32
+        self.sparse_chi2 = None  # float32
+
+
+class FitEngine:
+    """Grid resident in HBM + the batched fit pipeline.
+
+    Parameters
+    ----------
+    setup : gridprep.FitSetup
+    device : int or torch.device, default: current CUDA device
+    gmin_budget_bytes : size cap of the (group x star) minimum map of one batch
+    """
+
+    def __init__(self, setup, device=None, gmin_budget_bytes=8 << 30):
+        torch = _torch()
+        self.lib = _cabi.load()
+        if not torch.cuda.is_available():
+            raise RuntimeError("beast_b200.FitEngine needs a CUDA device (sm_100a); there is no CPU fallback")
+        self.device = torch.device("cuda", torch.cuda.current_device()) if device is None else torch.device(device)
+        if self.device.type != "cuda":
+            raise RuntimeError("beast_b200.FitEngine: device must be a CUDA device")
+        self.setup = setup
+        sm, smem, khz = C.c_int(), C.c_int(), C.c_int()
+        idx = self.device.index if self.device.index is not None else torch.cuda.current_device()
+        _cabi.check(self.lib.bf_device_info(idx, C.byref(sm), C.byref(smem), C.byref(khz)), "bf_device_info")
+        self.sm_count, self.clock_khz = sm.value, khz.value
+
+        def up(a):
+            return torch.from_numpy(np.ascontiguousarray(a)).to(self.device)
+
+        s = setup
+        with torch.cuda.device(self.device):
+            self.d_tiles = up(s.tiles)
+            self.d_msb, self.d_ivar = up(s.msb), up(s.ivar)
+            self.d_lnq, self.d_lnw = up(s.lnq), up(s.lnw)
+            self.d_bin_tab, self.d_q_tab = up(s.bin_tab), up(s.q_tab)
+            self.d_bin_off, self.d_bin_val = up(s.bin_off), up(s.bin_val)
+            self.d_inv_scale = up((1.0 / s.band_scale).astype(np.float64))
+            if s.pair_bin is not None:
+                self.d_pair_bin, self.d_pair_off = up(s.pair_bin), up(s.pair_off)
+            else:
+                self.d_pair_bin = self.d_pair_off = None
+        self.grid = ExactGrid(s.nb, s.n_models, s.ld_model, self.d_msb.data_ptr(),
+                              self.d_ivar.data_ptr(), self.d_lnq.data_ptr(), self.d_lnw.data_ptr())
+        self.params = ParamTables(s.n_q, s.total_bins, self.d_bin_tab.data_ptr(),
+                                  self.d_q_tab.data_ptr(), self.d_bin_off.data_ptr(),
+                                  self.d_bin_val.data_ptr())
+        per_star = s.n_groups * 4
+        mb = max(STAR_BLOCK, (gmin_budget_bytes // per_star) // STAR_BLOCK * STAR_BLOCK)
+        mb = min(mb, ((2**31 - 1) // max(s.n_groups, 1)) // STAR_BLOCK * STAR_BLOCK, 32768 * STAR_BLOCK)
+        self.max_batch = int(max(mb, STAR_BLOCK))
+        self.launches = 0  # kernels launched by this engine (bench.py reports it)
+
+    # ------------------------------------------------------------------------------
+    def _stream(self):
+        return C.c_void_p(_torch().cuda.current_stream(self.device).cuda_stream)
+
+    def dense(self, d_flux64, n):
+        """dense sweep of one batch; returns (gmin, starmin, ld_star)"""
+        torch = _torch()
+        s = self.setup
+        ld = (n + STAR_BLOCK - 1) // STAR_BLOCK * STAR_BLOCK
+        f32 = torch.zeros((s.nb, ld), dtype=torch.float32, device=self.device)
+        f32[:, :n] = (d_flux64 * self.d_inv_scale[None, :]).t().to(torch.float32)
+        gmin = torch.empty((s.n_groups, ld), dtype=torch.float32, device=self.device)
+        starmin = torch.full((ld,), float("inf"), dtype=torch.float32, device=self.device)
+        tpi = self.lib.bf_dense_tiles_per_item(s.n_tiles, n, self.sm_count)
+        _cabi.call("bf_dense_chi2", s.nb, s.n_tiles, _ptr(self.d_tiles), n, ld, _ptr(f32),
+                   _ptr(gmin), _ptr(starmin), tpi, self._stream())
+        self.launches += 1
+        return gmin, starmin, ld
+
+    def select(self, gmin, starmin, ld, n, threshold):
+        """group lists of one batch; returns (offsets[n*SPLIT+1], list)"""
+        torch = _torch()
+        s = self.setup
+        tau = float(-2.0 * threshold)
+        nc = n * SELECT_SPLIT
+        counts = torch.empty(nc, dtype=torch.int32, device=self.device)
+        offsets = torch.empty(nc + 1, dtype=torch.int32, device=self.device)
+        scratch = torch.empty(int(self.lib.bf_scan_scratch_elems(nc)), dtype=torch.int32, device=self.device)
+        st = self._stream()
+        _cabi.call("bf_select_count", s.n_groups, n, ld, _ptr(gmin), _ptr(starmin), tau, s.err_a,
+                   s.err_b, _ptr(counts), st)
+        _cabi.call("bf_exclusive_scan_u32", nc, _ptr(counts), _ptr(offsets), _ptr(scratch), st)
+        total = int(offsets[-1].item()) & 0xFFFFFFFF  # the one host sync of a batch
+        lst = torch.empty(max(total, 1), dtype=torch.int32, device=self.device)
+        _cabi.call("bf_select_fill", s.n_groups, n, ld, _ptr(gmin), _ptr(starmin), tau, s.err_a,
+                   s.err_b, _ptr(offsets), _ptr(lst), st)
+        self.launches += 5
+        return offsets, lst, total
+
+    def fit_batch(self, flux, threshold=-10.0, percentiles=(16.0, 50.0, 84.0), want_pdf2d=False,
+                  sparse=None, rng=None):
+        """Fit one batch (<= max_batch stars).  ``flux``: (n, nb) float64 NumPy array or
+        torch tensor (host or device).  Returns a dict of device tensors."""
+        torch = _torch()
+        s = self.setup
+        with torch.cuda.device(self.device):
+            if isinstance(flux, np.ndarray):
+                flux = torch.from_numpy(np.ascontiguousarray(flux, dtype=np.float64))
+            d_flux = flux.to(self.device, dtype=torch.float64, non_blocking=True).contiguous()
+            n = d_flux.shape[0]
+            if n > self.max_batch:
+                raise ValueError("batch of %d stars exceeds max_batch=%d" % (n, self.max_batch))
+            gmin, starmin, ld = self.dense(d_flux, n)
+            offsets, lst, total = self.select(gmin, starmin, ld, n, threshold)
+            st = self._stream()
+            dev = self.device
+            pmax = torch.empty(n, dtype=torch.float64, device=dev)
+            pmax_j = torch.empty(n, dtype=torch.int64, device=dev)
+            _cabi.call("bf_exact_max", C.byref(self.grid), n, ld, _ptr(d_flux), _ptr(gmin),
+                       _ptr(starmin), s.err_a, s.err_b, _ptr(offsets), _ptr(lst), _ptr(pmax),
+                       _ptr(pmax_j), st)
+            del gmin
+            o = {
+                "Pmax": pmax, "Pmax_j": pmax_j,
+                "total_log_norm": torch.empty(n, dtype=torch.float64, device=dev),
+                "chi2min": torch.empty(n, dtype=torch.float64, device=dev),
+                "chi2min_j": torch.empty(n, dtype=torch.int64, device=dev),
+                "n_sparse": torch.empty(n, dtype=torch.int32, device=dev),
+                "exp_vals": torch.empty((n, s.n_q), dtype=torch.float64, device=dev),
+                "pdf1d": torch.empty((n, s.total_bins), dtype=torch.float64, device=dev),
+                "per_vals": torch.empty((n, s.n_q, 3), dtype=torch.float64, device=dev),
+            }
+            mask = torch.empty(max(total, 1) * (GROUP // 32), dtype=torch.int32, device=dev)
+            prefix = torch.empty(max(total, 1), dtype=torch.int32, device=dev)
+            outs = StarOutputs(o["total_log_norm"].data_ptr(), o["chi2min"].data_ptr(),
+                               o["chi2min_j"].data_ptr(), o["n_sparse"].data_ptr(),
+                               o["exp_vals"].data_ptr(), o["pdf1d"].data_ptr(),
+                               o["per_vals"].data_ptr(), mask.data_ptr(), prefix.data_ptr())
+            pct = (C.c_double * 3)(*[float(x) for x in percentiles])
+            _cabi.call("bf_exact_accumulate", C.byref(self.grid), C.byref(self.params), n,
+                       _ptr(d_flux), _ptr(pmax), float(threshold), _ptr(offsets), _ptr(lst), pct,
+                       C.byref(outs), st)
+            self.launches += 2
+            off2 = offsets.view(-1)[:: SELECT_SPLIT]
+            o["n_groups_selected"] = (off2[1:].to(torch.int64) & 0xFFFFFFFF) - (off2[:-1].to(torch.int64) & 0xFFFFFFFF)
+
+            if want_pdf2d and self.d_pair_bin is not None:
+                row = int(s.pair_off[-1])
+                pdf2d = torch.zeros((n, row), dtype=torch.float64, device=dev)
+                _cabi.call("bf_pdf2d_accumulate", C.byref(self.grid), len(s.pairs),
+                           _ptr(self.d_pair_bin), _ptr(self.d_pair_off), n, _ptr(d_flux),
+                           _ptr(pmax), _ptr(o["total_log_norm"]), float(threshold),
+                           _ptr(offsets), _ptr(lst), _ptr(pdf2d), st)
+                self.launches += 1
+                o["pdf2d"] = pdf2d
+
+            if sparse is not None:
+                # sparse = "all" or an int (lnp_npts): random subsample of the sparse set drawn
+                # exactly like the reference does, np.random.choice(indx, size, replace=False)
+                # (fit.py:694-700) -- only the set size matters for the random stream.
+                ns_host = (o["n_sparse"].cpu().numpy().astype(np.int64)) & 0xFFFFFFFF
+                if sparse == "all":
+                    cnt = ns_host
+                    ranks = None
+                else:
+                    npts = int(sparse)
+                    cnt = np.minimum(ns_host, npts)
+                    parts = []
+                    choose = (rng.choice if rng is not None else np.random.choice)
+                    for e in range(n):
+                        if npts < ns_host[e]:
+                            parts.append(np.asarray(choose(int(ns_host[e]), size=npts, replace=False)))
+                        else:
+                            parts.append(np.arange(ns_host[e]))
+                    ranks = np.concatenate(parts).astype(np.int32) if parts else np.zeros(0, np.int32)
+                rec_off = np.zeros(n + 1, dtype=np.int64)
+                rec_off[1:] = np.cumsum(cnt)
+                nrec = int(rec_off[-1])
+                d_rec_off = torch.from_numpy(rec_off).to(dev)
+                d_ranks = torch.from_numpy(ranks).to(dev) if ranks is not None and nrec else None
+                out_j = torch.empty(max(nrec, 1), dtype=torch.int64, device=dev)
+                out_lnp = torch.empty(max(nrec, 1), dtype=torch.float32, device=dev)
+                out_chi2 = torch.empty(max(nrec, 1), dtype=torch.float32, device=dev)
+                if nrec:
+                    _cabi.call("bf_sparse_gather", C.byref(self.grid), n, _ptr(d_flux),
+                               _ptr(offsets), _ptr(lst), _ptr(mask), _ptr(prefix),
+                               _ptr(d_rec_off), _ptr(d_ranks), _ptr(out_j), _ptr(out_lnp),
+                               _ptr(out_chi2), st)
+                    self.launches += 1
+                o["sparse_off"] = rec_off
+                o["sparse_j"], o["sparse_lnp"], o["sparse_chi2"] = out_j[:nrec], out_lnp[:nrec], out_chi2[:nrec]
+            return o
+
+    # ------------------------------------------------------------------------------
+    def fit(self, fluxes, threshold=-10.0, percentiles=(16.0, 50.0, 84.0), want_pdf2d=False,
+            sparse=None, batch=None, rng=None):
+        """Fit all stars of ``fluxes`` (ns, nb) in batches; returns a host ``FitResult``."""
+        torch = _torch()
+        s = self.setup
+        fluxes = np.ascontiguousarray(fluxes, dtype=np.float64)
+        ns = fluxes.shape[0]
+        if fluxes.ndim != 2 or fluxes.shape[1] != s.nb:
+            raise ValueError("fluxes must have shape (n_stars, %d)" % s.nb)
+        bs = min(batch or self.max_batch, self.max_batch)
+        pair_len = int(s.pair_off[-1]) if (want_pdf2d and s.pair_off is not None) else 0
+        res = FitResult(ns, s.n_q, s.total_bins, pair_len)
+        sp_j, sp_l, sp_c, sp_cnt = [], [], [], []
+        for a in range(0, ns, bs):
+            b = min(ns, a + bs)
+            o = self.fit_batch(fluxes[a:b], threshold, percentiles, want_pdf2d, sparse, rng)
+            res.Pmax[a:b] = o["Pmax"].cpu().numpy()
+            res.Pmax_j[a:b] = o["Pmax_j"].cpu().numpy()
+            res.total_log_norm[a:b] = o["total_log_norm"].cpu().numpy()
+            res.chi2min[a:b] = o["chi2min"].cpu().numpy()
+            res.chi2min_j[a:b] = o["chi2min_j"].cpu().numpy()
+            res.n_sparse[a:b] = o["n_sparse"].cpu().numpy().astype(np.int64) & 0xFFFFFFFF
+            res.n_groups_selected[a:b] = o["n_groups_selected"].cpu().numpy()
+            res.exp_vals[a:b] = o["exp_vals"].cpu().numpy()
+            res.per_vals[a:b] = o["per_vals"].cpu().numpy()
+            res.pdf1d[a:b] = o["pdf1d"].cpu().numpy()
+            if pair_len:
+                res.pdf2d[a:b] = o["pdf2d"].cpu().numpy()
+            if sparse is not None:
+                sp_cnt.append(np.diff(o["sparse_off"]))
+                sp_j.append(o["sparse_j"].cpu().numpy())
+                sp_l.append(o["sparse_lnp"].cpu().numpy())
+                sp_c.append(o["sparse_chi2"].cpu().numpy())
+        if sparse is not None:
+            res.sparse_off = np.zeros(ns + 1, dtype=np.int64)
+            res.sparse_off[1:] = np.cumsum(np.concatenate(sp_cnt))
+            res.sparse_j = np.concatenate(sp_j)
+            res.sparse_lnp = np.concatenate(sp_l)
+            res.sparse_chi2 = np.concatenate(sp_c)
+        torch.cuda.synchronize(self.device)
+        return res

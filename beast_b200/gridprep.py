@@ -1,0 +1,269 @@
+"""
+Host-side setup of a fit: everything ``Q_all_memory`` prepares before its star
+loop (reference ``beast/fitting/fit.py:396-573``), laid out for the kernels.
+
+What is computed here, once per (grid, noise model, parameter list):
+
+* zero-weight filter ``g0_indxs`` and the log prior weights (fit.py:402, 411-415)
+* completeness check (fit.py:404-409)
+* ``model_seds_with_bias``, ``ivar`` and the symlog "full model flux" parameters
+  (fit.py:444, 456-465; tools/symlog.py:9-28)
+* the 1D bin layout of every parameter and the bin number of every model
+  (fit.py:236-310, pdf1d.py:32-117) -- as one byte per (model, parameter) instead
+  of the reference's per-bin index lists
+* optional 2D bin layouts (fit.py:511-573, pdf2d.py:38-120)
+* the FP32 tiles of the dense pass and the FP64 band-major arrays of the exact pass
+  (layouts: include/beast_b200.h)
+
+Nothing here touches CUDA; ``engine.FitEngine`` uploads the arrays.
+"""
+
+from __future__ import annotations
+
+import math
+import warnings
+
+import numpy as np
+
+from ._cabi import CHUNK, GROUP, MAX_BANDS, MAX_PARAMS, TILE_MODELS
+
+SKIP_KEYS = "osl keep weight grid_weight prior_weight fullgrid_idx stage specgrid_indx phase eep".split()
+LOG_SPACED_PARAMS = {"M_ini", "M_act", "radius"}
+SYMLOG_THRESHOLD = 1e-20
+FP32_U = 2.0**-24
+ERR_SAFETY = 4.0
+
+
+def symlog(y, C=SYMLOG_THRESHOLD):
+    """symmetric log used for the flux parameters (tools/symlog.py:9-28)"""
+    return np.sign(y) * np.log10(1.0 + np.abs(y / C))
+
+
+class ParamBins:
+    """bin centres + 0-based bin number per model of one parameter (pdf1d.py:32-117)"""
+
+    __slots__ = ("name", "nbins", "bin_vals", "bin_num")
+
+    def __init__(self, name, values, nbins, logspacing, minval, maxval, uniqvals):
+        v = np.array(values, dtype=np.float64)
+        lo = v.min() if minval is None else minval
+        hi = v.max() if maxval is None else maxval
+        uniq = np.asarray(uniqvals, dtype=np.float64)
+        if logspacing:
+            lo, hi = math.log10(lo), math.log10(hi)
+            v = np.log10(v)
+            uniq = np.log10(uniq)
+        step = (hi - lo) / (nbins - 1) if nbins > 1 else 1
+        if len(uniq) > nbins:
+            centres = lo + np.arange(nbins) * step
+            edges = lo + (np.arange(nbins + 1) - 0.5) * step
+        else:
+            centres = np.array(uniq)
+            edges = np.zeros(nbins + 1)
+            if nbins > 1:
+                edges[1:-1] = 0.5 * (centres[:-1] + centres[1:])
+                edges[0] = centres[0] - (edges[1] - centres[0])
+                edges[-1] = centres[-1] + (centres[-1] - edges[-2])
+            else:
+                edges[0], edges[1] = 0.95 * centres[0], 1.05 * centres[0]
+        num = np.digitize(v, edges)
+        if np.any((num < 1) | (num > nbins)):
+            raise ValueError(
+                "Not all the physics grid model points mapped to 1d ppdf bins - should not happen"
+            )
+        self.name = name
+        self.nbins = int(nbins)
+        self.bin_num = (num - 1).astype(np.int32)
+        self.bin_vals = np.power(10.0, centres) if logspacing else centres
+
+
+class PairBins:
+    """equal-width 2D bins of a parameter pair (pdf2d.py:38-120); -1 = outside every cell"""
+
+    __slots__ = ("name", "nb1", "nb2", "bin_vals_p1", "bin_vals_p2", "bin_num")
+
+    def __init__(self, name, spec1, spec2):
+        def axis(spec):
+            vals, nbins, logsp, lo, hi, _ = spec
+            v = np.array(vals, dtype=np.float64)
+            lo = v.min() if lo is None else lo
+            hi = v.max() if hi is None else hi
+            if logsp:
+                lo, hi, v = math.log10(lo), math.log10(hi), np.log10(v)
+            step = (hi - lo) / (nbins - 1) if nbins > 1 else 1
+            centres = lo + np.arange(nbins) * step
+            edges = lo + (np.arange(nbins + 1) - 0.5) * step
+            num = np.digitize(v, edges) - 1
+            return (np.power(10.0, centres) if logsp else centres), num, int(nbins)
+
+        c1, n1, self.nb1 = axis(spec1)
+        c2, n2, self.nb2 = axis(spec2)
+        bad = (n1 < 0) | (n1 >= self.nb1) | (n2 < 0) | (n2 >= self.nb2)
+        self.name = name
+        self.bin_vals_p1, self.bin_vals_p2 = c1, c2
+        self.bin_num = np.where(bad, -1, n1 * self.nb2 + n2).astype(np.int32)
+
+
+def _bin_spec(qname, max_nbins, sedgrid, full_model_flux, filters, grid_info_dict):
+    """values, nbins, log spacing, range override, unique values (fit.py:236-310)"""
+    if "_bias" in qname:
+        fname = qname.replace("_wd_bias", "").replace("symlog", "")
+        vals = full_model_flux[:, filters.index(fname)]
+    else:
+        vals = np.asarray(sedgrid[qname])
+    if grid_info_dict is not None and qname in grid_info_dict:
+        info = grid_info_dict[qname]
+        n_uniq, uniq, lo, hi = info["num_unique"], info["unique_vals"], info["min"], info["max"]
+    else:
+        uniq = np.unique(vals)
+        n_uniq, lo, hi = len(uniq), None, None
+    nbins = max_nbins if n_uniq > max_nbins else n_uniq
+    return vals, nbins, qname in LOG_SPACED_PARAMS, lo, hi, uniq
+
+
+def _pad_to(n, mult):
+    return ((n + mult - 1) // mult) * mult
+
+
+class FitSetup:
+    """All star-independent inputs of the kernels, as NumPy arrays."""
+
+    def __init__(self, sedgrid, obsmodel, qnames_in, max_nbins=200, pdf2d_param_list=None,
+                 make_pdf2d=False, grid_info_dict=None, do_not_normalize=False,
+                 use_full_cov_matrix=True):
+        weight = np.asarray(sedgrid["weight"], dtype=np.float64)
+        filters = list(sedgrid.filters)
+        nb = len(filters)
+        if nb > MAX_BANDS:
+            raise NotImplementedError("at most %d bands are supported (got %d)" % (MAX_BANDS, nb))
+        (g0,) = np.where(weight > 0.0)
+        for i in range(nb):
+            if np.any(np.asarray(obsmodel["completeness"])[:, i] <= 0.0):
+                raise ValueError("models with zero completeness present in the observation model")
+        lnw = np.log(weight[g0])
+        if not do_not_normalize:
+            lnw = lnw - np.log(weight[g0].sum())
+        if len(weight) != len(g0):
+            warnings.warn("some zero weight models exist")
+        if (use_full_cov_matrix and "q_norm" in obsmodel and "icov_diag" in obsmodel
+                and "icov_offdiag" in obsmodel):
+            raise NotImplementedError(
+                "full-covariance noise models (q_norm/icov_diag/icov_offdiag, fit.py:432-444) are "
+                "not on the CUDA path yet; pass use_full_cov_matrix=False to fit with the "
+                "diagonal noise model")
+
+        seds = sedgrid.seds.read() if hasattr(sedgrid.seds, "read") else np.asarray(sedgrid.seds)
+        err = np.asarray(obsmodel["error"], dtype=np.float64)
+        msb_full = seds + np.asarray(obsmodel["bias"], dtype=np.float64)
+        ivar_full = 1.0 / err**2
+        full_model_flux = symlog(msb_full)
+
+        self.filters = filters
+        self.lamb = np.asarray(sedgrid.lamb)
+        self.nb = nb
+        self.n_full = len(weight)
+        self.qnames = list(qnames_in) + ["symlog" + f + "_wd_bias" for f in filters]
+        nq = len(self.qnames)
+        if nq > MAX_PARAMS:
+            raise NotImplementedError("at most %d parameters are supported (got %d)" % (MAX_PARAMS, nq))
+        self.specgrid_indx = np.asarray(sedgrid["specgrid_indx"])
+
+        # ---- 1D bins -------------------------------------------------------------
+        self.qcols, self.bins = [], []
+        for q in self.qnames:
+            vals, nbins, logsp, lo, hi, uniq = _bin_spec(
+                q, max_nbins, sedgrid, full_model_flux, filters, grid_info_dict)
+            if nbins > 256:
+                raise NotImplementedError(
+                    "parameter %s needs %d bins; the kernels store bin numbers in one byte "
+                    "(max_nbins <= 256)" % (q, nbins))
+            self.qcols.append(np.asarray(vals, dtype=np.float64))
+            self.bins.append(ParamBins(q, vals, nbins, logsp, lo, hi, uniq))
+        self.bin_off = np.zeros(nq + 1, dtype=np.int32)
+        self.bin_off[1:] = np.cumsum([b.nbins for b in self.bins])
+        self.total_bins = int(self.bin_off[-1])
+        self.bin_val = np.concatenate([b.bin_vals for b in self.bins]).astype(np.float64)
+
+        # ---- 2D bins -------------------------------------------------------------
+        self.pairs = []
+        if make_pdf2d:
+            if pdf2d_param_list is None:
+                raise KeyError("pdf2d_param_list cannot be None if saving 2D PDFs")
+            params = [q for q in self.qnames
+                      if q in pdf2d_param_list and len(np.unique(sedgrid[q])) > 1]
+            specs = {q: _bin_spec(q, max_nbins, sedgrid, full_model_flux, filters, grid_info_dict)
+                     for q in params}
+            for i in range(len(params)):
+                for j in range(i + 1, len(params)):
+                    self.pairs.append(
+                        PairBins(params[i] + "+" + params[j], specs[params[i]], specs[params[j]]))
+
+        # ---- drop models the kernels cannot rank (non-finite constants) -----------
+        lnq = nb * (0.5 * np.log(2.0 * np.pi)) - 0.5 * np.sum(np.log(ivar_full[g0]), axis=1)
+        c = -lnq + lnw
+        ok = np.isfinite(c) & np.isfinite(msb_full[g0]).all(axis=1) & np.isfinite(ivar_full[g0]).all(axis=1)
+        if not ok.all():
+            warnings.warn("%d models with non-finite noise model / flux values are ignored"
+                          % int((~ok).sum()))
+            g0, lnw, lnq, c = g0[ok], lnw[ok], lnq[ok], c[ok]
+        if len(g0) == 0:
+            raise ValueError("no model with positive weight and finite noise model")
+        self.g0_indxs = g0.astype(np.int64)
+        nm = len(g0)
+        nmp = _pad_to(nm, TILE_MODELS)
+        self.n_models, self.ld_model = nm, nmp
+        self.n_tiles = nmp // TILE_MODELS
+        self.n_groups = nmp // GROUP
+
+        # ---- exact FP64 arrays, band-major --------------------------------------
+        msb = np.zeros((nb, nmp))
+        ivar = np.zeros((nb, nmp))
+        msb[:, :nm] = msb_full[g0].T
+        ivar[:, :nm] = ivar_full[g0].T
+        self.msb, self.ivar = msb, ivar
+        self.lnq = np.zeros(nmp)
+        self.lnq[:nm] = lnq
+        self.lnw = np.zeros(nmp)
+        self.lnw[:nm] = lnw
+
+        # ---- FP32 tiles of the dense pass ---------------------------------------
+        inv_sigma = 1.0 / np.abs(err[g0])  # (nm, nb); error may be stored negative
+        scale = np.median(np.abs(msb_full[g0]), axis=0)
+        scale = np.where((scale > 0) & np.isfinite(scale), scale, 1.0)
+        self.band_scale = scale
+        a = msb_full[g0] * inv_sigma
+        self.c_off = float(c.max())
+        rows = np.zeros((2 * nb + 1, nmp), dtype=np.float32)
+        rows[:nb, :nm] = (inv_sigma * scale[None, :]).T
+        rows[nb:2 * nb, :nm] = (-a).T
+        rows[2 * nb, :] = 3.0e38
+        rows[2 * nb, :nm] = -2.0 * (c - self.c_off)
+        self.tiles = np.ascontiguousarray(
+            rows.reshape(2 * nb + 1, self.n_tiles, TILE_MODELS).transpose(1, 0, 2))
+        a_max = float(np.abs(a).max())
+        self.err_a = float(ERR_SAFETY * 6.0 * FP32_U * math.sqrt(nb) * a_max)
+        self.err_b = float(ERR_SAFETY * 16.0 * FP32_U)
+
+        # ---- chunk-major parameter tables ---------------------------------------
+        nch = nmp // CHUNK
+        btab = np.zeros((nq, nmp), dtype=np.uint8)
+        qtab = np.zeros((nq, nmp), dtype=np.float64)
+        for k in range(nq):
+            btab[k, :nm] = self.bins[k].bin_num[g0]
+            qtab[k, :nm] = self.qcols[k][g0]
+        self.bin_tab = np.ascontiguousarray(btab.reshape(nq, nch, CHUNK).transpose(1, 0, 2))
+        self.q_tab = np.ascontiguousarray(qtab.reshape(nq, nch, CHUNK).transpose(1, 0, 2))
+        if self.pairs:
+            pb = np.full((len(self.pairs), nmp), -1, dtype=np.int32)
+            for p, pair in enumerate(self.pairs):
+                pb[p, :nm] = pair.bin_num[g0]
+            self.pair_bin = pb
+            self.pair_off = np.zeros(len(self.pairs) + 1, dtype=np.int64)
+            self.pair_off[1:] = np.cumsum([pr.nb1 * pr.nb2 for pr in self.pairs])
+        else:
+            self.pair_bin = None
+            self.pair_off = None
+
+    @property
+    def n_q(self):
+        return len(self.qnames)

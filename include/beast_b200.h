@@ -77,16 +77,20 @@ int bf_dense_tiles_per_item(int64_t n_tiles, int64_t n_stars, int sm_count);
  * Group selection -- the conservative superset of fit.py:670
  *   indx = where(lnp - max(lnp) > threshold)
  * at group granularity: group g is kept for star s when
- *   gmin[g][s] < starmin[s] + tau        (tau = -2*threshold + FP32 margin).
+ *   gmin[g][s] < x + 2*(err_a*sqrt(x) + err_b*x),   x = starmin[s] + tau,  tau = -2*threshold.
+ * err_a, err_b bound the FP32 rounding error of the dense pass for models with chi2 <= x
+ * (err_a = k*6u*sqrt(nb)*max|a|, err_b = k*16u, u = 2^-24; see DESIGN.md "margins"), so every
+ * member of the exact sparse set lies in a kept group.
  * counts : out [n_stars][BF_SELECT_SPLIT] uint32 (bf_select_count)
  * offsets: in  [n_stars*BF_SELECT_SPLIT + 1] uint32 exclusive scan of counts
  * list   : out group ids, ascending per star (bf_select_fill)
  * ------------------------------------------------------------------------- */
 int bf_select_count(int64_t n_groups, int64_t n_stars, int64_t ld_star, const float* gmin,
-                    const float* starmin, float tau, uint32_t* counts, void* stream);
+                    const float* starmin, float tau, float err_a, float err_b, uint32_t* counts,
+                    void* stream);
 int bf_select_fill(int64_t n_groups, int64_t n_stars, int64_t ld_star, const float* gmin,
-                   const float* starmin, float tau, const uint32_t* offsets, uint32_t* list,
-                   void* stream);
+                   const float* starmin, float tau, float err_a, float err_b,
+                   const uint32_t* offsets, uint32_t* list, void* stream);
 
 /* Exclusive prefix sum of n uint32 (out[n] = total).  scratch: >= bf_scan_scratch_elems(n)
  * uint32.  Plumbing for the variable-length per-star lists. */
@@ -113,13 +117,14 @@ typedef struct {
 } bf_exact_grid;
 
 /* Exact per-star maximum of lnP and its first index (fit.py:670, 684, 719, 727):
- * evaluates only groups with gmin < starmin + tau_tight.
+ * evaluates only groups whose FP32 minimum is within the error bound of the star's minimum
+ * (the exact argmax cannot be anywhere else).
  * flux64 [n_stars][nb] double.  pmax [n_stars] double, pmax_j [n_stars] int64 (filtered index,
  * -1 when the star has no finite lnP). */
 int bf_exact_max(const bf_exact_grid* grid, int64_t n_stars, int64_t ld_star,
-                 const double* flux64, const float* gmin, const float* starmin, float tau_tight,
-                 const uint32_t* offsets, const uint32_t* list, double* pmax, int64_t* pmax_j,
-                 void* stream);
+                 const double* flux64, const float* gmin, const float* starmin, float err_a,
+                 float err_b, const uint32_t* offsets, const uint32_t* list, double* pmax,
+                 int64_t* pmax_j, void* stream);
 
 /* ---------------------------------------------------------------------------
  * Per-parameter tables for the marginal PDFs / expectations, chunk-major:

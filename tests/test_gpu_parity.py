@@ -1,0 +1,65 @@
+"""CUDA path vs the reference's own outputs (golden fixtures) and vs the oracle.
+
+Everything here goes through the C ABI (libbeast_b200.so via ctypes)."""
+import numpy as np
+import pytest
+
+from tests import util
+
+pytestmark = pytest.mark.gpu
+
+
+def _engine(g, nz, args):
+    from beast_b200.engine import FitEngine
+    from beast_b200.gridprep import FitSetup
+
+    setup = FitSetup(g, nz, list(args["keys"]), max_nbins=args["max_nbins"],
+                     pdf2d_param_list=args["pdf2d_param_list"],
+                     make_pdf2d=args["pdf2d_param_list"] is not None,
+                     do_not_normalize=args["do_not_normalize"])
+    return setup, FitEngine(setup)
+
+
+@pytest.mark.parametrize("case", util.GOLDEN_CASES)
+def test_golden_case(case):
+    g, nz, obs, args, ref = util.load_golden(case)
+    setup, eng = _engine(g, nz, args)
+    want2d = args["pdf2d_param_list"] is not None
+    res = eng.fit(obs.fluxes, threshold=args["threshold"], want_pdf2d=want2d, sparse="all")
+    assert eng.launches > 0
+    util.compare_to_reference(setup, res, ref, n_pdf2d=len(setup.pairs) if want2d else 0)
+    util.compare_sparse(setup, res, ref["sparse_off"], ref["sparse_idx"], ref["sparse_lnp"],
+                        ref["sparse_chi2"])
+    if want2d:
+        assert [p.name for p in setup.pairs] == ref["pdf2d_pairs"]
+
+
+def test_c1_against_oracle():
+    """BASELINE.json configs[0] shape (1e5 models, 6 bands) on a star subsample, vs the oracle."""
+    from beast_b200 import synth
+    from oracle import fit_oracle as fo
+
+    g, nz, obs = synth.make_config("C1", nstars=48, seed=77)
+    keys = fo.default_keys(g)
+    ost = fo.OracleSetup(g, nz, keys, max_nbins=50)
+    want = fo.fit_all(obs.fluxes, ost, threshold=-10.0, fast=True)
+    args = dict(keys=keys, max_nbins=50, pdf2d_param_list=None, do_not_normalize=False)
+    setup, eng = _engine(g, nz, args)
+    res = eng.fit(obs.fluxes, threshold=-10.0, sparse="all")
+    util.compare_to_reference(setup, res, want)
+    off = np.zeros(len(obs) + 1, dtype=np.int64)
+    off[1:] = np.cumsum([len(s[0]) for s in want["sparse"]])
+    util.compare_sparse(setup, res, off, np.concatenate([s[0] for s in want["sparse"]]),
+                        np.concatenate([s[1] for s in want["sparse"]]),
+                        np.concatenate([s[2] for s in want["sparse"]]))
+
+
+def test_batching_is_invisible():
+    """splitting the catalog into batches must not change any output bit"""
+    g, nz, obs, args, ref = util.load_golden("small_thr10")
+    setup, eng = _engine(g, nz, args)
+    a = eng.fit(obs.fluxes, threshold=args["threshold"], sparse="all")
+    b = eng.fit(obs.fluxes, threshold=args["threshold"], sparse="all", batch=7)
+    for name in ("Pmax", "Pmax_j", "total_log_norm", "chi2min", "chi2min_j", "exp_vals", "pdf1d",
+                 "per_vals", "sparse_j", "sparse_lnp"):
+        np.testing.assert_array_equal(getattr(a, name), getattr(b, name), err_msg=name)
