@@ -88,6 +88,8 @@ PROTOTYPES = {
     "bf_sparse_gather": (C.c_int, [C.POINTER(ExactGrid), i64, c_void_p, c_void_p, c_void_p,
                                    c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p,
                                    c_void_p, c_void_p]),
+    "bf_sparse_sample_ranks": (C.c_int, [i64, c_void_p, c_void_p, C.c_uint64, i64, c_void_p,
+                                         c_void_p]),
     "bf_pdf2d_accumulate": (C.c_int, [C.POINTER(ExactGrid), C.c_int, c_void_p, c_void_p, i64,
                                       c_void_p, c_void_p, c_void_p, C.c_double, c_void_p,
                                       c_void_p, c_void_p, c_void_p]),

@@ -58,6 +58,50 @@ sparse_gather_kernel(bf_exact_grid grid, const double* __restrict__ flux64,
   }
 }
 
+// ---- device-side random subsample of each star's sparse set ---------------------------
+// The reference draws np.random.choice(indx, lnp_npts, replace=False) per star
+// (fit.py:694-700), which shuffles the whole set on the host: O(|S|) per star.  Here each
+// star gets min(|S|, npts) *distinct* pseudo-random ranks from a keyed 4-round Feistel
+// permutation of [0, |S|) (cycle walking), O(npts) per star and reproducible from the seed.
+__device__ __forceinline__ uint32_t mix32(uint32_t x) {
+  x ^= x >> 16; x *= 0x7feb352du; x ^= x >> 15; x *= 0x846ca68bu; x ^= x >> 16;
+  return x;
+}
+
+__device__ __forceinline__ uint32_t feistel_perm(uint32_t i, uint32_t n, uint32_t key) {
+  // domain 2^(2h) >= n
+  int bits = 32 - __clz(n - 1 > 0 ? n - 1 : 1);
+  const int h = (bits + 1) / 2;
+  const uint32_t hm = (1u << h) - 1u;
+  uint32_t x = i;
+  do {
+    uint32_t l = x >> h, r = x & hm;
+#pragma unroll
+    for (int round = 0; round < 4; ++round) {
+      const uint32_t f = mix32(r ^ (key + 0x9e3779b9u * (round + 1))) & hm;
+      const uint32_t nl = r;
+      r = l ^ f;
+      l = nl;
+    }
+    x = (l << h) | r;
+  } while (x >= n);
+  return x;
+}
+
+__global__ void sample_ranks_kernel(int64_t n_stars, const uint32_t* __restrict__ n_sparse,
+                                    const int64_t* __restrict__ rec_off, uint64_t seed,
+                                    int64_t star_base, uint32_t* __restrict__ ranks) {
+  const int64_t s = blockIdx.x;
+  const uint32_t n = n_sparse[s];
+  const int64_t r0 = rec_off[s], r1 = rec_off[s + 1];
+  const uint32_t k = static_cast<uint32_t>(r1 - r0);
+  const uint64_t sid = static_cast<uint64_t>(star_base + s);
+  const uint32_t key = mix32(static_cast<uint32_t>(seed) ^ mix32(static_cast<uint32_t>(sid) * 0x9e3779b9u +
+                                                               static_cast<uint32_t>(seed >> 32)));
+  for (uint32_t i = threadIdx.x; i < k; i += blockDim.x)
+    ranks[r0 + i] = (k >= n) ? i : feistel_perm(i, n, key);
+}
+
 // one warp per listed group; weights are already normalised: exp(lnp - total_log_norm)
 constexpr int kPdf2dWarps = 8;
 
@@ -133,5 +177,17 @@ extern "C" int bf_pdf2d_accumulate(const bf_exact_grid* grid, int n_pairs, const
       *grid, n_pairs, pair_bin, pair_off, flux64, pmax, total_log_norm, threshold, offsets, list,
       pdf2d);
   BF_CHECK_LAUNCH("pdf2d_kernel");
+  return BF_OK;
+}
+
+extern "C" int bf_sparse_sample_ranks(int64_t n_stars, const uint32_t* n_sparse,
+                                      const int64_t* rec_off, uint64_t seed, int64_t star_base,
+                                      uint32_t* ranks, void* stream) {
+  using namespace bf;
+  BF_REQUIRE(n_stars > 0 && n_stars < (1LL << 31), "bf_sparse_sample_ranks: bad n_stars");
+  BF_REQUIRE(n_sparse && rec_off && ranks, "bf_sparse_sample_ranks: null pointer");
+  sample_ranks_kernel<<<static_cast<unsigned>(n_stars), 128, 0, static_cast<cudaStream_t>(stream)>>>(
+      n_stars, n_sparse, rec_off, seed, star_base, ranks);
+  BF_CHECK_LAUNCH("sample_ranks_kernel");
   return BF_OK;
 }

@@ -106,6 +106,39 @@ class FitEngine:
         mb = min(mb, ((2**31 - 1) // max(s.n_groups, 1)) // STAR_BLOCK * STAR_BLOCK, 32768 * STAR_BLOCK)
         self.max_batch = int(max(mb, STAR_BLOCK))
         self.launches = 0  # kernels launched by this engine (bench.py reports it)
+        self.profile = False  # when True, CUDA events bracket every stage (see stage_ms())
+        self._events = []
+
+    # ------------------------------------------------------------------------------
+    class _Timed:
+        def __init__(self, eng, name):
+            self.eng, self.name = eng, name
+
+        def __enter__(self):
+            if self.eng.profile:
+                torch = _torch()
+                self.e0 = torch.cuda.Event(enable_timing=True)
+                self.e1 = torch.cuda.Event(enable_timing=True)
+                self.e0.record(torch.cuda.current_stream(self.eng.device))
+
+        def __exit__(self, *exc):
+            if self.eng.profile:
+                self.e1.record(_torch().cuda.current_stream(self.eng.device))
+                self.eng._events.append((self.name, self.e0, self.e1))
+
+    def _timed(self, name):
+        return FitEngine._Timed(self, name)
+
+    def stage_ms(self, reset=True):
+        """per-stage device time (ms, summed over the launches since the last reset) and launch
+        counts, from CUDA events on the launching stream; call after a synchronize."""
+        tot, cnt = {}, {}
+        for name, e0, e1 in self._events:
+            tot[name] = tot.get(name, 0.0) + e0.elapsed_time(e1)
+            cnt[name] = cnt.get(name, 0) + 1
+        if reset:
+            self._events = []
+        return tot, cnt
 
     # ------------------------------------------------------------------------------
     def _stream(self):
@@ -121,8 +154,9 @@ class FitEngine:
         gmin = torch.empty((s.n_groups, ld), dtype=torch.float32, device=self.device)
         starmin = torch.full((ld,), float("inf"), dtype=torch.float32, device=self.device)
         tpi = self.lib.bf_dense_tiles_per_item(s.n_tiles, n, self.sm_count)
-        _cabi.call("bf_dense_chi2", s.nb, s.n_tiles, _ptr(self.d_tiles), n, ld, _ptr(f32),
-                   _ptr(gmin), _ptr(starmin), tpi, self._stream())
+        with self._timed("dense"):
+            _cabi.call("bf_dense_chi2", s.nb, s.n_tiles, _ptr(self.d_tiles), n, ld, _ptr(f32),
+                       _ptr(gmin), _ptr(starmin), tpi, self._stream())
         self.launches += 1
         return gmin, starmin, ld
 
@@ -136,18 +170,67 @@ class FitEngine:
         offsets = torch.empty(nc + 1, dtype=torch.int32, device=self.device)
         scratch = torch.empty(int(self.lib.bf_scan_scratch_elems(nc)), dtype=torch.int32, device=self.device)
         st = self._stream()
-        _cabi.call("bf_select_count", s.n_groups, n, ld, _ptr(gmin), _ptr(starmin), tau, s.err_a,
-                   s.err_b, _ptr(counts), st)
+        with self._timed("select_count"):
+            _cabi.call("bf_select_count", s.n_groups, n, ld, _ptr(gmin), _ptr(starmin), tau,
+                       s.err_a, s.err_b, _ptr(counts), st)
         _cabi.call("bf_exclusive_scan_u32", nc, _ptr(counts), _ptr(offsets), _ptr(scratch), st)
         total = int(offsets[-1].item()) & 0xFFFFFFFF  # the one host sync of a batch
         lst = torch.empty(max(total, 1), dtype=torch.int32, device=self.device)
-        _cabi.call("bf_select_fill", s.n_groups, n, ld, _ptr(gmin), _ptr(starmin), tau, s.err_a,
-                   s.err_b, _ptr(offsets), _ptr(lst), st)
+        with self._timed("select_fill"):
+            _cabi.call("bf_select_fill", s.n_groups, n, ld, _ptr(gmin), _ptr(starmin), tau,
+                       s.err_a, s.err_b, _ptr(offsets), _ptr(lst), st)
         self.launches += 5
         return offsets, lst, total
 
+    def _sparse_records(self, o, sparse, lnp_rng, rng, seed, star_base, d_flux, offsets, lst, mask,
+                        prefix, n):
+        """sparse lnP records (fit.py:693-709).  ``sparse`` = "all" or lnp_npts.
+
+        lnp_rng="numpy": ranks drawn on the host with np.random.choice(n, size, replace=False),
+        the call the reference makes (only the set size feeds its random stream), so a seeded
+        run reproduces the reference's selection.  lnp_rng="device": ranks from
+        bf_sparse_sample_ranks (same distribution, O(lnp_npts) per star, no host round trip
+        of the sets)."""
+        torch = _torch()
+        dev, st = self.device, self._stream()
+        n_sp = o["n_sparse"].to(torch.int64) & 0xFFFFFFFF
+        ranks = None
+        if sparse == "all" or lnp_rng == "device":
+            cnt = n_sp if sparse == "all" else torch.clamp(n_sp, max=int(sparse))
+            d_rec_off = torch.zeros(n + 1, dtype=torch.int64, device=dev)
+            d_rec_off[1:] = torch.cumsum(cnt, 0)
+            nrec = int(d_rec_off[-1].item())
+            if sparse != "all" and nrec:
+                ranks = torch.empty(nrec, dtype=torch.int32, device=dev)
+                _cabi.call("bf_sparse_sample_ranks", n, _ptr(o["n_sparse"]), _ptr(d_rec_off),
+                           int(seed) & 0xFFFFFFFFFFFFFFFF, int(star_base), _ptr(ranks), st)
+                self.launches += 1
+        else:
+            ns_host = n_sp.cpu().numpy()
+            npts = int(sparse)
+            choose = rng.choice if rng is not None else np.random.choice
+            parts = [np.asarray(choose(int(m), size=npts, replace=False)) if npts < m else np.arange(m)
+                     for m in ns_host]
+            rec_off = np.zeros(n + 1, dtype=np.int64)
+            rec_off[1:] = np.cumsum(np.minimum(ns_host, npts))
+            nrec = int(rec_off[-1])
+            d_rec_off = torch.from_numpy(rec_off).to(dev)
+            if nrec:
+                ranks = torch.from_numpy(np.concatenate(parts).astype(np.int32)).to(dev)
+        out_j = torch.empty(max(nrec, 1), dtype=torch.int64, device=dev)
+        out_lnp = torch.empty(max(nrec, 1), dtype=torch.float32, device=dev)
+        out_chi2 = torch.empty(max(nrec, 1), dtype=torch.float32, device=dev)
+        if nrec:
+            with self._timed("sparse_gather"):
+                _cabi.call("bf_sparse_gather", C.byref(self.grid), n, _ptr(d_flux), _ptr(offsets),
+                           _ptr(lst), _ptr(mask), _ptr(prefix), _ptr(d_rec_off), _ptr(ranks),
+                           _ptr(out_j), _ptr(out_lnp), _ptr(out_chi2), st)
+            self.launches += 1
+        o["sparse_off"] = d_rec_off
+        o["sparse_j"], o["sparse_lnp"], o["sparse_chi2"] = out_j[:nrec], out_lnp[:nrec], out_chi2[:nrec]
+
     def fit_batch(self, flux, threshold=-10.0, percentiles=(16.0, 50.0, 84.0), want_pdf2d=False,
-                  sparse=None, rng=None):
+                  sparse=None, rng=None, lnp_rng="numpy", seed=0, star_base=0):
         """Fit one batch (<= max_batch stars).  ``flux``: (n, nb) float64 NumPy array or
         torch tensor (host or device).  Returns a dict of device tensors."""
         torch = _torch()
@@ -165,9 +248,10 @@ class FitEngine:
             dev = self.device
             pmax = torch.empty(n, dtype=torch.float64, device=dev)
             pmax_j = torch.empty(n, dtype=torch.int64, device=dev)
-            _cabi.call("bf_exact_max", C.byref(self.grid), n, ld, _ptr(d_flux), _ptr(gmin),
-                       _ptr(starmin), s.err_a, s.err_b, _ptr(offsets), _ptr(lst), _ptr(pmax),
-                       _ptr(pmax_j), st)
+            with self._timed("exact_max"):
+                _cabi.call("bf_exact_max", C.byref(self.grid), n, ld, _ptr(d_flux), _ptr(gmin),
+                           _ptr(starmin), s.err_a, s.err_b, _ptr(offsets), _ptr(lst), _ptr(pmax),
+                           _ptr(pmax_j), st)
             del gmin
             o = {
                 "Pmax": pmax, "Pmax_j": pmax_j,
@@ -186,9 +270,10 @@ class FitEngine:
                                o["exp_vals"].data_ptr(), o["pdf1d"].data_ptr(),
                                o["per_vals"].data_ptr(), mask.data_ptr(), prefix.data_ptr())
             pct = (C.c_double * 3)(*[float(x) for x in percentiles])
-            _cabi.call("bf_exact_accumulate", C.byref(self.grid), C.byref(self.params), n,
-                       _ptr(d_flux), _ptr(pmax), float(threshold), _ptr(offsets), _ptr(lst), pct,
-                       C.byref(outs), st)
+            with self._timed("accumulate"):
+                _cabi.call("bf_exact_accumulate", C.byref(self.grid), C.byref(self.params), n,
+                           _ptr(d_flux), _ptr(pmax), float(threshold), _ptr(offsets), _ptr(lst),
+                           pct, C.byref(outs), st)
             self.launches += 2
             off2 = offsets.view(-1)[:: SELECT_SPLIT]
             o["n_groups_selected"] = (off2[1:].to(torch.int64) & 0xFFFFFFFF) - (off2[:-1].to(torch.int64) & 0xFFFFFFFF)
@@ -204,45 +289,13 @@ class FitEngine:
                 o["pdf2d"] = pdf2d
 
             if sparse is not None:
-                # sparse = "all" or an int (lnp_npts): random subsample of the sparse set drawn
-                # exactly like the reference does, np.random.choice(indx, size, replace=False)
-                # (fit.py:694-700) -- only the set size matters for the random stream.
-                ns_host = (o["n_sparse"].cpu().numpy().astype(np.int64)) & 0xFFFFFFFF
-                if sparse == "all":
-                    cnt = ns_host
-                    ranks = None
-                else:
-                    npts = int(sparse)
-                    cnt = np.minimum(ns_host, npts)
-                    parts = []
-                    choose = (rng.choice if rng is not None else np.random.choice)
-                    for e in range(n):
-                        if npts < ns_host[e]:
-                            parts.append(np.asarray(choose(int(ns_host[e]), size=npts, replace=False)))
-                        else:
-                            parts.append(np.arange(ns_host[e]))
-                    ranks = np.concatenate(parts).astype(np.int32) if parts else np.zeros(0, np.int32)
-                rec_off = np.zeros(n + 1, dtype=np.int64)
-                rec_off[1:] = np.cumsum(cnt)
-                nrec = int(rec_off[-1])
-                d_rec_off = torch.from_numpy(rec_off).to(dev)
-                d_ranks = torch.from_numpy(ranks).to(dev) if ranks is not None and nrec else None
-                out_j = torch.empty(max(nrec, 1), dtype=torch.int64, device=dev)
-                out_lnp = torch.empty(max(nrec, 1), dtype=torch.float32, device=dev)
-                out_chi2 = torch.empty(max(nrec, 1), dtype=torch.float32, device=dev)
-                if nrec:
-                    _cabi.call("bf_sparse_gather", C.byref(self.grid), n, _ptr(d_flux),
-                               _ptr(offsets), _ptr(lst), _ptr(mask), _ptr(prefix),
-                               _ptr(d_rec_off), _ptr(d_ranks), _ptr(out_j), _ptr(out_lnp),
-                               _ptr(out_chi2), st)
-                    self.launches += 1
-                o["sparse_off"] = rec_off
-                o["sparse_j"], o["sparse_lnp"], o["sparse_chi2"] = out_j[:nrec], out_lnp[:nrec], out_chi2[:nrec]
+                self._sparse_records(o, sparse, lnp_rng, rng, seed, star_base, d_flux, offsets, lst,
+                                     mask, prefix, n)
             return o
 
     # ------------------------------------------------------------------------------
     def fit(self, fluxes, threshold=-10.0, percentiles=(16.0, 50.0, 84.0), want_pdf2d=False,
-            sparse=None, batch=None, rng=None):
+            sparse=None, batch=None, rng=None, lnp_rng="numpy", seed=0):
         """Fit all stars of ``fluxes`` (ns, nb) in batches; returns a host ``FitResult``."""
         torch = _torch()
         s = self.setup
@@ -256,7 +309,8 @@ class FitEngine:
         sp_j, sp_l, sp_c, sp_cnt = [], [], [], []
         for a in range(0, ns, bs):
             b = min(ns, a + bs)
-            o = self.fit_batch(fluxes[a:b], threshold, percentiles, want_pdf2d, sparse, rng)
+            o = self.fit_batch(fluxes[a:b], threshold, percentiles, want_pdf2d, sparse, rng,
+                               lnp_rng, seed, a)
             res.Pmax[a:b] = o["Pmax"].cpu().numpy()
             res.Pmax_j[a:b] = o["Pmax_j"].cpu().numpy()
             res.total_log_norm[a:b] = o["total_log_norm"].cpu().numpy()
@@ -270,7 +324,7 @@ class FitEngine:
             if pair_len:
                 res.pdf2d[a:b] = o["pdf2d"].cpu().numpy()
             if sparse is not None:
-                sp_cnt.append(np.diff(o["sparse_off"]))
+                sp_cnt.append(np.diff(o["sparse_off"].cpu().numpy()))
                 sp_j.append(o["sparse_j"].cpu().numpy())
                 sp_l.append(o["sparse_lnp"].cpu().numpy())
                 sp_c.append(o["sparse_chi2"].cpu().numpy())

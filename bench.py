@@ -1,0 +1,345 @@
+#!/usr/bin/env python
+"""
+Benchmark of the BEAST fitting hot path on B200 (contract: see DESIGN.md "Measurement").
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--config C2]
+
+A *step* is one pass of the hot path over the whole synthetic catalog of the named
+configuration (C2 = PHAT-like 6-band grid of 4e6 models, 1e5 stars, stats + pdf1d +
+sparse lnP).  ``value`` = star x model lnP evaluations per second with the fluxes already
+resident in HBM; ``e2e`` = the same through the public engine API with host fluxes in and
+all results back on the host, every step.  For N > 1 every rank fits its own 1e5 stars
+against a replicated grid (stars shard, no data-path collective): weak scaling.
+
+``--impl reference`` times the CPU restatement of the reference's star loop
+(oracle/fit_oracle.py, faithful mode) on the box's host cores, one process per core over
+disjoint star slices -- the reference's own parallel model (tools/run/helper_functions.py:55-58).
+"""
+import argparse
+import json
+import os
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+CONFIGS = {
+    # name: (axes name, stars per GPU, description)
+    "C1": ("C1", 1000, "synthetic PHAT 6-band SEDGrid 1e5 models, 1,000 stars"),
+    "C2": ("C2", 100000, "PHAT 6-band 4e6-model grid, 1e5 stars, stats+pdf1d+sparse lnP"),
+    "C4": ("C4", 200000, "8-band UV-NIR grid 1e7 models, 2e5 stars"),
+}
+THRESHOLD = -10.0  # summary_table_memory / run_fitting default (fit.py:924, run_fitting.py:303)
+MAX_NBINS = 200    # summary_table_memory default (fit.py:928)
+LNP_NPTS = 500     # run_fitting.py:305
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=3)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--config", default="C2", choices=sorted(CONFIGS))
+    ap.add_argument("--stars", type=int, default=None, help="override stars per GPU")
+    ap.add_argument("--max-nbins", type=int, default=MAX_NBINS)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--cpu-stars-per-core", type=int, default=2)
+    return ap.parse_args()
+
+
+# ---------------------------------------------------------------------------------------
+class ClockSampler(threading.Thread):
+    """samples SM clock + throttle reasons of one GPU during the timed region (NVML)"""
+
+    REASONS = {0x1: "gpu_idle", 0x2: "applications_clocks_setting", 0x4: "sw_power_cap",
+               0x8: "hw_slowdown", 0x10: "sync_boost", 0x20: "sw_thermal_slowdown",
+               0x40: "hw_thermal_slowdown", 0x80: "hw_power_brake_slowdown",
+               0x100: "display_clock_setting"}
+
+    def __init__(self, index):
+        super().__init__(daemon=True)
+        self.index, self.samples, self.reasons, self.stop_flag = index, [], set(), False
+        self.max_mhz, self.ok = None, False
+        try:
+            import pynvml
+
+            pynvml.nvmlInit()
+            self.nv = pynvml
+            self.h = pynvml.nvmlDeviceGetHandleByIndex(index)
+            self.max_mhz = pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM)
+            self.ok = True
+        except Exception:
+            self.ok = False
+
+    def run(self):
+        while self.ok and not self.stop_flag:
+            try:
+                self.samples.append(self.nv.nvmlDeviceGetClockInfo(self.h, self.nv.NVML_CLOCK_SM))
+                bits = self.nv.nvmlDeviceGetCurrentClocksEventReasons(self.h)
+                for b, name in self.REASONS.items():
+                    if bits & b and name != "gpu_idle":
+                        self.reasons.add(name)
+            except Exception:
+                pass
+            time.sleep(0.1)
+
+    def summary(self):
+        if not self.ok or not self.samples:
+            return {"sm_mhz": None, "sm_max_mhz": self.max_mhz, "reasons": ["nvml_unavailable"]}
+        return {"sm_mhz": float(np.median(self.samples)), "sm_max_mhz": self.max_mhz,
+                "reasons": sorted(self.reasons)}
+
+
+def measured_peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.isfile(p):
+        with open(p) as f:
+            return json.load(f), "MEASURED_PEAKS.json"
+    return {"hbm_gbs": 6650.0, "sm_max_mhz": 1965.0}, "fallback"
+
+
+def build_inputs(cfg, stars, seed):
+    from beast_b200 import synth
+
+    axes = CONFIGS[cfg][0]
+    if axes == "C4":
+        g = synth.make_sedgrid(axes, synth.UVNIR_FILTERS, synth.UVNIR_LAMB, seed=1234)
+    else:
+        g = synth.make_sedgrid(axes, seed=1234)
+    nz = synth.make_noisemodel(g)
+    obs = synth.make_observations(g, nz, stars, seed=seed, with_coords=False)
+    return g, nz, obs
+
+
+# ---------------------------------------------------------------------------------------
+_CPU = {}
+
+
+def _cpu_worker(args):
+    lo, hi = args
+    from oracle import fit_oracle as fo
+
+    st, fluxes = _CPU["setup"], _CPU["flux"]
+    t = time.perf_counter()
+    for e in range(lo, hi):
+        fo.fit_star(st, fluxes[e], THRESHOLD, fast=False)
+    return time.perf_counter() - t
+
+
+def cpu_reference_run(g, nz, obs, max_nbins, stars_per_core, steps, warmup):
+    """time the oracle's faithful star loop on all host cores; returns (evals/s per step list,
+    cores, sample description).  Setup (bins, index lists) is outside the timed region."""
+    import multiprocessing as mp
+
+    from oracle import fit_oracle as fo
+
+    cores = len(os.sched_getaffinity(0))
+    keys = fo.default_keys(g)
+    st = fo.OracleSetup(g, nz, keys, max_nbins=max_nbins)
+    for b in st.bins:
+        b.index_lists()
+    _CPU["setup"], _CPU["flux"] = st, obs.fluxes
+    nm = len(st.g0_indxs)
+    rates = []
+    ctx = mp.get_context("fork")
+    with ctx.Pool(cores) as pool:
+        for it in range(warmup + steps):
+            base = (it * cores * stars_per_core) % max(1, len(obs) - cores * stars_per_core)
+            jobs = [(base + c * stars_per_core, base + (c + 1) * stars_per_core) for c in range(cores)]
+            t = time.perf_counter()
+            pool.map(_cpu_worker, jobs)
+            dt = time.perf_counter() - t
+            if it >= warmup:
+                rates.append((cores * stars_per_core * nm / dt, dt))
+    sample = "%d stars (%d per core x %d cores) of the same catalog against the full %d-model grid per step" % (
+        cores * stars_per_core, stars_per_core, cores, nm)
+    return rates, cores, sample
+
+
+# ---------------------------------------------------------------------------------------
+def run_reference(args, rank, world):
+    if rank != 0:
+        return
+    stars = max(64, len(os.sched_getaffinity(0)) * args.cpu_stars_per_core * (args.steps + args.warmup))
+    g, nz, obs = build_inputs(args.config, stars, seed=4321)
+    rates, cores, sample = cpu_reference_run(g, nz, obs, args.max_nbins, args.cpu_stars_per_core,
+                                             args.steps, args.warmup)
+    nm = int(np.count_nonzero(g["weight"] > 0))
+    val = float(np.mean([r for r, _ in rates]))
+    ms = float(np.mean([dt for _, dt in rates]) * 1e3)
+    line = {
+        "impl": "reference", "metric": "star-model lnP evaluations per second", "value": val,
+        "unit": "star*model/s", "stars_per_s": val / nm, "n_gpus": args.gpus, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "config": workload_config(args, nm, stars),
+        "cpu_baseline": {"value": val, "unit": "star*model/s", "cores": cores, "kind": "port",
+                         "sample": sample},
+        "e2e": {"value": val, "unit": "star*model/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line), flush=True)
+
+
+def workload_config(args, nm, stars):
+    return {"workload": CONFIGS[args.config][1], "config": args.config, "models": nm,
+            "bands": 8 if args.config == "C4" else 6, "stars_per_gpu": stars,
+            "threshold": THRESHOLD, "max_nbins": args.max_nbins, "lnp_npts": LNP_NPTS,
+            "outputs": "stats+pdf1d+sparse lnP", "parallelism": "stars sharded, grid replicated",
+            "l2": "inputs larger than L2 (grid tiles + exact arrays + parameter tables > 126 MB)"}
+
+
+def run_ours(args, rank, world, local_rank):
+    import torch
+
+    from beast_b200.engine import FitEngine
+    from beast_b200.gridprep import FitSetup
+
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    dist = None
+    if world > 1:
+        import torch.distributed as dist_mod
+
+        dist = dist_mod
+        dist.init_process_group("nccl", device_id=dev)
+
+    stars = args.stars or CONFIGS[args.config][1]
+    g, nz, obs = build_inputs(args.config, stars, seed=4321 + rank)
+    keys = [k for k in g.keys() if k not in
+            "osl keep weight grid_weight prior_weight fullgrid_idx stage specgrid_indx phase eep".split()]
+    t0 = time.perf_counter()
+    setup = FitSetup(g, nz, keys, max_nbins=args.max_nbins)
+    eng = FitEngine(setup, device=dev, gmin_budget_bytes=24 << 30)
+    setup_s = time.perf_counter() - t0
+    nm = setup.n_models
+    fluxes = np.ascontiguousarray(obs.fluxes)
+    bs = eng.max_batch
+    batches = [(a, min(stars, a + bs)) for a in range(0, stars, bs)]
+    d_flux = [torch.from_numpy(fluxes[a:b]).to(dev) for a, b in batches]
+    pinned = torch.from_numpy(fluxes).pin_memory()
+
+    def barrier():
+        if dist is not None:
+            dist.barrier()
+        torch.cuda.synchronize(dev)
+
+    def step_resident():
+        for (a, b), df in zip(batches, d_flux):
+            eng.fit_batch(df, THRESHOLD, sparse=LNP_NPTS, lnp_rng="device", seed=1, star_base=a)
+
+    def step_e2e():
+        return eng.fit(pinned.numpy(), THRESHOLD, sparse=LNP_NPTS, lnp_rng="device", seed=1)
+
+    # ---- device-resident throughput ------------------------------------------------
+    for _ in range(args.warmup):
+        step_resident()
+    barrier()
+    eng.launches = 0
+    eng.profile = True
+    eng.stage_ms()
+    sampler = ClockSampler(local_rank)
+    sampler.start()
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    ev0.record()
+    for _ in range(args.steps):
+        step_resident()
+    ev1.record()
+    barrier()
+    sampler.stop_flag = True
+    ms_total = ev0.elapsed_time(ev1)
+    launches = eng.launches
+    stage_tot, stage_cnt = eng.stage_ms()
+    eng.profile = False
+    t = torch.tensor([ms_total], dtype=torch.float64, device=dev)
+    if dist is not None:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms_step = float(t.item()) / args.steps
+    value = world * stars * nm / (ms_step * 1e-3)
+
+    # ---- end to end through the engine API (host in, host out) -----------------------
+    step_e2e()
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        res = step_e2e()
+    barrier()
+    e2e_s = (time.perf_counter() - t0) / args.steps
+    t = torch.tensor([e2e_s], dtype=torch.float64, device=dev)
+    if dist is not None:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    e2e_s = float(t.item())
+    h2d = fluxes.nbytes
+    d2h = sum(getattr(res, n).nbytes for n in ("Pmax", "Pmax_j", "total_log_norm", "chi2min", "chi2min_j",
+                                                "exp_vals", "per_vals", "pdf1d", "sparse_j",
+                                                "sparse_lnp", "sparse_chi2")) + 4 * stars
+    if rank != 0:
+        return
+
+    # ---- roofline of the dominant kernel (dense FP32 sweep) ---------------------------
+    peaks, peak_src = measured_peaks()
+    nb = setup.nb
+    flop_per_eval = 4 * nb + 2  # 2*nb+1 FMA per star x model
+    dense_ms = stage_tot.get("dense", 0.0) / max(stage_cnt.get("dense", 1), 1)
+    evals_per_launch = stars * setup.ld_model / len(batches)
+    achieved = flop_per_eval * evals_per_launch / (dense_ms * 1e-3) / 1e12 if dense_ms else None
+    sm_max = float(peaks.get("sm_max_mhz", 1965.0))
+    peak_tf = eng.sm_count * 128 * 2 * sm_max * 1e6 / 1e12
+    roofline = {
+        "bound": "fp32", "kernel": "dense_chi2_kernel", "achieved": achieved, "peak": peak_tf,
+        "unit": "TFLOP/s", "frac": (achieved / peak_tf) if achieved else None, "traffic": None,
+        "peak_source": "%d SMs x 128 FP32 lanes x 2 x sm_max_mhz (%s); MEASURED_PEAKS.json has no "
+                       "FP32 entry" % (eng.sm_count, peak_src),
+        "dense_ms_per_launch": dense_ms, "flop_per_star_model": flop_per_eval,
+        "hbm_gbs_peak": peaks.get("hbm_gbs"),
+        "stage_ms_per_step": {k: v / args.steps for k, v in stage_tot.items()},
+    }
+
+    cpu = None
+    if world == 1 and not args.no_cpu_baseline:
+        rates, cores, sample = cpu_reference_run(g, nz, obs, args.max_nbins, args.cpu_stars_per_core, 1, 1)
+        cpu = {"value": rates[0][0], "unit": "star*model/s", "cores": cores, "kind": "port",
+               "sample": sample, "seconds": rates[0][1]}
+
+    line = {
+        "metric": "star-model lnP evaluations per second", "value": value, "unit": "star*model/s",
+        "stars_per_s": value / nm, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+        "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": "f32 dense sweep + f64 exact pass", "data": "synthetic",
+        "config": workload_config(args, nm, stars),
+        "clocks": sampler.summary(),
+        "e2e": {"value": world * stars * nm / e2e_s, "unit": "star*model/s",
+                "stars_per_s": world * stars / e2e_s, "seconds_per_step": e2e_s,
+                "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h)},
+        "gpu_launches": int(launches),
+        "roofline": roofline,
+        "cpu_baseline": cpu,
+        "setup_seconds": setup_s,
+        "mean_sparse_set": float(np.mean(res.n_sparse)),
+        "mean_groups_selected": float(np.mean(res.n_groups_selected)),
+    }
+    print(json.dumps(line), flush=True)
+    if dist is not None:
+        dist.destroy_process_group()
+
+
+def main():
+    args = parse_args()
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if args.impl == "reference":
+        run_reference(args, rank, world)
+        return
+    run_ours(args, rank, world, local_rank)
+
+
+if __name__ == "__main__":
+    main()

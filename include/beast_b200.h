@@ -170,6 +170,13 @@ int bf_sparse_gather(const bf_exact_grid* grid, int64_t n_stars, const double* f
                      const uint32_t* member_prefix, const int64_t* rec_off, const uint32_t* ranks,
                      int64_t* out_j, float* out_lnp, float* out_chi2, void* stream);
 
+/* Device-side stand-in for np.random.choice(indx, lnp_npts, replace=False) (fit.py:694-700):
+ * star s gets rec_off[s+1]-rec_off[s] = min(n_sparse[s], lnp_npts) distinct pseudo-random ranks
+ * (identity when the whole set is kept).  Same distribution as the reference, different
+ * random stream; the host path with NumPy's stream stays available in engine.py. */
+int bf_sparse_sample_ranks(int64_t n_stars, const uint32_t* n_sparse, const int64_t* rec_off,
+                           uint64_t seed, int64_t star_base, uint32_t* ranks, void* stream);
+
 /* ---------------------------------------------------------------------------
  * 2D PDFs (fitting/pdf2d.py:122-148, fit.py:758-762).
  *   pair_bin [n_pairs][ld_model] int32  flattened (b1*nb2+b2) bin, -1 = outside
