@@ -44,10 +44,21 @@ class ParamTables(C.Structure):
     _fields_ = [
         ("n_q", C.c_int),
         ("total_bins", C.c_int),
+        ("max_bins", C.c_int),
         ("bin_tab", c_void_p),
         ("q_tab", c_void_p),
+        ("q_lin", c_void_p),
         ("bin_off", c_void_p),
         ("bin_val", c_void_p),
+    ]
+
+
+class AccumScratch(C.Structure):
+    _fields_ = [
+        ("weights", c_void_p),
+        ("part_wsum", c_void_p),
+        ("part_chi2", c_void_p),
+        ("part_chi2_j", c_void_p),
     ]
 
 
@@ -76,15 +87,17 @@ PROTOTYPES = {
     "bf_select_count": (C.c_int, [i64, i64, i64, c_void_p, c_void_p, C.c_float, C.c_float,
                                   C.c_float, c_void_p, c_void_p]),
     "bf_select_fill": (C.c_int, [i64, i64, i64, c_void_p, c_void_p, C.c_float, C.c_float,
-                                 C.c_float, c_void_p, c_void_p, c_void_p]),
+                                 C.c_float, c_void_p, c_void_p, c_void_p, c_void_p]),
     "bf_scan_scratch_elems": (i64, [i64]),
     "bf_exclusive_scan_u32": (C.c_int, [i64, c_void_p, c_void_p, c_void_p, c_void_p]),
     "bf_exact_max": (C.c_int, [C.POINTER(ExactGrid), i64, i64, c_void_p, c_void_p, c_void_p,
                                C.c_float, C.c_float, c_void_p, c_void_p, c_void_p, c_void_p,
                                c_void_p]),
-    "bf_exact_accumulate": (C.c_int, [C.POINTER(ExactGrid), C.POINTER(ParamTables), i64, c_void_p,
-                                      c_void_p, C.c_double, c_void_p, c_void_p,
-                                      C.POINTER(C.c_double), C.POINTER(StarOutputs), c_void_p]),
+    "bf_exact_accumulate": (C.c_int, [C.POINTER(ExactGrid), C.POINTER(ParamTables), i64, i64, c_void_p,
+                                      c_void_p, C.c_double, c_void_p, c_void_p, c_void_p, c_void_p, i64,
+                                      i64,
+                                      C.POINTER(C.c_double), C.POINTER(AccumScratch),
+                                      C.POINTER(StarOutputs), c_void_p]),
     "bf_sparse_gather": (C.c_int, [C.POINTER(ExactGrid), i64, c_void_p, c_void_p, c_void_p,
                                    c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p,
                                    c_void_p, c_void_p]),

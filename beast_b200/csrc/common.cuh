@@ -118,6 +118,11 @@ __device__ __forceinline__ float select_threshold(float starmin, float tau, floa
   return x + 2.0f * (err_a * sqrtf(fmaxf(x, 0.0f)) + err_b * x) + 1e-6f;
 }
 
+// starmin entries are packed (FP32 bits << 32 | arg-min group)
+__device__ __forceinline__ float starmin_value(unsigned long long packed) {
+  return __uint_as_float(static_cast<unsigned int>(packed >> 32));
+}
+
 __device__ __forceinline__ int lane_id() { return threadIdx.x & 31; }
 
 }  // namespace bf

@@ -38,7 +38,7 @@ template <int NB>
 __global__ void __launch_bounds__(kDenseThreads, 3)
 dense_chi2_kernel(const float* __restrict__ tiles, int64_t n_tiles, int tiles_per_item,
                   const float* __restrict__ flux, int64_t ld_star, float* __restrict__ gmin,
-                  unsigned int* __restrict__ starmin) {
+                  unsigned long long* __restrict__ starmin) {
   constexpr int TM = BF_TILE_MODELS;
   constexpr int ROWS = 2 * NB + 1;
   constexpr uint32_t TILE_BYTES = DenseSmem<NB>::kTileBytes;
@@ -89,10 +89,12 @@ dense_chi2_kernel(const float* __restrict__ tiles, int64_t n_tiles, int tiles_pe
 
   const float kInf = __int_as_float(0x7f800000);
   float rmin[2 * kNPair], smin[2 * kNPair];
+  unsigned int sgrp[2 * kNPair];  // group that holds the running minimum
 #pragma unroll
   for (int q = 0; q < 2 * kNPair; ++q) {
     rmin[q] = kInf;
     smin[q] = kInf;
+    sgrp[q] = 0xffffffffu;
   }
 
   for (int i = 0; i < nt; ++i) {
@@ -146,7 +148,10 @@ dense_chi2_kernel(const float* __restrict__ tiles, int64_t n_tiles, int tiles_pe
 #pragma unroll
       for (int q = 0; q < 2 * kNPair; ++q) {
         gp[q * kDenseThreads] = rmin[q];
-        smin[q] = fminf(smin[q], rmin[q]);
+        if (rmin[q] < smin[q]) {
+          smin[q] = rmin[q];
+          sgrp[q] = static_cast<unsigned int>(gidx);
+        }
         rmin[q] = kInf;
       }
     }
@@ -154,16 +159,22 @@ dense_chi2_kernel(const float* __restrict__ tiles, int64_t n_tiles, int tiles_pe
     if ((tid & 31) == 0) mbar_arrive(&empty_bar[stage]);
   }
 
-  // acc >= 0 always (chi2 >= 0, c2 >= 0), so the IEEE bit pattern orders like the value
+  // acc >= 0 always (chi2 >= 0, c2 >= 0), so the IEEE bit pattern orders like the value;
+  // packed as (value bits << 32 | group) one 64-bit atomicMin keeps the arg-min group too
 #pragma unroll
   for (int q = 0; q < 2 * kNPair; ++q) {
-    if (smin[q] < kInf) atomicMin(starmin + star0 + q * kDenseThreads + tid, __float_as_uint(smin[q]));
+    if (smin[q] < kInf) {
+      const unsigned long long packed =
+          (static_cast<unsigned long long>(__float_as_uint(smin[q])) << 32) | sgrp[q];
+      atomicMin(starmin + star0 + q * kDenseThreads + tid, packed);
+    }
   }
 }
 
 template <int NB>
 static int launch_dense(int64_t n_tiles, const float* tiles, int64_t ld_star, const float* flux,
-                        float* gmin, float* starmin, int tiles_per_item, cudaStream_t st) {
+                        float* gmin, unsigned long long* starmin, int tiles_per_item,
+                        cudaStream_t st) {
   auto kern = dense_chi2_kernel<NB>;
   static bool configured[64] = {};
   int dev = 0;
@@ -176,7 +187,7 @@ static int launch_dense(int64_t n_tiles, const float* tiles, int64_t ld_star, co
   const int64_t n_items = (n_tiles + tiles_per_item - 1) / tiles_per_item;
   dim3 grid(static_cast<unsigned>(n_items), static_cast<unsigned>(ld_star / BF_STAR_BLOCK));
   kern<<<grid, kDenseThreads, DenseSmem<NB>::kBytes, st>>>(
-      tiles, n_tiles, tiles_per_item, flux, ld_star, gmin, reinterpret_cast<unsigned int*>(starmin));
+      tiles, n_tiles, tiles_per_item, flux, ld_star, gmin, starmin);
   BF_CHECK_LAUNCH("dense_chi2_kernel");
   return BF_OK;
 }
@@ -197,7 +208,7 @@ extern "C" int bf_dense_tiles_per_item(int64_t n_tiles, int64_t n_stars, int sm_
 }
 
 extern "C" int bf_dense_chi2(int nb, int64_t n_tiles, const float* tiles, int64_t n_stars,
-                             int64_t ld_star, const float* flux, float* gmin, float* starmin,
+                             int64_t ld_star, const float* flux, float* gmin, uint64_t* starmin,
                              int tiles_per_item, void* stream) {
   using namespace bf;
   BF_REQUIRE(nb >= 1 && nb <= BF_MAX_BANDS, "bf_dense_chi2: nb=%d out of range", nb);
@@ -211,7 +222,8 @@ extern "C" int bf_dense_chi2(int nb, int64_t n_tiles, const float* tiles, int64_
   switch (nb) {
 #define BF_CASE(N) \
   case N:          \
-    return launch_dense<N>(n_tiles, tiles, ld_star, flux, gmin, starmin, tiles_per_item, st);
+    return launch_dense<N>(n_tiles, tiles, ld_star, flux, gmin,                               \
+                           reinterpret_cast<unsigned long long*>(starmin), tiles_per_item, st);
     BF_CASE(1) BF_CASE(2) BF_CASE(3) BF_CASE(4) BF_CASE(5) BF_CASE(6) BF_CASE(7) BF_CASE(8)
     BF_CASE(9) BF_CASE(10) BF_CASE(11) BF_CASE(12)
 #undef BF_CASE

@@ -26,7 +26,7 @@ constexpr int kMaxWarps = 4;
 __global__ void __launch_bounds__(kMaxWarps * 32)
 exact_max_kernel(bf_exact_grid grid, int64_t n_stars, int64_t ld_star,
                  const double* __restrict__ flux64, const float* __restrict__ gmin,
-                 const float* __restrict__ starmin, float err_a, float err_b,
+                 const unsigned long long* __restrict__ starmin, float err_a, float err_b,
                  const uint32_t* __restrict__ offsets, const uint32_t* __restrict__ list,
                  double* __restrict__ pmax, int64_t* __restrict__ pmax_j) {
   __shared__ double sflux_all[kMaxWarps][BF_MAX_BANDS];
@@ -39,7 +39,7 @@ exact_max_kernel(bf_exact_grid grid, int64_t n_stars, int64_t ld_star,
 
   const uint32_t e0 = offsets[s * BF_SELECT_SPLIT];
   const uint32_t e1 = offsets[(s + 1) * BF_SELECT_SPLIT];
-  const float thr = select_threshold(starmin[s], 0.0f, err_a, err_b);
+  const float thr = select_threshold(starmin_value(starmin[s]), 0.0f, err_a, err_b);
 
   double best = -1.7976931348623157e308;
   int64_t best_j = -1;
@@ -88,7 +88,7 @@ exact_max_kernel(bf_exact_grid grid, int64_t n_stars, int64_t ld_star,
 }  // namespace bf
 
 extern "C" int bf_exact_max(const bf_exact_grid* grid, int64_t n_stars, int64_t ld_star,
-                            const double* flux64, const float* gmin, const float* starmin,
+                            const double* flux64, const float* gmin, const uint64_t* starmin,
                             float err_a, float err_b, const uint32_t* offsets,
                             const uint32_t* list,
                             double* pmax, int64_t* pmax_j, void* stream) {
@@ -99,7 +99,8 @@ extern "C" int bf_exact_max(const bf_exact_grid* grid, int64_t n_stars, int64_t 
              "bf_exact_max: null pointer");
   const unsigned blocks = static_cast<unsigned>((n_stars + kMaxWarps - 1) / kMaxWarps);
   exact_max_kernel<<<blocks, kMaxWarps * 32, 0, static_cast<cudaStream_t>(stream)>>>(
-      *grid, n_stars, ld_star, flux64, gmin, starmin, err_a, err_b, offsets, list, pmax, pmax_j);
+      *grid, n_stars, ld_star, flux64, gmin, reinterpret_cast<const unsigned long long*>(starmin),
+      err_a, err_b, offsets, list, pmax, pmax_j);
   BF_CHECK_LAUNCH("exact_max_kernel");
   return BF_OK;
 }

@@ -17,16 +17,18 @@ constexpr int kSelThreads = 128;
 template <bool FILL>
 __global__ void __launch_bounds__(kSelThreads)
 select_kernel(int64_t n_groups, int64_t n_stars, int64_t ld_star, const float* __restrict__ gmin,
-              const float* __restrict__ starmin, float tau, float err_a, float err_b,
+              const unsigned long long* __restrict__ starmin, float tau, float err_a,
+              float err_b,
               uint32_t* __restrict__ counts,
-              const uint32_t* __restrict__ offsets, uint32_t* __restrict__ list) {
+              const uint32_t* __restrict__ offsets, uint32_t* __restrict__ list,
+              uint32_t* __restrict__ entry_star) {
   const int64_t s = static_cast<int64_t>(blockIdx.x) * kSelThreads + threadIdx.x;
   if (s >= n_stars) return;
   const int c = blockIdx.y;
   const int64_t per = (n_groups + BF_SELECT_SPLIT - 1) / BF_SELECT_SPLIT;
   const int64_t g0 = c * per;
   const int64_t g1 = min(n_groups, g0 + per);
-  const float thr = select_threshold(starmin[s], tau, err_a, err_b);
+  const float thr = select_threshold(starmin_value(starmin[s]), tau, err_a, err_b);
   const float* p = gmin + s;
   uint32_t n = 0;
   uint32_t pos = FILL ? offsets[s * BF_SELECT_SPLIT + c] : 0u;
@@ -38,14 +40,22 @@ select_kernel(int64_t n_groups, int64_t n_stars, int64_t ld_star, const float* _
 #pragma unroll
     for (int u = 0; u < 8; ++u) {
       if (v[u] < thr) {
-        if (FILL) list[pos++] = static_cast<uint32_t>(g + u);
+        if (FILL) {
+          list[pos] = static_cast<uint32_t>(g + u);
+          if (entry_star) entry_star[pos] = static_cast<uint32_t>(s);
+          ++pos;
+        }
         ++n;
       }
     }
   }
   for (; g < g1; ++g) {
     if (__ldg(p + g * ld_star) < thr) {
-      if (FILL) list[pos++] = static_cast<uint32_t>(g);
+      if (FILL) {
+        list[pos] = static_cast<uint32_t>(g);
+        if (entry_star) entry_star[pos] = static_cast<uint32_t>(s);
+        ++pos;
+      }
       ++n;
     }
   }
@@ -151,28 +161,30 @@ static int run_scan(int64_t n, const uint32_t* in, uint32_t* out, uint32_t* scra
 }  // namespace bf
 
 extern "C" int bf_select_count(int64_t n_groups, int64_t n_stars, int64_t ld_star,
-                               const float* gmin, const float* starmin, float tau,
+                               const float* gmin, const uint64_t* starmin, float tau,
                                float err_a, float err_b, uint32_t* counts, void* stream) {
   using namespace bf;
   BF_REQUIRE(n_groups > 0 && n_stars > 0 && ld_star >= n_stars, "bf_select_count: bad sizes");
   BF_REQUIRE(gmin && starmin && counts, "bf_select_count: null pointer");
   dim3 grid(static_cast<unsigned>((n_stars + kSelThreads - 1) / kSelThreads), BF_SELECT_SPLIT);
   select_kernel<false><<<grid, kSelThreads, 0, static_cast<cudaStream_t>(stream)>>>(
-      n_groups, n_stars, ld_star, gmin, starmin, tau, err_a, err_b, counts, nullptr, nullptr);
+      n_groups, n_stars, ld_star, gmin, reinterpret_cast<const unsigned long long*>(starmin), tau,
+      err_a, err_b, counts, nullptr, nullptr, nullptr);
   BF_CHECK_LAUNCH("select_kernel<count>");
   return BF_OK;
 }
 
 extern "C" int bf_select_fill(int64_t n_groups, int64_t n_stars, int64_t ld_star,
-                              const float* gmin, const float* starmin, float tau,
+                              const float* gmin, const uint64_t* starmin, float tau,
                               float err_a, float err_b, const uint32_t* offsets,
-                              uint32_t* list, void* stream) {
+                              uint32_t* list, uint32_t* entry_star, void* stream) {
   using namespace bf;
   BF_REQUIRE(n_groups > 0 && n_stars > 0 && ld_star >= n_stars, "bf_select_fill: bad sizes");
   BF_REQUIRE(gmin && starmin && offsets && list, "bf_select_fill: null pointer");
   dim3 grid(static_cast<unsigned>((n_stars + kSelThreads - 1) / kSelThreads), BF_SELECT_SPLIT);
   select_kernel<true><<<grid, kSelThreads, 0, static_cast<cudaStream_t>(stream)>>>(
-      n_groups, n_stars, ld_star, gmin, starmin, tau, err_a, err_b, nullptr, offsets, list);
+      n_groups, n_stars, ld_star, gmin, reinterpret_cast<const unsigned long long*>(starmin), tau,
+      err_a, err_b, nullptr, offsets, list, entry_star);
   BF_CHECK_LAUNCH("select_kernel<fill>");
   return BF_OK;
 }

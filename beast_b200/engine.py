@@ -18,7 +18,8 @@ import ctypes as C
 import numpy as np
 
 from . import _cabi
-from ._cabi import GROUP, SELECT_SPLIT, STAR_BLOCK, ExactGrid, ParamTables, StarOutputs
+from ._cabi import (GROUP, SELECT_SPLIT, STAR_BLOCK, AccumScratch, ExactGrid, ParamTables,
+                    StarOutputs)
 
 _INF_BITS = 0x7F800000
 
@@ -34,27 +35,41 @@ def _ptr(t):
 
 
 class FitResult:
-    """Per-star outputs of one ``FitEngine.fit`` call (host NumPy arrays).
+    """Per-star outputs of one ``FitEngine.fit`` call (host NumPy arrays, page-locked so the
+    device->host copies run at full PCIe speed and asynchronously).
 
     Index arrays are in *filtered* model space (``j``); ``FitSetup.g0_indxs[j]`` maps to
     full-grid indices as the reference reports them (fit.py:719-728)."""
 
-    def __init__(self, ns, nq, total_bins, pair_len=0):
-        self.Pmax = np.zeros(ns)
-        self.Pmax_j = np.full(ns, -1, dtype=np.int64)
-        self.total_log_norm = np.zeros(ns)
-        self.chi2min = np.zeros(ns)
-        self.chi2min_j = np.full(ns, -1, dtype=np.int64)
-        self.n_sparse = np.zeros(ns, dtype=np.int64)
-        self.n_groups_selected = np.zeros(ns, dtype=np.int64)
-        self.exp_vals = np.zeros((ns, nq))
-        self.per_vals = np.zeros((ns, nq, 3))
-        self.pdf1d = np.zeros((ns, total_bins))
-        self.pdf2d = np.zeros((ns, pair_len)) if pair_len else None
+    _FIELDS = (("Pmax", "f8", ()), ("Pmax_j", "i8", ()), ("total_log_norm", "f8", ()),
+               ("chi2min", "f8", ()), ("chi2min_j", "i8", ()), ("n_sparse", "i4", ()),
+               ("n_groups_selected", "i8", ()))
+
+    def __init__(self, ns, nq, total_bins, pair_len=0, sparse_cap=0):
+        torch = _torch()
+        self._t = {}
+        self.ns = ns
+
+        def alloc(name, shape, dtype):
+            t = torch.empty(shape, dtype=dtype, pin_memory=True)
+            self._t[name] = t
+            setattr(self, name, t.numpy())
+
+        for name, kind, _ in self._FIELDS:
+            alloc(name, (ns,), {"f8": torch.float64, "i8": torch.int64, "i4": torch.int32}[kind])
+        alloc("exp_vals", (ns, nq), torch.float64)
+        alloc("per_vals", (ns, nq, 3), torch.float64)
+        alloc("pdf1d", (ns, total_bins), torch.float64)
+        self.pdf2d = None
+        if pair_len:
+            alloc("pdf2d", (ns, pair_len), torch.float64)
         self.sparse_off = None  # int64 [ns+1]
-        self.sparse_j = None  # int64 filtered indices
-        self.sparse_lnp = None  # float32
-        self.sparse_chi2 = None  # float32
+        self.sparse_j = self.sparse_lnp = self.sparse_chi2 = None
+        self.sparse_cap = sparse_cap
+        if sparse_cap:
+            alloc("_sp_j", (sparse_cap,), torch.int64)
+            alloc("_sp_lnp", (sparse_cap,), torch.float32)
+            alloc("_sp_chi2", (sparse_cap,), torch.float32)
 
 
 class FitEngine:
@@ -67,7 +82,7 @@ class FitEngine:
     gmin_budget_bytes : size cap of the (group x star) minimum map of one batch
     """
 
-    def __init__(self, setup, device=None, gmin_budget_bytes=8 << 30):
+    def __init__(self, setup, device=None, gmin_budget_bytes=8 << 30, scratch_budget_bytes=12 << 30):
         torch = _torch()
         self.lib = _cabi.load()
         if not torch.cuda.is_available():
@@ -87,10 +102,12 @@ class FitEngine:
         s = setup
         with torch.cuda.device(self.device):
             self.d_tiles = up(s.tiles)
+            self.d_tiles_coarse = up(s.tiles_coarse)
             self.d_msb, self.d_ivar = up(s.msb), up(s.ivar)
             self.d_lnq, self.d_lnw = up(s.lnq), up(s.lnw)
             self.d_bin_tab, self.d_q_tab = up(s.bin_tab), up(s.q_tab)
             self.d_bin_off, self.d_bin_val = up(s.bin_off), up(s.bin_val)
+            self.d_q_lin = up(s.q_lin)
             self.d_inv_scale = up((1.0 / s.band_scale).astype(np.float64))
             if s.pair_bin is not None:
                 self.d_pair_bin, self.d_pair_off = up(s.pair_bin), up(s.pair_off)
@@ -98,14 +115,18 @@ class FitEngine:
                 self.d_pair_bin = self.d_pair_off = None
         self.grid = ExactGrid(s.nb, s.n_models, s.ld_model, self.d_msb.data_ptr(),
                               self.d_ivar.data_ptr(), self.d_lnq.data_ptr(), self.d_lnw.data_ptr())
-        self.params = ParamTables(s.n_q, s.total_bins, self.d_bin_tab.data_ptr(),
-                                  self.d_q_tab.data_ptr(), self.d_bin_off.data_ptr(),
+        self.params = ParamTables(s.n_q, s.total_bins, s.max_bins, self.d_bin_tab.data_ptr(),
+                                  self.d_q_tab.data_ptr(), self.d_q_lin.data_ptr(),
+                                  self.d_bin_off.data_ptr(),
                                   self.d_bin_val.data_ptr())
         per_star = s.n_groups * 4
         mb = max(STAR_BLOCK, (gmin_budget_bytes // per_star) // STAR_BLOCK * STAR_BLOCK)
         mb = min(mb, ((2**31 - 1) // max(s.n_groups, 1)) // STAR_BLOCK * STAR_BLOCK, 32768 * STAR_BLOCK)
         self.max_batch = int(max(mb, STAR_BLOCK))
+        self.max_entries = int(max(1 << 16, scratch_budget_bytes // (GROUP * 8 + 24)))
         self.launches = 0  # kernels launched by this engine (bench.py reports it)
+        self._result_cache = {}
+        self._copy_stream = torch.cuda.Stream(device=self.device)
         self.profile = False  # when True, CUDA events bracket every stage (see stage_ms())
         self._events = []
 
@@ -144,18 +165,28 @@ class FitEngine:
     def _stream(self):
         return C.c_void_p(_torch().cuda.current_stream(self.device).cuda_stream)
 
-    def dense(self, d_flux64, n):
-        """dense sweep of one batch; returns (gmin, starmin, ld_star)"""
+    def _flux32(self, d_flux64, n):
+        torch = _torch()
+        ld = (n + STAR_BLOCK - 1) // STAR_BLOCK * STAR_BLOCK
+        f32 = torch.zeros((self.setup.nb, ld), dtype=torch.float32, device=self.device)
+        f32[:, :n] = (d_flux64 * self.d_inv_scale[None, :]).t().to(torch.float32)
+        return f32, ld
+
+    def dense(self, d_flux64, n, coarse=False):
+        """dense sweep of one batch over the full grid (or its coarse subsample);
+        returns (gmin, starmin, ld_star)"""
         torch = _torch()
         s = self.setup
-        ld = (n + STAR_BLOCK - 1) // STAR_BLOCK * STAR_BLOCK
-        f32 = torch.zeros((s.nb, ld), dtype=torch.float32, device=self.device)
-        f32[:, :n] = (d_flux64 * self.d_inv_scale[None, :]).t().to(torch.float32)
-        gmin = torch.empty((s.n_groups, ld), dtype=torch.float32, device=self.device)
-        starmin = torch.full((ld,), float("inf"), dtype=torch.float32, device=self.device)
-        tpi = self.lib.bf_dense_tiles_per_item(s.n_tiles, n, self.sm_count)
-        with self._timed("dense"):
-            _cabi.call("bf_dense_chi2", s.nb, s.n_tiles, _ptr(self.d_tiles), n, ld, _ptr(f32),
+        f32, ld = self._flux32(d_flux64, n)
+        tiles = self.d_tiles_coarse if coarse else self.d_tiles
+        n_tiles = int(tiles.shape[0])
+        gmin = torch.empty((n_tiles * (_cabi.TILE_MODELS // GROUP), ld), dtype=torch.float32,
+                           device=self.device)
+        # packed (FP32 bits << 32 | arg-min group), start at (+inf, no group)
+        starmin = torch.full((ld,), 0x7F800000FFFFFFFF, dtype=torch.int64, device=self.device)
+        tpi = self.lib.bf_dense_tiles_per_item(n_tiles, n, self.sm_count)
+        with self._timed("presort" if coarse else "dense"):
+            _cabi.call("bf_dense_chi2", s.nb, n_tiles, _ptr(tiles), n, ld, _ptr(f32),
                        _ptr(gmin), _ptr(starmin), tpi, self._stream())
         self.launches += 1
         return gmin, starmin, ld
@@ -176,11 +207,12 @@ class FitEngine:
         _cabi.call("bf_exclusive_scan_u32", nc, _ptr(counts), _ptr(offsets), _ptr(scratch), st)
         total = int(offsets[-1].item()) & 0xFFFFFFFF  # the one host sync of a batch
         lst = torch.empty(max(total, 1), dtype=torch.int32, device=self.device)
+        entry_star = torch.empty(max(total, 1), dtype=torch.int32, device=self.device)
         with self._timed("select_fill"):
             _cabi.call("bf_select_fill", s.n_groups, n, ld, _ptr(gmin), _ptr(starmin), tau,
-                       s.err_a, s.err_b, _ptr(offsets), _ptr(lst), st)
+                       s.err_a, s.err_b, _ptr(offsets), _ptr(lst), _ptr(entry_star), st)
         self.launches += 5
-        return offsets, lst, total
+        return offsets, lst, entry_star, total
 
     def _sparse_records(self, o, sparse, lnp_rng, rng, seed, star_base, d_flux, offsets, lst, mask,
                         prefix, n):
@@ -230,9 +262,15 @@ class FitEngine:
         o["sparse_j"], o["sparse_lnp"], o["sparse_chi2"] = out_j[:nrec], out_lnp[:nrec], out_chi2[:nrec]
 
     def fit_batch(self, flux, threshold=-10.0, percentiles=(16.0, 50.0, 84.0), want_pdf2d=False,
-                  sparse=None, rng=None, lnp_rng="numpy", seed=0, star_base=0):
+                  sparse=None, rng=None, lnp_rng="numpy", seed=0, star_base=0, presort=None):
         """Fit one batch (<= max_batch stars).  ``flux``: (n, nb) float64 NumPy array or
-        torch tensor (host or device).  Returns a dict of device tensors."""
+        torch tensor (host or device).  Returns a dict of device tensors in input order.
+
+        presort (default: on, except with lnp_rng="numpy" subsampling, whose random stream
+        follows catalog order): the batch is first swept against every 32nd model, stars are
+        ordered by the arg-min of that coarse sweep, and the whole pipeline runs in that order
+        -- neighbouring stars then select the same groups, so the exact pass finds its grid
+        and table lines in L2.  Outputs are put back in input order at the end."""
         torch = _torch()
         s = self.setup
         with torch.cuda.device(self.device):
@@ -242,8 +280,15 @@ class FitEngine:
             n = d_flux.shape[0]
             if n > self.max_batch:
                 raise ValueError("batch of %d stars exceeds max_batch=%d" % (n, self.max_batch))
+            if presort is None:
+                presort = not (sparse not in (None, "all") and lnp_rng == "numpy")
+            perm = None
+            if presort and n > 1:
+                _, cmin, _ = self.dense(d_flux, n, coarse=True)
+                perm = torch.argsort(cmin[:n] & 0xFFFFFFFF)
+                d_flux = d_flux[perm].contiguous()
             gmin, starmin, ld = self.dense(d_flux, n)
-            offsets, lst, total = self.select(gmin, starmin, ld, n, threshold)
+            offsets, lst, entry_star, total = self.select(gmin, starmin, ld, n, threshold)
             st = self._stream()
             dev = self.device
             pmax = torch.empty(n, dtype=torch.float64, device=dev)
@@ -265,18 +310,37 @@ class FitEngine:
             }
             mask = torch.empty(max(total, 1) * (GROUP // 32), dtype=torch.int32, device=dev)
             prefix = torch.empty(max(total, 1), dtype=torch.int32, device=dev)
+            pct = (C.c_double * 3)(*[float(x) for x in percentiles])
+            off_star = (offsets.view(-1)[:: SELECT_SPLIT].to(torch.int64) & 0xFFFFFFFF)
+            off_host = off_star.cpu().numpy()
+            # sub-ranges of stars whose lists fit the scratch budget
+            cuts, a0 = [], 0
+            while a0 < n:
+                b0 = int(np.searchsorted(off_host, off_host[a0] + self.max_entries, side="right")) - 1
+                b0 = min(n, max(b0, a0 + 1))
+                cuts.append((a0, b0))
+                a0 = b0
+            nmax = max(int(off_host[b0] - off_host[a0]) for a0, b0 in cuts)
+            w_scr = torch.empty(max(nmax, 1) * GROUP, dtype=torch.float64, device=dev)
+            p_w = torch.empty(max(nmax, 1), dtype=torch.float64, device=dev)
+            p_c = torch.empty(max(nmax, 1), dtype=torch.float64, device=dev)
+            p_j = torch.empty(max(nmax, 1), dtype=torch.int64, device=dev)
+            scr = AccumScratch(w_scr.data_ptr(), p_w.data_ptr(), p_c.data_ptr(), p_j.data_ptr())
             outs = StarOutputs(o["total_log_norm"].data_ptr(), o["chi2min"].data_ptr(),
                                o["chi2min_j"].data_ptr(), o["n_sparse"].data_ptr(),
                                o["exp_vals"].data_ptr(), o["pdf1d"].data_ptr(),
                                o["per_vals"].data_ptr(), mask.data_ptr(), prefix.data_ptr())
-            pct = (C.c_double * 3)(*[float(x) for x in percentiles])
-            with self._timed("accumulate"):
-                _cabi.call("bf_exact_accumulate", C.byref(self.grid), C.byref(self.params), n,
-                           _ptr(d_flux), _ptr(pmax), float(threshold), _ptr(offsets), _ptr(lst),
-                           pct, C.byref(outs), st)
-            self.launches += 2
-            off2 = offsets.view(-1)[:: SELECT_SPLIT]
-            o["n_groups_selected"] = (off2[1:].to(torch.int64) & 0xFFFFFFFF) - (off2[:-1].to(torch.int64) & 0xFFFFFFFF)
+            for a0, b0 in cuts:
+                base, cnt = int(off_host[a0]), int(off_host[b0] - off_host[a0])
+                with self._timed("accumulate"):
+                    _cabi.call("bf_exact_accumulate", C.byref(self.grid), C.byref(self.params),
+                               a0, b0 - a0, _ptr(d_flux), _ptr(pmax), float(threshold),
+                               _ptr(offsets), _ptr(lst), _ptr(entry_star), None, base, cnt,
+                               pct, C.byref(scr), C.byref(outs), st)
+                self.launches += 2
+            self.launches += 1
+            o["n_groups_selected"] = off_star[1:] - off_star[:-1]
+            o["n_sparse"] = o["n_sparse"]
 
             if want_pdf2d and self.d_pair_bin is not None:
                 row = int(s.pair_off[-1])
@@ -291,12 +355,44 @@ class FitEngine:
             if sparse is not None:
                 self._sparse_records(o, sparse, lnp_rng, rng, seed, star_base, d_flux, offsets, lst,
                                      mask, prefix, n)
+            if perm is not None:
+                self._unpermute(o, perm, n)
             return o
+
+    def _unpermute(self, o, perm, n):
+        """put the outputs of a presorted batch back in input order (row i of the sorted run
+        belongs to input star perm[i])"""
+        torch = _torch()
+        for name in ("Pmax", "Pmax_j", "total_log_norm", "chi2min", "chi2min_j", "n_sparse",
+                     "exp_vals", "pdf1d", "per_vals", "n_groups_selected", "pdf2d"):
+            if name in o:
+                dst = torch.empty_like(o[name])
+                dst[perm] = o[name]
+                o[name] = dst
+        if "sparse_off" in o:
+            off_s = o["sparse_off"]
+            cnt_s = off_s[1:] - off_s[:-1]
+            inv = torch.empty_like(perm)
+            inv[perm] = torch.arange(n, device=perm.device)
+            cnt = cnt_s[inv]
+            off = torch.zeros(n + 1, dtype=torch.int64, device=perm.device)
+            off[1:] = torch.cumsum(cnt, 0)
+            nrec = int(o["sparse_j"].shape[0])
+            if nrec:
+                src = torch.repeat_interleave(off_s[:-1][inv] - off[:-1], cnt) + torch.arange(
+                    nrec, device=perm.device)
+                for name in ("sparse_j", "sparse_lnp", "sparse_chi2"):
+                    o[name] = o[name][src]
+            o["sparse_off"] = off
 
     # ------------------------------------------------------------------------------
     def fit(self, fluxes, threshold=-10.0, percentiles=(16.0, 50.0, 84.0), want_pdf2d=False,
-            sparse=None, batch=None, rng=None, lnp_rng="numpy", seed=0):
-        """Fit all stars of ``fluxes`` (ns, nb) in batches; returns a host ``FitResult``."""
+            sparse=None, batch=None, rng=None, lnp_rng="numpy", seed=0, reuse_buffers=False):
+        """Fit all stars of ``fluxes`` (ns, nb) in batches; returns a host ``FitResult``.
+
+        Results are copied device->host asynchronously into page-locked arrays while the next
+        batch computes.  With ``reuse_buffers=True`` the engine keeps those arrays and hands
+        the same ones back on the next call of the same shape (they are overwritten then)."""
         torch = _torch()
         s = self.setup
         fluxes = np.ascontiguousarray(fluxes, dtype=np.float64)
@@ -305,34 +401,58 @@ class FitEngine:
             raise ValueError("fluxes must have shape (n_stars, %d)" % s.nb)
         bs = min(batch or self.max_batch, self.max_batch)
         pair_len = int(s.pair_off[-1]) if (want_pdf2d and s.pair_off is not None) else 0
-        res = FitResult(ns, s.n_q, s.total_bins, pair_len)
-        sp_j, sp_l, sp_c, sp_cnt = [], [], [], []
-        for a in range(0, ns, bs):
-            b = min(ns, a + bs)
-            o = self.fit_batch(fluxes[a:b], threshold, percentiles, want_pdf2d, sparse, rng,
-                               lnp_rng, seed, a)
-            res.Pmax[a:b] = o["Pmax"].cpu().numpy()
-            res.Pmax_j[a:b] = o["Pmax_j"].cpu().numpy()
-            res.total_log_norm[a:b] = o["total_log_norm"].cpu().numpy()
-            res.chi2min[a:b] = o["chi2min"].cpu().numpy()
-            res.chi2min_j[a:b] = o["chi2min_j"].cpu().numpy()
-            res.n_sparse[a:b] = o["n_sparse"].cpu().numpy().astype(np.int64) & 0xFFFFFFFF
-            res.n_groups_selected[a:b] = o["n_groups_selected"].cpu().numpy()
-            res.exp_vals[a:b] = o["exp_vals"].cpu().numpy()
-            res.per_vals[a:b] = o["per_vals"].cpu().numpy()
-            res.pdf1d[a:b] = o["pdf1d"].cpu().numpy()
-            if pair_len:
-                res.pdf2d[a:b] = o["pdf2d"].cpu().numpy()
-            if sparse is not None:
-                sp_cnt.append(np.diff(o["sparse_off"].cpu().numpy()))
-                sp_j.append(o["sparse_j"].cpu().numpy())
-                sp_l.append(o["sparse_lnp"].cpu().numpy())
-                sp_c.append(o["sparse_chi2"].cpu().numpy())
+        cap = ns * int(sparse) if (sparse is not None and sparse != "all") else 0
+        key = (ns, pair_len, cap)
+        res = self._result_cache.get(key) if reuse_buffers else None
+        if res is None:
+            res = FitResult(ns, s.n_q, s.total_bins, pair_len, cap)
+            if reuse_buffers:
+                self._result_cache = {key: res}
+        t = res._t
+        sp_parts, sp_cnt, keep = [], [], []
+        sp_pos = 0
+        with torch.cuda.device(self.device):
+            main = torch.cuda.current_stream(self.device)
+            copy_stream = self._copy_stream
+            for a in range(0, ns, bs):
+                b = min(ns, a + bs)
+                o = self.fit_batch(fluxes[a:b], threshold, percentiles, want_pdf2d, sparse, rng,
+                                   lnp_rng, seed, a)
+                done = torch.cuda.Event()
+                done.record(main)
+                copy_stream.wait_event(done)
+                with torch.cuda.stream(copy_stream):
+                    names = ["Pmax", "Pmax_j", "total_log_norm", "chi2min", "chi2min_j", "n_sparse",
+                             "n_groups_selected", "exp_vals", "per_vals", "pdf1d"]
+                    if pair_len:
+                        names.append("pdf2d")
+                    for name in names:
+                        o[name].record_stream(copy_stream)
+                        t[name][a:b].copy_(o[name], non_blocking=True)
+                    if sparse is not None:
+                        off = o["sparse_off"]
+                        nrec = int(o["sparse_j"].shape[0])
+                        sp_cnt.append(off)
+                        if cap:
+                            for name, src in (("_sp_j", "sparse_j"), ("_sp_lnp", "sparse_lnp"),
+                                              ("_sp_chi2", "sparse_chi2")):
+                                o[src].record_stream(copy_stream)
+                                t[name][sp_pos:sp_pos + nrec].copy_(o[src], non_blocking=True)
+                            sp_pos += nrec
+                        else:
+                            sp_parts.append([o["sparse_j"].cpu(), o["sparse_lnp"].cpu(),
+                                             o["sparse_chi2"].cpu()])
+                keep.append(o)
+            copy_stream.synchronize()
+            main.synchronize()
         if sparse is not None:
             res.sparse_off = np.zeros(ns + 1, dtype=np.int64)
-            res.sparse_off[1:] = np.cumsum(np.concatenate(sp_cnt))
-            res.sparse_j = np.concatenate(sp_j)
-            res.sparse_lnp = np.concatenate(sp_l)
-            res.sparse_chi2 = np.concatenate(sp_c)
-        torch.cuda.synchronize(self.device)
+            res.sparse_off[1:] = np.cumsum(np.concatenate([np.diff(x.cpu().numpy()) for x in sp_cnt]))
+            if cap:
+                n = int(res.sparse_off[-1])
+                res.sparse_j, res.sparse_lnp, res.sparse_chi2 = res._sp_j[:n], res._sp_lnp[:n], res._sp_chi2[:n]
+            else:
+                res.sparse_j = np.concatenate([p[0].numpy() for p in sp_parts])
+                res.sparse_lnp = np.concatenate([p[1].numpy() for p in sp_parts])
+                res.sparse_chi2 = np.concatenate([p[2].numpy() for p in sp_parts])
         return res

@@ -32,6 +32,7 @@ LOG_SPACED_PARAMS = {"M_ini", "M_act", "radius"}
 SYMLOG_THRESHOLD = 1e-20
 FP32_U = 2.0**-24
 ERR_SAFETY = 4.0
+COARSE_STRIDE = 32
 
 
 def symlog(y, C=SYMLOG_THRESHOLD):
@@ -182,6 +183,7 @@ class FitSetup:
         self.bin_off = np.zeros(nq + 1, dtype=np.int32)
         self.bin_off[1:] = np.cumsum([b.nbins for b in self.bins])
         self.total_bins = int(self.bin_off[-1])
+        self.max_bins = int(max(b.nbins for b in self.bins))
         self.bin_val = np.concatenate([b.bin_vals for b in self.bins]).astype(np.float64)
 
         # ---- 2D bins -------------------------------------------------------------
@@ -240,6 +242,14 @@ class FitSetup:
         rows[2 * nb, :nm] = -2.0 * (c - self.c_off)
         self.tiles = np.ascontiguousarray(
             rows.reshape(2 * nb + 1, self.n_tiles, TILE_MODELS).transpose(1, 0, 2))
+        # every COARSE_STRIDE-th model, for the cheap sweep that orders the stars of a batch
+        sub = rows[:, :nm:COARSE_STRIDE]
+        ncp = _pad_to(sub.shape[1], TILE_MODELS)
+        crow = np.zeros((2 * nb + 1, ncp), dtype=np.float32)
+        crow[2 * nb, :] = 3.0e38
+        crow[:, :sub.shape[1]] = sub
+        self.tiles_coarse = np.ascontiguousarray(
+            crow.reshape(2 * nb + 1, ncp // TILE_MODELS, TILE_MODELS).transpose(1, 0, 2))
         a_max = float(np.abs(a).max())
         self.err_a = float(ERR_SAFETY * 6.0 * FP32_U * math.sqrt(nb) * a_max)
         self.err_b = float(ERR_SAFETY * 16.0 * FP32_U)
@@ -247,10 +257,18 @@ class FitSetup:
         # ---- chunk-major parameter tables ---------------------------------------
         nch = nmp // CHUNK
         btab = np.zeros((nq, nmp), dtype=np.uint8)
-        qtab = np.zeros((nq, nmp), dtype=np.float64)
+        # parameter values for the expectations in 32-bit fixed point over each parameter's
+        # range: q = q_lin[k,0] + q_lin[k,1] * fix, |rounding| <= range * 2^-33
+        qtab = np.zeros((nq, nmp), dtype=np.int32)
+        self.q_lin = np.zeros((nq, 2), dtype=np.float64)
         for k in range(nq):
             btab[k, :nm] = self.bins[k].bin_num[g0]
-            qtab[k, :nm] = self.qcols[k][g0]
+            col = self.qcols[k][g0]
+            lo, hi = float(col.min()), float(col.max())
+            scale = (hi - lo) / 4294967294.0
+            self.q_lin[k] = (0.5 * (lo + hi), scale)
+            if scale > 0:
+                qtab[k, :nm] = np.rint((col - self.q_lin[k, 0]) / scale).astype(np.int64).astype(np.int32)
         self.bin_tab = np.ascontiguousarray(btab.reshape(nq, nch, CHUNK).transpose(1, 0, 2))
         self.q_tab = np.ascontiguousarray(qtab.reshape(nq, nch, CHUNK).transpose(1, 0, 2))
         if self.pairs:

@@ -62,12 +62,14 @@ int bf_device_info(int device, int* sm_count, int* smem_optin_bytes, int* clock_
  * flux  : [nb][ld_star] float, observed flux / s_b, star-fastest.
  * gmin  : out [n_tiles*BF_TILE_MODELS/BF_GROUP][ld_star] float,
  *         min over the group of  acc = chi2 + c2  (= -2 (lnP - c_off)) in FP32.
- * starmin : in/out [ld_star] float, atomically lowered to min over all models
- *         (caller initialises to +inf bits / 0x7f800000).
+ * starmin : in/out [ld_star] uint64, packed (FP32 bits of the minimum << 32 | group that
+ *         holds it), atomically lowered over all models; caller initialises every entry to
+ *         0x7f800000ffffffff (+inf, no group).  The arg-min group lets the caller order
+ *         stars so that neighbours touch the same part of the grid.
  * ld_star must be a multiple of BF_STAR_BLOCK and >= n_stars.
  * ------------------------------------------------------------------------- */
 int bf_dense_chi2(int nb, int64_t n_tiles, const float* tiles, int64_t n_stars,
-                  int64_t ld_star, const float* flux, float* gmin, float* starmin,
+                  int64_t ld_star, const float* flux, float* gmin, uint64_t* starmin,
                   int tiles_per_item, void* stream);
 
 /* Suggested tiles_per_item for a device with `sm_count` SMs. */
@@ -84,13 +86,14 @@ int bf_dense_tiles_per_item(int64_t n_tiles, int64_t n_stars, int sm_count);
  * counts : out [n_stars][BF_SELECT_SPLIT] uint32 (bf_select_count)
  * offsets: in  [n_stars*BF_SELECT_SPLIT + 1] uint32 exclusive scan of counts
  * list   : out group ids, ascending per star (bf_select_fill)
+ * entry_star : optional out, star index of every list position (same length as list)
  * ------------------------------------------------------------------------- */
 int bf_select_count(int64_t n_groups, int64_t n_stars, int64_t ld_star, const float* gmin,
-                    const float* starmin, float tau, float err_a, float err_b, uint32_t* counts,
+                    const uint64_t* starmin, float tau, float err_a, float err_b, uint32_t* counts,
                     void* stream);
 int bf_select_fill(int64_t n_groups, int64_t n_stars, int64_t ld_star, const float* gmin,
-                   const float* starmin, float tau, float err_a, float err_b,
-                   const uint32_t* offsets, uint32_t* list, void* stream);
+                   const uint64_t* starmin, float tau, float err_a, float err_b,
+                   const uint32_t* offsets, uint32_t* list, uint32_t* entry_star, void* stream);
 
 /* Exclusive prefix sum of n uint32 (out[n] = total).  scratch: >= bf_scan_scratch_elems(n)
  * uint32.  Plumbing for the variable-length per-star lists. */
@@ -122,7 +125,7 @@ typedef struct {
  * flux64 [n_stars][nb] double.  pmax [n_stars] double, pmax_j [n_stars] int64 (filtered index,
  * -1 when the star has no finite lnP). */
 int bf_exact_max(const bf_exact_grid* grid, int64_t n_stars, int64_t ld_star,
-                 const double* flux64, const float* gmin, const float* starmin, float err_a,
+                 const double* flux64, const float* gmin, const uint64_t* starmin, float err_a,
                  float err_b, const uint32_t* offsets, const uint32_t* list, double* pmax,
                  int64_t* pmax_j, void* stream);
 
@@ -130,15 +133,21 @@ int bf_exact_max(const bf_exact_grid* grid, int64_t n_stars, int64_t ld_star,
  * Per-parameter tables for the marginal PDFs / expectations, chunk-major:
  *   bin_tab [ld_model/8][n_q][8] uint8   0-based pdf1d bin of each model
  *                                        (np.digitize result, pdf1d.py:90)
- *   q_tab   [ld_model/8][n_q][8] double  parameter value of each model (fit.py:733-737)
+ *   q_tab   [ld_model/8][n_q][8] int32   parameter value of each model (fit.py:733-737) in
+ *                                        32-bit fixed point: q = q_lin[2k] + q_lin[2k+1] * fix,
+ *                                        i.e. a rounding of 2^-33 of the parameter's range;
+ *                                        sums are accumulated in FP64
+ *   q_lin   [n_q][2] double              offset and scale of that encoding
  *   bin_off [n_q+1] int32                start of parameter k's bins in a star's pdf row
  *   bin_val [bin_off[n_q]] double        bin centres (pdf1d.bin_vals)
  * ------------------------------------------------------------------------- */
 typedef struct {
   int n_q;
   int total_bins;
+  int max_bins; /* largest bin count of any parameter (<= 256) */
   const uint8_t* bin_tab;
-  const double* q_tab;
+  const int32_t* q_tab;
+  const double* q_lin;
   const int32_t* bin_off;
   const double* bin_val;
 } bf_param_tables;
@@ -155,12 +164,34 @@ typedef struct {
   uint32_t* member_prefix;/* [n_list] members of the star before this group        */
 } bf_star_outputs;
 
+/* Scratch of the sparse pass, one slot per listed group of the stars being processed
+ * (slot = list position - entry_base). */
+typedef struct {
+  double* weights;      /* [n_entries][BF_GROUP] exp(lnP - Pmax) of members, 0 otherwise */
+  double* part_wsum;    /* [n_entries] sum of the group's weights                        */
+  double* part_chi2;    /* [n_entries] smallest member chi2 of the group                 */
+  int64_t* part_chi2_j; /* [n_entries] its model index (-1: no member)                   */
+} bf_accum_scratch;
+
 /* Sparse pass: exact sparse set, weights, normalisation, chi2min, expectations, 1D PDFs
- * and p16/p50/p84 (fit.py:670-755).  percentiles [3] host doubles in percent. */
+ * and p16/p50/p84 (fit.py:670-755) for stars [star_begin, star_begin + n_stars) of the
+ * batch-wide arrays passed in.
+ * Two launches: (1) one warp per listed group evaluates the exact lnP of its 64 models and
+ * stores membership bits, weights and per-group partial sums; (2) one block per star builds
+ * the histograms, expectations and percentiles from them.
+ * entry_star : [list length] star index of every list position (from bf_select_fill).
+ * star_order : optional [n_stars] int32 permutation; block i works on star star_order[i]
+ *              (callers sort by arg-min group so that concurrent blocks share L2 lines).
+ * entry_base / n_entries : list range of those stars,
+ *              [offsets[star_begin*SPLIT], offsets[(star_begin+n_stars)*SPLIT]), covered by `scratch`.
+ * percentiles_host : [3] host doubles in percent. */
 int bf_exact_accumulate(const bf_exact_grid* grid, const bf_param_tables* params,
-                        int64_t n_stars, const double* flux64, const double* pmax,
+                        int64_t star_begin, int64_t n_stars, const double* flux64, const double* pmax,
                         double threshold, const uint32_t* offsets, const uint32_t* list,
-                        const double* percentiles_host, const bf_star_outputs* out, void* stream);
+                        const uint32_t* entry_star, const int32_t* star_order,
+                        int64_t entry_base, int64_t n_entries,
+                        const double* percentiles_host, const bf_accum_scratch* scratch,
+                        const bf_star_outputs* out, void* stream);
 
 /* Sparse lnP record (fit.py:693-709): for star s, entries [rec_off[s], rec_off[s+1]) of
  * `ranks` hold 0-based positions inside the star's ascending sparse set; outputs the filtered

@@ -63,3 +63,42 @@ def test_batching_is_invisible():
     for name in ("Pmax", "Pmax_j", "total_log_norm", "chi2min", "chi2min_j", "exp_vals", "pdf1d",
                  "per_vals", "sparse_j", "sparse_lnp"):
         np.testing.assert_array_equal(getattr(a, name), getattr(b, name), err_msg=name)
+
+
+def test_device_subsample_is_a_valid_draw():
+    """lnp_npts subsample drawn on the device: min(|S|, npts) distinct members of the exact
+    sparse set per star, with their exact lnP (fit.py:693-709)"""
+    g, nz, obs, args, ref = util.load_golden("small_thr10")
+    setup, eng = _engine(g, nz, args)
+    full = eng.fit(obs.fluxes, threshold=args["threshold"], sparse="all")
+    npts = 20
+    sub = eng.fit(obs.fluxes, threshold=args["threshold"], sparse=npts, lnp_rng="device", seed=3)
+    again = eng.fit(obs.fluxes, threshold=args["threshold"], sparse=npts, lnp_rng="device", seed=3)
+    np.testing.assert_array_equal(sub.sparse_j, again.sparse_j)
+    for e in range(len(obs)):
+        fa, fb = full.sparse_off[e], full.sparse_off[e + 1]
+        sa, sb = sub.sparse_off[e], sub.sparse_off[e + 1]
+        assert sb - sa == min(fb - fa, npts)
+        picked = sub.sparse_j[sa:sb]
+        assert len(set(picked.tolist())) == sb - sa
+        lookup = dict(zip(full.sparse_j[fa:fb].tolist(), full.sparse_lnp[fa:fb].tolist()))
+        for j, v in zip(picked.tolist(), sub.sparse_lnp[sa:sb].tolist()):
+            assert lookup[j] == v
+
+
+def test_numpy_subsample_follows_reference_stream():
+    """lnp_rng="numpy": the ranks are np.random.choice(|S|, npts, replace=False) in catalog
+    order, the call the reference makes (fit.py:696)"""
+    g, nz, obs, args, ref = util.load_golden("small_thr10")
+    setup, eng = _engine(g, nz, args)
+    full = eng.fit(obs.fluxes, threshold=args["threshold"], sparse="all")
+    npts = 20
+    np.random.seed(1234)
+    sub = eng.fit(obs.fluxes, threshold=args["threshold"], sparse=npts, lnp_rng="numpy")
+    np.random.seed(1234)
+    for e in range(len(obs)):
+        fa, fb = full.sparse_off[e], full.sparse_off[e + 1]
+        indx = np.arange(fb - fa)
+        rindx = np.random.choice(indx, size=npts, replace=False) if npts < len(indx) else indx
+        sa, sb = sub.sparse_off[e], sub.sparse_off[e + 1]
+        np.testing.assert_array_equal(sub.sparse_j[sa:sb], full.sparse_j[fa:fb][rindx])

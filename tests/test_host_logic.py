@@ -1,0 +1,134 @@
+"""Host-side mirror of the reference interface: setup, layouts, errors, writers (CPU only)."""
+import numpy as np
+import pytest
+
+from beast_b200 import fitsio, synth
+from beast_b200.gridprep import FitSetup
+from oracle import fit_oracle as fo
+from tests import util
+
+
+@pytest.fixture(scope="module")
+def small():
+    g = synth.make_sedgrid("tiny", seed=21)
+    g["weight"][::5] = 0.0
+    nz = synth.make_noisemodel(g)
+    obs = synth.make_observations(g, nz, 6, seed=22)
+    return g, nz, obs
+
+
+def test_setup_matches_oracle_setup(small):
+    g, nz, obs = small
+    keys = fo.default_keys(g)
+    with pytest.warns(UserWarning, match="zero weight"):
+        st = FitSetup(g, nz, list(keys), max_nbins=50, pdf2d_param_list=["Av", "logT"], make_pdf2d=True)
+    ost = fo.OracleSetup(g, nz, keys, max_nbins=50, pdf2d_param_list=["Av", "logT"], make_pdf2d=True)
+    assert st.qnames == ost.qnames
+    np.testing.assert_array_equal(st.g0_indxs, ost.g0_indxs)
+    nm = st.n_models
+    np.testing.assert_array_equal(st.lnw[:nm], ost.g0_weights)
+    np.testing.assert_array_equal(st.msb[:, :nm], ost.model_wbias[ost.g0_indxs].T)
+    np.testing.assert_array_equal(st.ivar[:, :nm], ost.ivar[ost.g0_indxs].T)
+    np.testing.assert_array_equal(st.lnq[:nm], ost.lnq[ost.g0_indxs])
+    for k, (b, ob) in enumerate(zip(st.bins, ost.bins)):
+        np.testing.assert_array_equal(b.bin_vals, ob.bin_vals)
+        np.testing.assert_array_equal(b.bin_num, ob.bin_num)
+    assert [p.name for p in st.pairs] == ost.pairs
+    for p, op in zip(st.pairs, ost.bins2d):
+        np.testing.assert_array_equal(p.bin_num, op.bin_num)
+
+
+def test_device_layouts(small):
+    g, nz, obs = small
+    st = FitSetup(g, nz, ["Av", "M_ini", "logT"], max_nbins=20)
+    nb, nm = st.nb, st.n_models
+    assert st.ld_model % 256 == 0 and st.tiles.shape == (st.n_tiles, 2 * nb + 1, 256)
+    rows = st.tiles.transpose(1, 0, 2).reshape(2 * nb + 1, -1)
+    # acc = sum (f*r - a)^2 + c2 reproduces -2 (lnP - c_off) of the oracle
+    ost = fo.OracleSetup(g, nz, ["Av", "M_ini", "logT"], max_nbins=20)
+    f = obs.fluxes[0]
+    lnp, _ = fo.lnp_chi2_nm(f, ost.model_wbias, ost.ivar, lnq=ost.lnq)
+    lnp = lnp[ost.g0_indxs] + ost.g0_weights
+    fs = (f / st.band_scale).astype(np.float32).astype(np.float64)
+    acc = rows[2 * nb, :nm].astype(np.float64)
+    for b in range(nb):
+        acc += (fs[b] * rows[b, :nm] + rows[nb + b, :nm]) ** 2
+    np.testing.assert_allclose(-0.5 * acc + st.c_off, lnp, rtol=0, atol=5e-3)
+    assert np.all(rows[2 * nb, nm:] > 1e38) and rows[2 * nb, :nm].min() == 0.0
+    # chunk-major tables
+    assert st.bin_tab.shape == (st.ld_model // 8, st.n_q, 8) and st.bin_tab.dtype == np.uint8
+    j = 37
+    for k in range(st.n_q):
+        assert st.bin_tab[j // 8, k, j % 8] == st.bins[k].bin_num[st.g0_indxs[j]]
+        dec = st.q_lin[k, 0] + st.q_lin[k, 1] * float(st.q_tab[j // 8, k, j % 8])
+        col = st.qcols[k][st.g0_indxs]
+        assert abs(dec - col[j]) <= (col.max() - col.min()) * 2.0**-32 + 1e-300
+    assert st.err_a > 0 and st.err_b > 0
+
+
+def test_error_conventions(small):
+    g, nz, obs = small
+    bad = dict(nz)
+    bad["completeness"] = nz["completeness"].copy()
+    bad["completeness"][0, 0] = 0.0
+    with pytest.raises(ValueError, match="models with zero completeness present"):
+        FitSetup(g, bad, ["Av"])
+    with pytest.raises(KeyError, match="pdf2d_param_list cannot be None"):
+        FitSetup(g, nz, ["Av"], make_pdf2d=True)
+    from beast_b200 import fit
+
+    with pytest.raises(KeyError, match='Key "nope" not recognized'):
+        fit.summary_table_memory(obs, nz, g, keys=["Av", "nope"])
+    with pytest.raises(KeyError, match="pdf2d_param_list cannot be None"):
+        fit.summary_table_memory(obs, nz, g, keys=["Av"], pdf2d_outname="x.fits")
+    cov = dict(nz)
+    cov["q_norm"] = np.zeros(len(g))
+    cov["icov_diag"] = nz["error"] ** -2
+    cov["icov_offdiag"] = np.zeros((len(g), 15))
+    with pytest.raises(NotImplementedError, match="full-covariance"):
+        FitSetup(g, cov, ["Av"])
+    FitSetup(g, cov, ["Av"], use_full_cov_matrix=False)
+
+
+def test_fits_round_trip(tmp_path):
+    a = np.arange(12.0).reshape(3, 4)
+    b = np.arange(24.0).reshape(2, 3, 4)
+    p = str(tmp_path / "img.fits")
+    fitsio.write_image_file(p, [a, b], ["Av", "Av+logT"])
+    hdus = fitsio.read_fits(p)
+    assert hdus[0][1].shape == (2, 2) and not hdus[0][1].any()
+    assert hdus[1][0]["EXTNAME"] == "Av" and hdus[1][0]["XTENSION"] == "IMAGE"
+    np.testing.assert_array_equal(hdus[1][1], a)
+    np.testing.assert_array_equal(hdus[2][1], b)
+    assert hdus[2][0]["NAXIS1"] == 4 and hdus[2][0]["NAXIS3"] == 2
+    t = str(tmp_path / "tab.fits")
+    cols = {"Name": np.array(["PHAT J1", "x"]), "Av_Best": np.array([0.5, 1.5]),
+            "Pmax_indx": np.array([7, 9])}
+    fitsio.write_table_file(t, [cols, {"filternames": np.array(["F1", "F22"]), "wavelengths": np.array([1., 2.])}])
+    hd = fitsio.read_fits(t)
+    assert list(hd[1][1]) == ["Name", "Av_Best", "Pmax_indx"]
+    assert list(hd[1][1]["Name"]) == ["PHAT J1", "x"] and hd[1][1]["Pmax_indx"].dtype.kind == "i"
+    np.testing.assert_array_equal(hd[1][1]["Av_Best"], [0.5, 1.5])
+    assert list(hd[2][1]["filternames"]) == ["F1", "F22"]
+    import os
+
+    assert os.path.getsize(t) % 2880 == 0 and os.path.getsize(p) % 2880 == 0
+
+
+def test_iau_names():
+    from beast_b200.fit import IAU_names_and_extra_info
+
+    obs = synth.SyntheticObservations(np.ones((2, 6)), synth.PHAT_FILTERS, ra=[10.684708, 11.0],
+                                      dec=[41.26875, -0.5])
+    r = IAU_names_and_extra_info(obs, surveyname="PHAT")
+    assert r["Name"][0] == "PHAT J004244.3299+411607.500"
+    assert r["Name"][1].endswith("-003000.000")
+    assert set(synth.PHAT_FILTERS) <= set(r) and "RA" in r and "DEC" in r
+    noname = IAU_names_and_extra_info(synth.SyntheticObservations(np.ones((3, 6)), synth.PHAT_FILTERS))
+    assert noname["Name"] == ["noname"] * 3
+
+
+def test_golden_fixture_inputs_are_self_contained():
+    g, nz, obs, args, ref = util.load_golden("tiny_thr10_pdf2d")
+    assert len(g) == 1920 and obs.fluxes.shape == (16, 6) and args["threshold"] == -10.0
+    assert (g["weight"] == 0).sum() > 0
