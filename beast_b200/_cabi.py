@@ -90,6 +90,7 @@ PROTOTYPES = {
                                  C.c_float, c_void_p, c_void_p, c_void_p, c_void_p]),
     "bf_scan_scratch_elems": (i64, [i64]),
     "bf_exclusive_scan_u32": (C.c_int, [i64, c_void_p, c_void_p, c_void_p, c_void_p]),
+    "bf_exclusive_scan_u32_noalloc": (C.c_int, [i64, c_void_p, c_void_p, c_void_p]),
     "bf_exact_max": (C.c_int, [C.POINTER(ExactGrid), i64, i64, c_void_p, c_void_p, c_void_p,
                                C.c_float, C.c_float, c_void_p, c_void_p, c_void_p, c_void_p,
                                c_void_p]),

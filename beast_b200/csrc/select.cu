@@ -146,6 +146,12 @@ scan_apply(int64_t n, const uint32_t* __restrict__ in, const uint32_t* __restric
   }
 }
 
+// ---- scratch for bf_exclusive_scan_u32_noalloc ------------------------------------------
+// One tile sum per 2048 input elements.  Lives in the module image: every GPU that loads this
+// library carries these 256 KiB until the process exits.
+constexpr int64_t kStaticScanTiles = 65536;
+static __device__ __align__(256) uint32_t g_scan_tile_sums[kStaticScanTiles];
+
 static int run_scan(int64_t n, const uint32_t* in, uint32_t* out, uint32_t* scratch,
                     cudaStream_t st) {
   const int64_t n_tiles = (n + kScanTile - 1) / kScanTile;
@@ -201,4 +207,39 @@ extern "C" int bf_exclusive_scan_u32(int64_t n, const uint32_t* in, uint32_t* ou
   BF_REQUIRE(in && out && scratch, "bf_exclusive_scan_u32: null pointer");
   BF_REQUIRE((n + kScanTile - 1) / kScanTile < (1LL << 31), "bf_exclusive_scan_u32: n too large");
   return run_scan(n, in, out, scratch, static_cast<cudaStream_t>(stream));
+}
+
+/* Prefix sum for callers that cannot give the library any scratch memory -- see the header.
+ *
+ * `g_scan_tile_sums` above is only a host-side handle for the device array: passing that name
+ * to a kernel from host code would hand the kernel a host address.  The real device address
+ * is looked up with cudaGetSymbolAddress, once per GPU, while that GPU is the current device,
+ * and remembered per device ordinal. */
+extern "C" int bf_exclusive_scan_u32_noalloc(int64_t n, const uint32_t* in, uint32_t* out,
+                                             void* stream) {
+  using namespace bf;
+  BF_REQUIRE(n > 0, "bf_exclusive_scan_u32_noalloc: n must be positive");
+  BF_REQUIRE(in && out, "bf_exclusive_scan_u32_noalloc: null pointer");
+  const int64_t n_tiles = (n + kScanTile - 1) / kScanTile;
+  if (n_tiles > kStaticScanTiles) {
+    set_error("bf_exclusive_scan_u32_noalloc: n=%lld exceeds the built-in scratch (at most %lld "
+              "elements); use bf_exclusive_scan_u32 with caller-provided scratch instead",
+              static_cast<long long>(n), static_cast<long long>(kStaticScanTiles * kScanTile));
+    return BF_ERR_TOO_LARGE;
+  }
+  int dev = 0;
+  BF_CUDA_TRY(cudaGetDevice(&dev));
+  static uint32_t* scratch_of_device[64] = {};
+  if (dev < 0 || dev >= 64) {
+    set_error("bf_exclusive_scan_u32_noalloc: device ordinal %d not supported", dev);
+    return BF_ERR_UNSUPPORTED;
+  }
+  if (scratch_of_device[dev] == nullptr) {
+    uint32_t* p = nullptr;
+    BF_CUDA_TRY(cudaGetSymbolAddress(reinterpret_cast<void**>(&p), g_scan_tile_sums));
+    scratch_of_device[dev] = p;
+  }
+  // every tile sum of this call is written by the first kernel before the second reads it,
+  // so nothing left over from an earlier call has to be cleared
+  return run_scan(n, in, out, scratch_of_device[dev], static_cast<cudaStream_t>(stream));
 }

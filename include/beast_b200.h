@@ -101,6 +101,27 @@ int64_t bf_scan_scratch_elems(int64_t n);
 int bf_exclusive_scan_u32(int64_t n, const uint32_t* in, uint32_t* out, uint32_t* scratch,
                           void* stream);
 
+/* Same prefix sum for callers that cannot supply scratch.  (No counterpart in the reference;
+ * this exists for hosts of the library, not for BEAST.)
+ *
+ * Who needs it: an application that has handed all of a GPU's memory to its own arena and
+ * treats any further cudaMalloc as an error, or a plugin slot whose contract forbids allocating
+ * (and the implicit device-wide synchronisation that cudaMalloc/cudaFree bring) once the
+ * pipeline is running.  Such a caller still owns `in` and `out`, but has nowhere to put the
+ * tile sums, so they live in a fixed array inside the library image instead.
+ *
+ * Limits and rules:
+ *  - n <= 65536 * 2048 = 134,217,728 elements; larger inputs are refused with BF_ERR_TOO_LARGE
+ *    (use bf_exclusive_scan_u32).  The array costs 256 KiB on every GPU that loads the library,
+ *    for the life of the process.
+ *  - The first call on each GPU looks up the array's device address (with that GPU current);
+ *    make that first call before starting any stream capture.
+ *  - All calls on one GPU share the array.  Its previous contents never matter (each call
+ *    overwrites what it later reads), but two calls that overlap on the GPU -- different streams,
+ *    or different host threads -- race on it: serialise them.
+ *  - Nothing is allocated or freed, on host or device. */
+int bf_exclusive_scan_u32_noalloc(int64_t n, const uint32_t* in, uint32_t* out, void* stream);
+
 /* ---------------------------------------------------------------------------
  * Exact (FP64) grid, band-major, ld_model = padded model count:
  *   msb  [nb][ld_model]  seds+bias            (fit.py:463)
