@@ -98,7 +98,7 @@ PROTOTYPES = {
                                       c_void_p, C.c_double, c_void_p, c_void_p, c_void_p, c_void_p, i64,
                                       i64,
                                       C.POINTER(C.c_double), C.POINTER(AccumScratch),
-                                      C.POINTER(StarOutputs), c_void_p]),
+                                      C.POINTER(StarOutputs), c_void_p, c_void_p]),
     "bf_sparse_gather": (C.c_int, [C.POINTER(ExactGrid), i64, c_void_p, c_void_p, c_void_p,
                                    c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p,
                                    c_void_p, c_void_p]),

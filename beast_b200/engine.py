@@ -127,6 +127,7 @@ class FitEngine:
         self.launches = 0  # kernels launched by this engine (bench.py reports it)
         self._result_cache = {}
         self._copy_stream = torch.cuda.Stream(device=self.device)
+        self._aux_stream = torch.cuda.Stream(device=self.device)
         self.profile = False  # when True, CUDA events bracket every stage (see stage_ms())
         self._events = []
 
@@ -336,9 +337,9 @@ class FitEngine:
                     _cabi.call("bf_exact_accumulate", C.byref(self.grid), C.byref(self.params),
                                a0, b0 - a0, _ptr(d_flux), _ptr(pmax), float(threshold),
                                _ptr(offsets), _ptr(lst), _ptr(entry_star), None, base, cnt,
-                               pct, C.byref(scr), C.byref(outs), st)
-                self.launches += 2
-            self.launches += 1
+                               pct, C.byref(scr), C.byref(outs), st,
+                               C.c_void_p(self._aux_stream.cuda_stream))
+                self.launches += 3
             o["n_groups_selected"] = off_star[1:] - off_star[:-1]
             o["n_sparse"] = o["n_sparse"]
 

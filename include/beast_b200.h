@@ -197,22 +197,24 @@ typedef struct {
 /* Sparse pass: exact sparse set, weights, normalisation, chi2min, expectations, 1D PDFs
  * and p16/p50/p84 (fit.py:670-755) for stars [star_begin, star_begin + n_stars) of the
  * batch-wide arrays passed in.
- * Two launches: (1) one warp per listed group evaluates the exact lnP of its 64 models and
- * stores membership bits, weights and per-group partial sums; (2) one block per star builds
- * the histograms, expectations and percentiles from them.
+ * Three launches: (1) one warp per listed group evaluates the exact lnP of its 64 models and
+ * stores membership bits, weights and per-group partial sums; (2) one block per star sums
+ * w*q into the expectations; (3) one block per star builds the histograms and percentiles.
  * entry_star : [list length] star index of every list position (from bf_select_fill).
  * star_order : optional [n_stars] int32 permutation; block i works on star star_order[i]
  *              (callers sort by arg-min group so that concurrent blocks share L2 lines).
  * entry_base / n_entries : list range of those stars,
  *              [offsets[star_begin*SPLIT], offsets[(star_begin+n_stars)*SPLIT]), covered by `scratch`.
- * percentiles_host : [3] host doubles in percent. */
+ * percentiles_host : [3] host doubles in percent.
+ * aux_stream : optional second stream; when given, the expectation kernel runs on it next to
+ *              the histogram kernel (ordered by events; `stream` has joined it on return). */
 int bf_exact_accumulate(const bf_exact_grid* grid, const bf_param_tables* params,
                         int64_t star_begin, int64_t n_stars, const double* flux64, const double* pmax,
                         double threshold, const uint32_t* offsets, const uint32_t* list,
                         const uint32_t* entry_star, const int32_t* star_order,
                         int64_t entry_base, int64_t n_entries,
                         const double* percentiles_host, const bf_accum_scratch* scratch,
-                        const bf_star_outputs* out, void* stream);
+                        const bf_star_outputs* out, void* stream, void* aux_stream);
 
 /* Sparse lnP record (fit.py:693-709): for star s, entries [rec_off[s], rec_off[s+1]) of
  * `ranks` hold 0-based positions inside the star's ascending sparse set; outputs the filtered
