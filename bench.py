@@ -80,11 +80,13 @@ class ClockSampler(threading.Thread):
     def run(self):
         while self.ok and not self.stop_flag:
             try:
-                self.samples.append(self.nv.nvmlDeviceGetClockInfo(self.h, self.nv.NVML_CLOCK_SM))
+                mhz = self.nv.nvmlDeviceGetClockInfo(self.h, self.nv.NVML_CLOCK_SM)
                 bits = self.nv.nvmlDeviceGetCurrentClocksEventReasons(self.h)
-                for b, name in self.REASONS.items():
-                    if bits & b and name != "gpu_idle":
-                        self.reasons.add(name)
+                if getattr(self, "recording", True):
+                    self.samples.append(mhz)
+                    for b, name in self.REASONS.items():
+                        if bits & b and name != "gpu_idle":
+                            self.reasons.add(name)
             except Exception:
                 pass
             time.sleep(0.1)
@@ -188,7 +190,7 @@ def run_reference(args, rank, world):
 
 
 def workload_config(args, nm, stars):
-    return {"workload": CONFIGS[args.config][1], "config": args.config, "models": nm,
+    return {"workload": CONFIGS[args.config][2], "config": args.config, "models": nm,
             "bands": 8 if args.config == "C4" else 6, "stars_per_gpu": stars,
             "threshold": THRESHOLD, "max_nbins": args.max_nbins, "lnp_npts": LNP_NPTS,
             "outputs": "stats+pdf1d+sparse lnP", "parallelism": "stars sharded, grid replicated",
@@ -239,14 +241,16 @@ def run_ours(args, rank, world, local_rank):
                        reuse_buffers=True)
 
     # ---- device-resident throughput ------------------------------------------------
+    sampler = ClockSampler(local_rank)  # started before the warm-up: the first NVML queries stall
+    sampler.recording = False           # CUDA API calls for a while on some drivers
+    sampler.start()
     for _ in range(args.warmup):
         step_resident()
     barrier()
     eng.launches = 0
     eng.profile = True
     eng.stage_ms()
-    sampler = ClockSampler(local_rank)
-    sampler.start()
+    sampler.recording = True
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     barrier()
     ev0.record()
@@ -291,11 +295,18 @@ def run_ours(args, rank, world, local_rank):
     dense_ms = stage_tot.get("dense", 0.0) / max(stage_cnt.get("dense", 1), 1)
     evals_per_launch = stars * setup.ld_model / len(batches)
     achieved = flop_per_eval * evals_per_launch / (dense_ms * 1e-3) / 1e12 if dense_ms else None
+    # DRAM traffic of one dense launch: every block of 1024 stars streams the tiles once, plus the
+    # group-minimum map (validated against ncu dram__bytes: profiles/r01_dense_chi2_ncu.md)
+    stars_per_launch = stars / len(batches)
+    ld = -(-int(stars_per_launch) // 1024) * 1024
+    traffic = (ld // 1024) * setup.tiles.nbytes + setup.n_groups * ld * 4
     sm_max = float(peaks.get("sm_max_mhz", 1965.0))
     peak_tf = eng.sm_count * 128 * 2 * sm_max * 1e6 / 1e12
     roofline = {
         "bound": "fp32", "kernel": "dense_chi2_kernel", "achieved": achieved, "peak": peak_tf,
-        "unit": "TFLOP/s", "frac": (achieved / peak_tf) if achieved else None, "traffic": None,
+        "unit": "TFLOP/s", "frac": (achieved / peak_tf) if achieved else None, "traffic": int(traffic),
+        "traffic_note": "bytes per launch = star blocks x tile bytes + group-minimum map; equals ncu "
+                        "dram__bytes_read+write of the same kernel (profiles/r01_dense_chi2_ncu.md)",
         "peak_source": "%d SMs x 128 FP32 lanes x 2 x sm_max_mhz (%s); MEASURED_PEAKS.json has no "
                        "FP32 entry" % (eng.sm_count, peak_src),
         "dense_ms_per_launch": dense_ms, "flop_per_star_model": flop_per_eval,
