@@ -121,6 +121,7 @@ def build_inputs(cfg, stars, seed):
 
 # ---------------------------------------------------------------------------------------
 _CPU = {}
+_OUT = sys.stdout
 
 
 def _cpu_worker(args):
@@ -186,7 +187,8 @@ def run_reference(args, rank, world):
         "e2e": {"value": val, "unit": "star*model/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
-    print(json.dumps(line), flush=True)
+    _OUT.write(json.dumps(line) + "\n")
+    _OUT.flush()
 
 
 def workload_config(args, nm, stars):
@@ -337,12 +339,17 @@ def run_ours(args, rank, world, local_rank):
         "mean_sparse_set": float(np.mean(res.n_sparse)),
         "mean_groups_selected": float(np.mean(res.n_groups_selected)),
     }
-    print(json.dumps(line), flush=True)
+    _OUT.write(json.dumps(line) + "\n")
+    _OUT.flush()
     if dist is not None:
         dist.destroy_process_group()
 
 
 def main():
+    # keep stdout for the one JSON line: libraries (NCCL's version banner, ...) write there too
+    global _OUT
+    _OUT = os.fdopen(os.dup(1), "w")
+    os.dup2(2, 1)
     args = parse_args()
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
