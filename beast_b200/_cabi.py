@@ -37,6 +37,7 @@ class ExactGrid(C.Structure):
         ("ivar", c_void_p),
         ("lnq", c_void_p),
         ("lnw", c_void_p),
+        ("cov_off", c_void_p),
     ]
 
 
@@ -83,6 +84,8 @@ PROTOTYPES = {
     "bf_device_info": (C.c_int, [C.c_int, C.POINTER(C.c_int), C.POINTER(C.c_int), C.POINTER(C.c_int)]),
     "bf_dense_chi2": (C.c_int, [C.c_int, i64, c_void_p, i64, i64, c_void_p, c_void_p, c_void_p,
                                 C.c_int, c_void_p]),
+    "bf_dense_chi2_cov": (C.c_int, [C.c_int, i64, c_void_p, i64, i64, c_void_p, c_void_p, c_void_p,
+                                    C.c_int, c_void_p]),
     "bf_dense_tiles_per_item": (C.c_int, [i64, i64, C.c_int]),
     "bf_select_count": (C.c_int, [i64, i64, i64, c_void_p, c_void_p, C.c_float, C.c_float,
                                   C.c_float, c_void_p, c_void_p]),

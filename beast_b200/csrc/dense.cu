@@ -23,25 +23,31 @@
 namespace bf {
 
 constexpr int kDenseThreads = 128;
-constexpr int kDenseStages = 4;
-constexpr int kDensePrefetch = 2;  // tiles in flight ahead of the consumer
 constexpr int kNPair = BF_STAR_BLOCK / kDenseThreads / 2;  // star pairs per thread (4)
 
-template <int NB>
+// COV = full-covariance likelihood (N_covar_chi2, fit_metrics/likelihood.py:58-106): the tile
+// then carries, per model, -m'_b = -(sed+bias)/s_b, D_b = icov_diag_b s_b^2, the packed upper
+// triangle O_kl = 2 icov_offdiag_kl s_k s_l (k<l, row-major) and c2, and
+//   acc = sum_b t_b^2 D_b + sum_k t_k sum_{l>k} O_kl t_l + c2,   t_b = f_b/s_b - m'_b.
+template <int NB, bool COV>
 struct DenseSmem {
-  static constexpr int kRows = 2 * NB + 1;
+  static constexpr int kRows = COV ? 2 * NB + NB * (NB - 1) / 2 + 1 : 2 * NB + 1;
+  static constexpr int kStages = COV ? 3 : 4;
+  static constexpr int kPrefetch = COV ? 1 : 2;  // tiles in flight ahead of the consumer
   static constexpr uint32_t kTileBytes = kRows * BF_TILE_MODELS * sizeof(float);
-  static constexpr uint32_t kBytes = kDenseStages * kTileBytes + 2 * kDenseStages * sizeof(uint64_t);
+  static constexpr uint32_t kBytes = kStages * kTileBytes + 2 * kStages * sizeof(uint64_t);
 };
 
-template <int NB>
-__global__ void __launch_bounds__(kDenseThreads, 3)
+template <int NB, bool COV>
+__global__ void __launch_bounds__(kDenseThreads, COV ? 2 : 3)
 dense_chi2_kernel(const float* __restrict__ tiles, int64_t n_tiles, int tiles_per_item,
                   const float* __restrict__ flux, int64_t ld_star, float* __restrict__ gmin,
                   unsigned long long* __restrict__ starmin) {
   constexpr int TM = BF_TILE_MODELS;
-  constexpr int ROWS = 2 * NB + 1;
-  constexpr uint32_t TILE_BYTES = DenseSmem<NB>::kTileBytes;
+  constexpr int ROWS = DenseSmem<NB, COV>::kRows;
+  constexpr int kDenseStages = DenseSmem<NB, COV>::kStages;
+  constexpr int kDensePrefetch = DenseSmem<NB, COV>::kPrefetch;
+  constexpr uint32_t TILE_BYTES = DenseSmem<NB, COV>::kTileBytes;
   constexpr int GROUPS_PER_TILE = TM / BF_GROUP;
 
   extern __shared__ __align__(128) unsigned char smem_raw[];
@@ -116,31 +122,72 @@ dense_chi2_kernel(const float* __restrict__ tiles, int64_t n_tiles, int tiles_pe
     const float* sb = stage_buf + stage * (ROWS * TM);
 #pragma unroll 1
     for (int g = 0; g < GROUPS_PER_TILE; ++g) {
+      if constexpr (!COV) {
 #pragma unroll 2
-      for (int m = g * BF_GROUP; m < (g + 1) * BF_GROUP; m += 2) {
-        float2 r[NB], na[NB];
-#pragma unroll
-        for (int b = 0; b < NB; ++b) {
-          r[b] = *reinterpret_cast<const float2*>(sb + b * TM + m);
-          na[b] = *reinterpret_cast<const float2*>(sb + (NB + b) * TM + m);
-        }
-        const float2 c2 = *reinterpret_cast<const float2*>(sb + 2 * NB * TM + m);
-#pragma unroll
-        for (int p = 0; p < kNPair; ++p) {
-          f32x2 acc0 = pack2(c2.x, c2.x);
-          f32x2 acc1 = pack2(c2.y, c2.y);
+        for (int m = g * BF_GROUP; m < (g + 1) * BF_GROUP; m += 2) {
+          float2 r[NB], na[NB];
 #pragma unroll
           for (int b = 0; b < NB; ++b) {
-            const f32x2 t0 = fma2(f[p][b], pack2(r[b].x, r[b].x), pack2(na[b].x, na[b].x));
-            const f32x2 t1 = fma2(f[p][b], pack2(r[b].y, r[b].y), pack2(na[b].y, na[b].y));
-            acc0 = fma2(t0, t0, acc0);
-            acc1 = fma2(t1, t1, acc1);
+            r[b] = *reinterpret_cast<const float2*>(sb + b * TM + m);
+            na[b] = *reinterpret_cast<const float2*>(sb + (NB + b) * TM + m);
           }
-          float a0l, a0h, a1l, a1h;
-          unpack2(acc0, a0l, a0h);
-          unpack2(acc1, a1l, a1h);
-          rmin[2 * p] = min3(rmin[2 * p], a0l, a1l);
-          rmin[2 * p + 1] = min3(rmin[2 * p + 1], a0h, a1h);
+          const float2 c2 = *reinterpret_cast<const float2*>(sb + 2 * NB * TM + m);
+#pragma unroll
+          for (int p = 0; p < kNPair; ++p) {
+            f32x2 acc0 = pack2(c2.x, c2.x);
+            f32x2 acc1 = pack2(c2.y, c2.y);
+#pragma unroll
+            for (int b = 0; b < NB; ++b) {
+              const f32x2 t0 = fma2(f[p][b], pack2(r[b].x, r[b].x), pack2(na[b].x, na[b].x));
+              const f32x2 t1 = fma2(f[p][b], pack2(r[b].y, r[b].y), pack2(na[b].y, na[b].y));
+              acc0 = fma2(t0, t0, acc0);
+              acc1 = fma2(t1, t1, acc1);
+            }
+            float a0l, a0h, a1l, a1h;
+            unpack2(acc0, a0l, a0h);
+            unpack2(acc1, a1l, a1h);
+            rmin[2 * p] = min3(rmin[2 * p], a0l, a1l);
+            rmin[2 * p + 1] = min3(rmin[2 * p + 1], a0h, a1h);
+          }
+        }
+      } else {
+        constexpr int NP = NB * (NB - 1) / 2;
+        const f32x2 one = pack2(1.0f, 1.0f), zero = pack2(0.0f, 0.0f);
+#pragma unroll 1
+        for (int m = g * BF_GROUP; m < (g + 1) * BF_GROUP; ++m) {
+          float nm[NB], dg[NB], off[NP > 0 ? NP : 1];
+#pragma unroll
+          for (int b = 0; b < NB; ++b) {
+            nm[b] = sb[b * TM + m];
+            dg[b] = sb[(NB + b) * TM + m];
+          }
+#pragma unroll
+          for (int q = 0; q < NP; ++q) off[q] = sb[(2 * NB + q) * TM + m];
+          const float c2 = sb[(2 * NB + NP) * TM + m];
+#pragma unroll
+          for (int p = 0; p < kNPair; ++p) {
+            f32x2 t[NB];
+#pragma unroll
+            for (int b = 0; b < NB; ++b) t[b] = fma2(f[p][b], one, pack2(nm[b], nm[b]));
+            f32x2 acc = pack2(c2, c2);
+#pragma unroll
+            for (int b = 0; b < NB; ++b) {
+              const f32x2 u = fma2(t[b], pack2(dg[b], dg[b]), zero);
+              acc = fma2(u, t[b], acc);
+            }
+            int q = 0;
+#pragma unroll
+            for (int k = 0; k < NB - 1; ++k) {
+              f32x2 v = zero;
+#pragma unroll
+              for (int l = k + 1; l < NB; ++l, ++q) v = fma2(t[l], pack2(off[q], off[q]), v);
+              acc = fma2(v, t[k], acc);
+            }
+            float al, ah;
+            unpack2(acc, al, ah);
+            rmin[2 * p] = fminf(rmin[2 * p], al);
+            rmin[2 * p + 1] = fminf(rmin[2 * p + 1], ah);
+          }
         }
       }
       const int64_t gidx = (t_begin + i) * GROUPS_PER_TILE + g;
@@ -171,22 +218,22 @@ dense_chi2_kernel(const float* __restrict__ tiles, int64_t n_tiles, int tiles_pe
   }
 }
 
-template <int NB>
+template <int NB, bool COV>
 static int launch_dense(int64_t n_tiles, const float* tiles, int64_t ld_star, const float* flux,
                         float* gmin, unsigned long long* starmin, int tiles_per_item,
                         cudaStream_t st) {
-  auto kern = dense_chi2_kernel<NB>;
+  auto kern = dense_chi2_kernel<NB, COV>;
   static bool configured[64] = {};
   int dev = 0;
   BF_CUDA_TRY(cudaGetDevice(&dev));
   if (dev < 64 && !configured[dev]) {
     BF_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                     DenseSmem<NB>::kBytes));
+                                     DenseSmem<NB, COV>::kBytes));
     configured[dev] = true;
   }
   const int64_t n_items = (n_tiles + tiles_per_item - 1) / tiles_per_item;
   dim3 grid(static_cast<unsigned>(n_items), static_cast<unsigned>(ld_star / BF_STAR_BLOCK));
-  kern<<<grid, kDenseThreads, DenseSmem<NB>::kBytes, st>>>(
+  kern<<<grid, kDenseThreads, DenseSmem<NB, COV>::kBytes, st>>>(
       tiles, n_tiles, tiles_per_item, flux, ld_star, gmin, starmin);
   BF_CHECK_LAUNCH("dense_chi2_kernel");
   return BF_OK;
@@ -207,9 +254,9 @@ extern "C" int bf_dense_tiles_per_item(int64_t n_tiles, int64_t n_stars, int sm_
   return static_cast<int>(tpi);
 }
 
-extern "C" int bf_dense_chi2(int nb, int64_t n_tiles, const float* tiles, int64_t n_stars,
-                             int64_t ld_star, const float* flux, float* gmin, uint64_t* starmin,
-                             int tiles_per_item, void* stream) {
+static int dense_entry(bool cov, int nb, int64_t n_tiles, const float* tiles, int64_t n_stars,
+                       int64_t ld_star, const float* flux, float* gmin, uint64_t* starmin,
+                       int tiles_per_item, void* stream) {
   using namespace bf;
   BF_REQUIRE(nb >= 1 && nb <= BF_MAX_BANDS, "bf_dense_chi2: nb=%d out of range", nb);
   BF_REQUIRE(n_tiles > 0 && n_stars > 0, "bf_dense_chi2: empty problem");
@@ -219,16 +266,42 @@ extern "C" int bf_dense_chi2(int nb, int64_t n_tiles, const float* tiles, int64_
   BF_REQUIRE(tiles && flux && gmin && starmin, "bf_dense_chi2: null pointer");
   BF_REQUIRE(ld_star / BF_STAR_BLOCK <= 65535, "bf_dense_chi2: too many stars per call");
   cudaStream_t st = static_cast<cudaStream_t>(stream);
+  unsigned long long* sm = reinterpret_cast<unsigned long long*>(starmin);
+  if (!cov) {
+    switch (nb) {
+#define BF_CASE(N) \
+  case N:          \
+    return launch_dense<N, false>(n_tiles, tiles, ld_star, flux, gmin, sm, tiles_per_item, st);
+      BF_CASE(1) BF_CASE(2) BF_CASE(3) BF_CASE(4) BF_CASE(5) BF_CASE(6) BF_CASE(7) BF_CASE(8)
+      BF_CASE(9) BF_CASE(10) BF_CASE(11) BF_CASE(12)
+#undef BF_CASE
+      default:
+        set_error("bf_dense_chi2: nb=%d not instantiated (1..12)", nb);
+        return BF_ERR_UNSUPPORTED;
+    }
+  }
   switch (nb) {
 #define BF_CASE(N) \
   case N:          \
-    return launch_dense<N>(n_tiles, tiles, ld_star, flux, gmin,                               \
-                           reinterpret_cast<unsigned long long*>(starmin), tiles_per_item, st);
-    BF_CASE(1) BF_CASE(2) BF_CASE(3) BF_CASE(4) BF_CASE(5) BF_CASE(6) BF_CASE(7) BF_CASE(8)
-    BF_CASE(9) BF_CASE(10) BF_CASE(11) BF_CASE(12)
+    return launch_dense<N, true>(n_tiles, tiles, ld_star, flux, gmin, sm, tiles_per_item, st);
+    BF_CASE(2) BF_CASE(3) BF_CASE(4) BF_CASE(5) BF_CASE(6) BF_CASE(7) BF_CASE(8)
 #undef BF_CASE
     default:
-      set_error("bf_dense_chi2: nb=%d not instantiated (1..12)", nb);
+      set_error("bf_dense_chi2_cov: nb=%d not instantiated (2..8)", nb);
       return BF_ERR_UNSUPPORTED;
   }
+}
+
+extern "C" int bf_dense_chi2(int nb, int64_t n_tiles, const float* tiles, int64_t n_stars,
+                             int64_t ld_star, const float* flux, float* gmin, uint64_t* starmin,
+                             int tiles_per_item, void* stream) {
+  return dense_entry(false, nb, n_tiles, tiles, n_stars, ld_star, flux, gmin, starmin,
+                     tiles_per_item, stream);
+}
+
+extern "C" int bf_dense_chi2_cov(int nb, int64_t n_tiles, const float* tiles, int64_t n_stars,
+                                 int64_t ld_star, const float* flux, float* gmin,
+                                 uint64_t* starmin, int tiles_per_item, void* stream) {
+  return dense_entry(true, nb, n_tiles, tiles, n_stars, ld_star, flux, gmin, starmin,
+                     tiles_per_item, stream);
 }

@@ -11,10 +11,28 @@ constexpr int kWordsPerGroup = BF_GROUP / 32;
 __device__ __forceinline__ void exact_lnp(const bf_exact_grid& g, const double* sflux, int64_t j,
                                           double& lnp, double& chi2) {
   double acc = 0.0;
-  for (int b = 0; b < g.nb; ++b) {
-    const double d = __dsub_rn(sflux[b], g.msb[static_cast<int64_t>(b) * g.ld_model + j]);
-    const double dd = __dmul_rn(d, d);
-    acc = __dadd_rn(acc, __dmul_rn(dd, g.ivar[static_cast<int64_t>(b) * g.ld_model + j]));
+  if (g.cov_off == nullptr) {
+    for (int b = 0; b < g.nb; ++b) {
+      const double d = __dsub_rn(sflux[b], g.msb[static_cast<int64_t>(b) * g.ld_model + j]);
+      const double dd = __dmul_rn(d, d);
+      acc = __dadd_rn(acc, __dmul_rn(dd, g.ivar[static_cast<int64_t>(b) * g.ld_model + j]));
+    }
+  } else {
+    // N_covar_chi2 (likelihood.py:88-106): diagonal terms, then for each k the packed
+    // off-diagonal row dotted with the remaining residuals, times the k-th residual
+    double d[BF_MAX_BANDS];
+    for (int b = 0; b < g.nb; ++b) {
+      d[b] = __dsub_rn(sflux[b], g.msb[static_cast<int64_t>(b) * g.ld_model + j]);
+      acc = __dadd_rn(acc, __dmul_rn(__dmul_rn(d[b], d[b]),
+                                     g.ivar[static_cast<int64_t>(b) * g.ld_model + j]));
+    }
+    int m = 0;
+    for (int k = 0; k < g.nb - 1; ++k) {
+      double t = 0.0;
+      for (int l = k + 1; l < g.nb; ++l, ++m)
+        t = __dadd_rn(t, __dmul_rn(g.cov_off[static_cast<int64_t>(m) * g.ld_model + j], d[l]));
+      acc = __dadd_rn(acc, __dmul_rn(t, d[k]));
+    }
   }
   chi2 = acc;
   lnp = __dadd_rn(__dsub_rn(-g.lnq[j], __dmul_rn(0.5, acc)), g.lnw[j]);

@@ -105,6 +105,7 @@ class FitEngine:
             self.d_tiles_coarse = up(s.tiles_coarse)
             self.d_msb, self.d_ivar = up(s.msb), up(s.ivar)
             self.d_lnq, self.d_lnw = up(s.lnq), up(s.lnw)
+            self.d_cov_off = up(s.cov_off) if s.cov_off is not None else None
             self.d_bin_tab, self.d_q_tab = up(s.bin_tab), up(s.q_tab)
             self.d_bin_off, self.d_bin_val = up(s.bin_off), up(s.bin_val)
             self.d_q_lin = up(s.q_lin)
@@ -114,7 +115,8 @@ class FitEngine:
             else:
                 self.d_pair_bin = self.d_pair_off = None
         self.grid = ExactGrid(s.nb, s.n_models, s.ld_model, self.d_msb.data_ptr(),
-                              self.d_ivar.data_ptr(), self.d_lnq.data_ptr(), self.d_lnw.data_ptr())
+                              self.d_ivar.data_ptr(), self.d_lnq.data_ptr(), self.d_lnw.data_ptr(),
+                              self.d_cov_off.data_ptr() if self.d_cov_off is not None else None)
         self.params = ParamTables(s.n_q, s.total_bins, s.max_bins, self.d_bin_tab.data_ptr(),
                                   self.d_q_tab.data_ptr(), self.d_q_lin.data_ptr(),
                                   self.d_bin_off.data_ptr(),
@@ -187,7 +189,8 @@ class FitEngine:
         starmin = torch.full((ld,), 0x7F800000FFFFFFFF, dtype=torch.int64, device=self.device)
         tpi = self.lib.bf_dense_tiles_per_item(n_tiles, n, self.sm_count)
         with self._timed("presort" if coarse else "dense"):
-            _cabi.call("bf_dense_chi2", s.nb, n_tiles, _ptr(tiles), n, ld, _ptr(f32),
+            _cabi.call("bf_dense_chi2_cov" if s.full_cov else "bf_dense_chi2", s.nb, n_tiles,
+                       _ptr(tiles), n, ld, _ptr(f32),
                        _ptr(gmin), _ptr(starmin), tpi, self._stream())
         self.launches += 1
         return gmin, starmin, ld

@@ -11,8 +11,7 @@ Differences a user can observe, all documented in DESIGN.md:
   when ``lnp_rng="numpy"`` (default here); ``lnp_rng="device"`` is the fast variant;
 * ``save_every_npts`` checkpoints are written at batch boundaries (a batch is a multiple of
   ``save_every_npts`` stars), not after every ``save_every_npts``-th star;
-* full-covariance noise models raise ``NotImplementedError`` unless
-  ``use_full_cov_matrix=False``.
+* full-covariance noise models are supported for 2..8 bands.
 """
 
 from __future__ import annotations
@@ -267,7 +266,7 @@ def Q_all_memory(prev_result, obs, sedgrid, obsmodel, qnames_in, p=[16.0, 50.0, 
                          use_full_cov_matrix=use_full_cov_matrix)
         engine = FitEngine(setup, device=device)
     setup = engine.setup
-    print("not using full covariance matrix")
+    print("using full covariance matrix" if setup.full_cov else "not using full covariance matrix")
     # the reference appends to the caller's list; keep that observable behaviour
     for f in setup.filters:
         qnames_in.append("symlog" + f + "_wd_bias")

@@ -146,17 +146,21 @@ class FitSetup:
             lnw = lnw - np.log(weight[g0].sum())
         if len(weight) != len(g0):
             warnings.warn("some zero weight models exist")
-        if (use_full_cov_matrix and "q_norm" in obsmodel and "icov_diag" in obsmodel
-                and "icov_offdiag" in obsmodel):
-            raise NotImplementedError(
-                "full-covariance noise models (q_norm/icov_diag/icov_offdiag, fit.py:432-444) are "
-                "not on the CUDA path yet; pass use_full_cov_matrix=False to fit with the "
-                "diagonal noise model")
+        # the noise model carries full covariance matrices -> N_covar_logLikelihood (fit.py:432-444)
+        self.full_cov = bool(use_full_cov_matrix and "q_norm" in obsmodel
+                             and "icov_diag" in obsmodel and "icov_offdiag" in obsmodel)
+        if self.full_cov and not (2 <= nb <= 8):
+            raise NotImplementedError("the full-covariance kernels are built for 2..8 bands")
 
         seds = sedgrid.seds.read() if hasattr(sedgrid.seds, "read") else np.asarray(sedgrid.seds)
         err = np.asarray(obsmodel["error"], dtype=np.float64)
         msb_full = seds + np.asarray(obsmodel["bias"], dtype=np.float64)
-        ivar_full = 1.0 / err**2
+        if self.full_cov:
+            ivar_full = np.asarray(obsmodel["icov_diag"], dtype=np.float64)  # diagonal of C^-1
+            two_off_full = 2.0 * np.asarray(obsmodel["icov_offdiag"], dtype=np.float64)
+            q_norm = np.asarray(obsmodel["q_norm"], dtype=np.float64)
+        else:
+            ivar_full = 1.0 / err**2
         full_model_flux = symlog(msb_full)
 
         self.filters = filters
@@ -201,9 +205,16 @@ class FitSetup:
                         PairBins(params[i] + "+" + params[j], specs[params[i]], specs[params[j]]))
 
         # ---- drop models the kernels cannot rank (non-finite constants) -----------
-        lnq = nb * (0.5 * np.log(2.0 * np.pi)) - 0.5 * np.sum(np.log(ivar_full[g0]), axis=1)
+        if self.full_cov:
+            # lnP = (-0.5 nb ln 2pi + q_norm) - 0.5 chi2 (likelihood.py:206-216); stored negated so
+            # that the kernels use one expression for both likelihoods
+            lnq = -(-0.5 * nb * np.log(2.0 * np.pi) + q_norm[g0])
+        else:
+            lnq = nb * (0.5 * np.log(2.0 * np.pi)) - 0.5 * np.sum(np.log(ivar_full[g0]), axis=1)
         c = -lnq + lnw
         ok = np.isfinite(c) & np.isfinite(msb_full[g0]).all(axis=1) & np.isfinite(ivar_full[g0]).all(axis=1)
+        if self.full_cov:
+            ok &= np.isfinite(two_off_full[g0]).all(axis=1)
         if not ok.all():
             warnings.warn("%d models with non-finite noise model / flux values are ignored"
                           % int((~ok).sum()))
@@ -228,31 +239,51 @@ class FitSetup:
         self.lnw = np.zeros(nmp)
         self.lnw[:nm] = lnw
 
+        npair = nb * (nb - 1) // 2
+        if self.full_cov:
+            cov_off = np.zeros((max(npair, 1), nmp))
+            cov_off[:npair, :nm] = two_off_full[g0].T
+            self.cov_off = cov_off
+        else:
+            self.cov_off = None
+
         # ---- FP32 tiles of the dense pass ---------------------------------------
-        inv_sigma = 1.0 / np.abs(err[g0])  # (nm, nb); error may be stored negative
         scale = np.median(np.abs(msb_full[g0]), axis=0)
         scale = np.where((scale > 0) & np.isfinite(scale), scale, 1.0)
         self.band_scale = scale
-        a = msb_full[g0] * inv_sigma
         self.c_off = float(c.max())
-        rows = np.zeros((2 * nb + 1, nmp), dtype=np.float32)
-        rows[:nb, :nm] = (inv_sigma * scale[None, :]).T
-        rows[nb:2 * nb, :nm] = (-a).T
-        rows[2 * nb, :] = 3.0e38
-        rows[2 * nb, :nm] = -2.0 * (c - self.c_off)
+        if self.full_cov:
+            nrows = 2 * nb + npair + 1
+            rows = np.zeros((nrows, nmp), dtype=np.float32)
+            rows[:nb, :nm] = (-msb_full[g0] / scale[None, :]).T
+            rows[nb:2 * nb, :nm] = (ivar_full[g0] * scale[None, :] ** 2).T
+            iu = np.triu_indices(nb, k=1)
+            rows[2 * nb:2 * nb + npair, :nm] = (two_off_full[g0] * (scale[iu[0]] * scale[iu[1]])[None, :]).T
+            a = msb_full[g0] * np.sqrt(np.abs(ivar_full[g0]))
+        else:
+            nrows = 2 * nb + 1
+            inv_sigma = 1.0 / np.abs(err[g0])  # (nm, nb); error may be stored negative
+            a = msb_full[g0] * inv_sigma
+            rows = np.zeros((nrows, nmp), dtype=np.float32)
+            rows[:nb, :nm] = (inv_sigma * scale[None, :]).T
+            rows[nb:2 * nb, :nm] = (-a).T
+        rows[nrows - 1, :] = 3.0e38
+        rows[nrows - 1, :nm] = -2.0 * (c - self.c_off)
         self.tiles = np.ascontiguousarray(
-            rows.reshape(2 * nb + 1, self.n_tiles, TILE_MODELS).transpose(1, 0, 2))
+            rows.reshape(nrows, self.n_tiles, TILE_MODELS).transpose(1, 0, 2))
         # every COARSE_STRIDE-th model, for the cheap sweep that orders the stars of a batch
         sub = rows[:, :nm:COARSE_STRIDE]
         ncp = _pad_to(sub.shape[1], TILE_MODELS)
-        crow = np.zeros((2 * nb + 1, ncp), dtype=np.float32)
-        crow[2 * nb, :] = 3.0e38
+        crow = np.zeros((nrows, ncp), dtype=np.float32)
+        crow[nrows - 1, :] = 3.0e38
         crow[:, :sub.shape[1]] = sub
         self.tiles_coarse = np.ascontiguousarray(
-            crow.reshape(2 * nb + 1, ncp // TILE_MODELS, TILE_MODELS).transpose(1, 0, 2))
+            crow.reshape(nrows, ncp // TILE_MODELS, TILE_MODELS).transpose(1, 0, 2))
         a_max = float(np.abs(a).max())
-        self.err_a = float(ERR_SAFETY * 6.0 * FP32_U * math.sqrt(nb) * a_max)
-        self.err_b = float(ERR_SAFETY * 16.0 * FP32_U)
+        # cross terms: every residual meets up to nb-1 others, with |O_kl| <= sqrt(D_k D_l)
+        cov_factor = float(nb) if self.full_cov else 1.0
+        self.err_a = float(ERR_SAFETY * cov_factor * 6.0 * FP32_U * math.sqrt(nb) * a_max)
+        self.err_b = float(ERR_SAFETY * cov_factor * 16.0 * FP32_U)
 
         # ---- chunk-major parameter tables ---------------------------------------
         nch = nmp // CHUNK

@@ -36,6 +36,7 @@ __all__ = [
     "SyntheticObservations",
     "make_sedgrid",
     "make_noisemodel",
+    "make_noisemodel_fullcov",
     "make_observations",
     "make_config",
 ]
@@ -292,6 +293,30 @@ def make_noisemodel(sedgrid, snr_cap=100.0, depth_scale=1.0):
     compl1 = 1.0 / (1.0 + np.exp(-(snr - 5.0) / 0.8))
     completeness = np.repeat(np.clip(compl1, 1e-4, 1.0)[:, None], nb, axis=1)
     return {"error": error, "bias": bias, "completeness": completeness}
+
+
+def make_noisemodel_fullcov(sedgrid, snr_cap=100.0, depth_scale=1.0):
+    """Trunchen-like noise model: the toothpick sigma/bias/completeness plus a full covariance
+    per model, C = diag(sigma) R diag(sigma) with a band-to-band correlation that grows for
+    faint (crowding-limited) models.  Adds the three arrays that switch the fit to the
+    full-covariance likelihood (fit.py:432-444): ``q_norm`` = -1/2 ln det C,
+    ``icov_diag`` and ``icov_offdiag`` (upper triangle of C^-1 packed row-major, k < l), the
+    packing of ``observationmodel/noisemodel/trunchen.py:388-421``."""
+    nz = make_noisemodel(sedgrid, snr_cap=snr_cap, depth_scale=depth_scale)
+    sig = nz["error"]
+    nm, nb = sig.shape
+    snr = (sedgrid.seds / sig).max(axis=1)
+    rho = 0.15 + 0.35 / (1.0 + np.exp((snr - 8.0) / 3.0))  # (nm,)
+    lag = np.abs(np.arange(nb)[:, None] - np.arange(nb)[None, :])
+    R = rho[:, None, None] ** lag[None, :, :]
+    C = sig[:, :, None] * R * sig[:, None, :]
+    iC = np.linalg.inv(C)
+    _, logdet = np.linalg.slogdet(C)
+    iu = np.triu_indices(nb, k=1)
+    nz["q_norm"] = -0.5 * logdet
+    nz["icov_diag"] = np.ascontiguousarray(np.diagonal(iC, axis1=1, axis2=2))
+    nz["icov_offdiag"] = np.ascontiguousarray(iC[:, iu[0], iu[1]])
+    return nz
 
 
 def make_observations(sedgrid, noisemodel, nstars, seed=4321, with_coords=True):

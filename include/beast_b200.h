@@ -72,6 +72,16 @@ int bf_dense_chi2(int nb, int64_t n_tiles, const float* tiles, int64_t n_stars,
                   int64_t ld_star, const float* flux, float* gmin, uint64_t* starmin,
                   int tiles_per_item, void* stream);
 
+/* Same sweep for the full-covariance likelihood (N_covar_logLikelihood / N_covar_chi2,
+ * fitting/fit_metrics/likelihood.py:58-106, 170-218; selected at fit.py:432-444).
+ * tiles : [n_tiles][2*nb + nb(nb-1)/2 + 1][BF_TILE_MODELS] float.  Rows: -m'_b = -(sed_b+bias_b)/s_b,
+ *         D_b = icov_diag_b*s_b^2, O_kl = 2*icov_offdiag_kl*s_k*s_l (k<l packed row-major, the order
+ *         of observationmodel/noisemodel/trunchen.py:394-400), c2 = -2*(c - c_off) with
+ *         c = -nb/2 ln 2pi + q_norm + ln w.  Everything else as bf_dense_chi2.  nb = 2..8. */
+int bf_dense_chi2_cov(int nb, int64_t n_tiles, const float* tiles, int64_t n_stars,
+                      int64_t ld_star, const float* flux, float* gmin, uint64_t* starmin,
+                      int tiles_per_item, void* stream);
+
 /* Suggested tiles_per_item for a device with `sm_count` SMs. */
 int bf_dense_tiles_per_item(int64_t n_tiles, int64_t n_stars, int sm_count);
 
@@ -138,6 +148,11 @@ typedef struct {
   const double* ivar;
   const double* lnq;
   const double* lnw;
+  /* full covariance (optional, NULL = diagonal noise model): [nb(nb-1)/2][ld_model]
+   * 2*icov_offdiag packed k<l row-major; then `ivar` holds icov_diag and `lnq` holds
+   * nb/2 ln 2pi - q_norm, so that lnP = (-lnq - 0.5*chi2) + lnw in both cases
+   * (likelihood.py:212-216). */
+  const double* cov_off;
 } bf_exact_grid;
 
 /* Exact per-star maximum of lnP and its first index (fit.py:670, 684, 719, 727):

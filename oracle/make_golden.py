@@ -36,6 +36,8 @@ CASES = {
     "tiny_thr40_nonorm": ("tiny", 12, 12, dict(threshold=-40.0, max_nbins=200,
                                                do_not_normalize=True), 0),
     "small_thr10": ("small", 24, 13, dict(threshold=-10.0, max_nbins=50), 5),
+    # full-covariance (trunchen-like) noise model: N_covar_logLikelihood path, fit.py:432-444
+    "tiny_fullcov": ("tiny", 12, 14, dict(threshold=-10.0, max_nbins=40), 6),
 }
 
 
@@ -64,7 +66,7 @@ def make_case(name):
     g = synth.make_sedgrid(axes, seed=seed)
     if zstride:
         g["weight"][::zstride] = 0.0
-    nz = synth.make_noisemodel(g)
+    nz = synth.make_noisemodel_fullcov(g) if "fullcov" in name else synth.make_noisemodel(g)
     obs = synth.make_observations(g, nz, nstars, seed=seed + 100)
     keys = fit_oracle.default_keys(g)
     ref = ref_shim.run_reference_fit(obs, g, nz, keys, **kw)

@@ -162,15 +162,19 @@ def reference_sparse_set(flux, sedgrid, obsmodel, threshold=-10.0, do_not_normal
     Returns (full-grid indices int64, lnp float64, chi2 float64).
     """
     load_reference_fit()
-    from beast.fitting.fit_metrics.likelihood import N_logLikelihood_NM
+    from beast.fitting.fit_metrics.likelihood import N_covar_logLikelihood, N_logLikelihood_NM
 
     (g0_indxs,) = np.where(sedgrid["weight"] > 0.0)
     g0_weights = np.log(sedgrid["weight"][g0_indxs])
     if not do_not_normalize:
         g0_weights = g0_weights - np.log(sedgrid["weight"][g0_indxs].sum())
-    ivar = 1.0 / np.asfortranarray(obsmodel["error"]) ** 2
     mod = np.asfortranarray(sedgrid.seds + obsmodel["bias"])
-    lnp, chi2 = N_logLikelihood_NM(flux, mod, ivar, mask=np.zeros(len(flux), dtype=bool))
+    if "q_norm" in obsmodel and "icov_diag" in obsmodel and "icov_offdiag" in obsmodel:
+        lnp, chi2 = N_covar_logLikelihood(flux, mod, obsmodel["q_norm"], obsmodel["icov_diag"],
+                                          2.0 * obsmodel["icov_offdiag"])  # fit.py:440-442, 648-655
+    else:
+        ivar = 1.0 / np.asfortranarray(obsmodel["error"]) ** 2
+        lnp, chi2 = N_logLikelihood_NM(flux, mod, ivar, mask=np.zeros(len(flux), dtype=bool))
     lnp = lnp[g0_indxs] + g0_weights
     chi2 = chi2[g0_indxs]
     (indx,) = np.where((lnp - max(lnp[np.isfinite(lnp)])) > threshold)

@@ -100,3 +100,29 @@ def test_high_signal_to_noise_selection_margin():
     setup, res = _fit(g, nz, obs.fluxes, keys, -10.0, 50, sparse="all")
     util.compare_to_reference(setup, res, want)
     np.testing.assert_array_equal(res.n_sparse, [len(s[0]) for s in want["sparse"]])
+
+
+@pytest.mark.parametrize("bands", [6, 8])
+def test_full_covariance_against_oracle(bands):
+    """trunchen-like noise model: N_covar_logLikelihood path (fit.py:432-444, likelihood.py:58-106)"""
+    from beast_b200 import synth
+    from oracle import fit_oracle as fo
+
+    if bands == 8:
+        g = synth.make_sedgrid((5, 9, 2, 6, 3, 2, 1), synth.UVNIR_FILTERS, synth.UVNIR_LAMB, seed=91)
+    else:
+        g = synth.make_sedgrid("small", seed=91)
+    nz = synth.make_noisemodel_fullcov(g)
+    obs = synth.make_observations(g, nz, 33, seed=92)
+    keys = ["Av", "Rv", "M_ini", "logA", "logT", "logL"]
+    ost = fo.OracleSetup(g, nz, keys, max_nbins=60)
+    assert ost.full_cov
+    want = fo.fit_all(obs.fluxes, ost, -10.0, fast=True)
+    setup, res = _fit(g, nz, obs.fluxes, keys, -10.0, 60, sparse="all")
+    assert setup.full_cov
+    util.compare_to_reference(setup, res, want)
+    off = np.zeros(len(obs) + 1, dtype=np.int64)
+    off[1:] = np.cumsum([len(s[0]) for s in want["sparse"]])
+    util.compare_sparse(setup, res, off, np.concatenate([s[0] for s in want["sparse"]]),
+                        np.concatenate([s[1] for s in want["sparse"]]),
+                        np.concatenate([s[2] for s in want["sparse"]]))

@@ -85,9 +85,8 @@ def test_error_conventions(small):
     cov["q_norm"] = np.zeros(len(g))
     cov["icov_diag"] = nz["error"] ** -2
     cov["icov_offdiag"] = np.zeros((len(g), 15))
-    with pytest.raises(NotImplementedError, match="full-covariance"):
-        FitSetup(g, cov, ["Av"])
-    FitSetup(g, cov, ["Av"], use_full_cov_matrix=False)
+    assert FitSetup(g, cov, ["Av"]).full_cov  # fit.py:432-444: switches on the three arrays
+    assert not FitSetup(g, cov, ["Av"], use_full_cov_matrix=False).full_cov
 
 
 def test_fits_round_trip(tmp_path):

@@ -5,7 +5,7 @@ import numpy as np
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 GOLDEN = os.path.join(ROOT, "tests", "golden")
-GOLDEN_CASES = ["tiny_thr10_pdf2d", "tiny_thr40_nonorm", "small_thr10"]
+GOLDEN_CASES = ["tiny_thr10_pdf2d", "tiny_thr40_nonorm", "small_thr10", "tiny_fullcov"]
 
 # parity tolerances (BASELINE.json north_star; reference regression test helpers.py:33-112)
 LNP_ATOL = 1e-4       # lnP-like quantities: Pmax, total_log_norm, sparse lnp
