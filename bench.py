@@ -316,6 +316,38 @@ def run_ours(args, rank, world, local_rank):
         "stage_ms_per_step": {k: v / args.steps for k, v in stage_tot.items()},
     }
 
+    # ---- the step before the fit: trim_models flags pass, HBM-bound (fitting/trim_grid.py) -----
+    trim_info = None
+    try:
+        import ctypes as C
+
+        from beast_b200 import _cabi
+
+        up = lambda a: torch.from_numpy(np.ascontiguousarray(a, dtype=np.float64)).to(dev)  # noqa: E731
+        t_seds, t_bias, t_unc, t_cmp = up(g.seds), up(nz["bias"]), up(nz["error"]), up(nz["completeness"])
+        lo, hi = up(fluxes.min(axis=0)), up(fluxes.max(axis=0))
+        pat = torch.empty(len(g), dtype=torch.int32, device=dev)
+        hist = torch.zeros(1 << (setup.nb + 1), dtype=torch.int32, device=dev)
+        P = lambda t: C.c_void_p(t.data_ptr())  # noqa: E731
+        st = C.c_void_p(torch.cuda.current_stream(dev).cuda_stream)
+        ta, tb = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        ms = []
+        for it in range(5):
+            ta.record()
+            _cabi.call("bf_trim_flags", setup.nb, len(g), P(t_seds), P(t_bias), P(t_unc), P(t_cmp), 3.0,
+                       P(lo), P(hi), P(pat), P(hist), st)
+            tb.record()
+            torch.cuda.synchronize(dev)
+            ms.append(ta.elapsed_time(tb))
+        nbytes = 4 * t_seds.numel() * 8 + 4 * len(g)
+        best = min(ms[1:])
+        trim_info = {"kernel": "trim_flags_kernel", "models": len(g), "ms": best,
+                     "achieved_gbs": nbytes / best / 1e6, "peak_gbs": peaks.get("hbm_gbs"),
+                     "frac": nbytes / best / 1e6 / float(peaks.get("hbm_gbs", 6650.0)), "bound": "hbm"}
+        del t_seds, t_bias, t_unc, t_cmp
+    except Exception as exc:  # the fit numbers above stand on their own
+        trim_info = {"error": repr(exc)}
+
     cpu = None
     if world == 1 and not args.no_cpu_baseline:
         rates, cores, sample = cpu_reference_run(g, nz, obs, args.max_nbins, args.cpu_stars_per_core, 1, 1)
@@ -335,6 +367,7 @@ def run_ours(args, rank, world, local_rank):
         "gpu_launches": int(launches),
         "roofline": roofline,
         "cpu_baseline": cpu,
+        "trim": trim_info,
         "setup_seconds": setup_s,
         "mean_sparse_set": float(np.mean(res.n_sparse)),
         "mean_groups_selected": float(np.mean(res.n_groups_selected)),

@@ -274,6 +274,29 @@ int bf_scale_rows(int64_t n_stars, int64_t row_len, const double* weight, double
 int bf_merge_finalize(const bf_param_tables* params, int64_t n_stars, double* pdf1d,
                       const double* percentiles_host, double* per_vals, void* stream);
 
+/* ---------------------------------------------------------------------------
+ * Grid trimming, the step before the fit (fitting/trim_grid.py:53-118).
+ * Inputs are the reference's own arrays, [n_models][nb] row-major doubles.
+ * bf_trim_flags : pattern[m] bit b = model m survives band b's test
+ *                   sed+bias + sigma_fac*error >= min_data[b]  and  sed+bias - sigma_fac*error <= max_data[b]
+ *                 (:98-109), bit 31 = completeness > 0 in every band (:84-88);
+ *                 hist[(pattern & 0xffff) | complete << nb] += 1, hist has 2^(nb+1) zeroed entries.
+ *                 min_data / max_data are DEVICE arrays of nb doubles.
+ * The caller resolves the reference's "skip a band that would leave nothing" rule (:110-111)
+ * from the histogram, then
+ * bf_trim_select : keep[m] = (pattern[m] & required) == required
+ * bf_trim_compact: indices[offsets[m]] = m for kept models (offsets = exclusive scan of keep),
+ *                  i.e. the reference's ascending `indxs`.
+ * ------------------------------------------------------------------------- */
+int bf_trim_flags(int nb, int64_t n_models, const double* seds, const double* bias,
+                  const double* unc, const double* completeness, double sigma_fac,
+                  const double* min_data, const double* max_data, uint32_t* pattern,
+                  uint32_t* hist, void* stream);
+int bf_trim_select(int64_t n_models, const uint32_t* pattern, uint32_t required, uint32_t* keep,
+                   void* stream);
+int bf_trim_compact(int64_t n_models, const uint32_t* keep, const uint32_t* offsets,
+                    int64_t* indices, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

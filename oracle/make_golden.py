@@ -105,6 +105,27 @@ def make_case(name):
     print("wrote", path, "%.0f kB" % (os.path.getsize(path) / 1e3))
 
 
+def make_trim_case(name="trim_tiny"):
+    """inputs + the index list the reference's trim_models keeps (trim_grid.py:53-125)"""
+    g = synth.make_sedgrid("tiny", seed=21)
+    nz = synth.make_noisemodel(g)
+    nz["completeness"][::13, 1] = 0.0
+    obs = synth.make_observations(g, nz, 30, seed=22)
+    bright = np.argsort(obs.fluxes[:, 3])[12:]
+    obs = synth.SyntheticObservations(obs.fluxes[bright], g.filters)
+    cap = ref_shim.run_reference_trim(g, nz, obs)
+    path = os.path.join(GOLDEN_DIR, name + ".npz")
+    np.savez_compressed(path, seds=g.seds, bias=nz["bias"], error=nz["error"],
+                        completeness=nz["completeness"], obs_flux=obs.fluxes,
+                        filters=np.array(g.filters), ref_indxs=cap["cols"]["fullgrid_idx"],
+                        ref_seds=cap["seds"], ref_error=cap["noise_error"])
+    print("wrote", path, "%.0f kB" % (os.path.getsize(path) / 1e3), len(cap["cols"]["fullgrid_idx"]), "of", len(g))
+
+
 if __name__ == "__main__":
-    for n in sys.argv[1:] or CASES:
-        make_case(n)
+    names = sys.argv[1:] or list(CASES) + ["trim_tiny"]
+    for n in names:
+        if n.startswith("trim"):
+            make_trim_case(n)
+        else:
+            make_case(n)

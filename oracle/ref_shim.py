@@ -179,3 +179,47 @@ def reference_sparse_set(flux, sedgrid, obsmodel, threshold=-10.0, do_not_normal
     chi2 = chi2[g0_indxs]
     (indx,) = np.where((lnp - max(lnp[np.isfinite(lnp)])) > threshold)
     return g0_indxs[indx].astype(np.int64), lnp[indx], chi2[indx]
+
+
+def run_reference_trim(sedgrid, noisemodel, obsdata, sigma_fac=3.0, trunchen=False):
+    """Execute the reference ``trim_models`` (fitting/trim_grid.py:10) with its grid / file
+    writers replaced by captures; returns the ``fullgrid_idx`` column it would have written."""
+    load_reference_fit()
+    captured = {}
+
+    class _Grid:  # stands in for SEDGrid(lamb, seds=..., grid=..., backend="memory")
+        def __init__(self, lamb, seds=None, grid=None, backend=None):
+            captured["seds"] = np.array(seds)
+            captured["cols"] = dict(grid)
+            self.header = {}
+
+        def write(self, name):
+            captured["sed_outname"] = name
+
+    class _File:
+        def __init__(self):
+            self.root = None
+
+        def create_array(self, root, name, arr):
+            captured["noise_" + name] = np.array(arr)
+
+        def __enter__(self):
+            return self
+
+        def __exit__(self, *a):
+            return False
+
+    sys.modules["tables"].open_file = lambda *a, **k: _File()
+    sys.modules["beast.physicsmodel.grid"].SEDGrid = _Grid
+    sys.modules.pop("beast.fitting.trim_grid", None)
+    from beast.fitting import trim_grid
+
+    class _G:  # the reference reads sedgrid.seds, .lamb and .grid (a table of columns)
+        seds = sedgrid.seds
+        lamb = sedgrid.lamb
+        grid = {k: sedgrid[k] for k in sedgrid.keys()}
+
+    with contextlib.redirect_stdout(io.StringIO()):
+        trim_grid.trim_models(_G, noisemodel, obsdata, "sed_out", "noise_out", sigma_fac=sigma_fac,
+                              trunchen=trunchen)
+    return captured
