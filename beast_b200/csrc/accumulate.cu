@@ -23,6 +23,8 @@ namespace bf {
 
 constexpr int kMaxRounds = BF_MAX_PARAMS / 32;
 constexpr int kWeightWarps = 8;
+constexpr int kStageDoubles = BF_GROUP;  // per-warp staging: the current group's weights
+constexpr int kSideBlocksPerSm = 64;  // grid cap of the grid-stride kernels, in blocks per SM
 
 __global__ void __launch_bounds__(kWeightWarps * 32)
 exact_weights_kernel(bf_exact_grid grid, int64_t n_stars, const double* __restrict__ flux64,
@@ -31,8 +33,9 @@ exact_weights_kernel(bf_exact_grid grid, int64_t n_stars, const double* __restri
                      int64_t entry_base, int64_t n_entries, bf_accum_scratch sc,
                      uint32_t* __restrict__ member_mask, uint32_t* __restrict__ member_prefix) {
   const int lane = threadIdx.x & 31;
-  const int64_t slot = static_cast<int64_t>(blockIdx.x) * kWeightWarps + (threadIdx.x >> 5);
-  if (slot >= n_entries) return;
+  // grid-stride over the groups
+  for (int64_t slot = static_cast<int64_t>(blockIdx.x) * kWeightWarps + (threadIdx.x >> 5);
+       slot < n_entries; slot += static_cast<int64_t>(gridDim.x) * kWeightWarps) {
   const uint32_t e = static_cast<uint32_t>(entry_base + slot);
   const int64_t s = entry_star[e];
   const double* sflux = flux64 + s * grid.nb;
@@ -82,6 +85,7 @@ exact_weights_kernel(bf_exact_grid grid, int64_t n_stars, const double* __restri
     sc.part_chi2_j[slot] = chij;
     member_prefix[e] = cnt;  // turned into an exclusive prefix by hist_kernel
   }
+  }
 }
 
 
@@ -95,7 +99,7 @@ struct HistSmem {
     size_t h = static_cast<size_t>(nw) * rounds * max_bins * 32;
     const size_t c = static_cast<size_t>(nw) * kMaxBinsPerParam;
     if (h < c) h = c;
-    return (h + static_cast<size_t>(nw) * BF_GROUP + 3 * static_cast<size_t>(nw) + 8) * sizeof(double);
+    return (h + static_cast<size_t>(nw) * kStageDoubles + 3 * static_cast<size_t>(nw) + 8) * sizeof(double);
   }
 };
 
@@ -109,14 +113,16 @@ constexpr int kExpWarps = 8;
 __global__ void __launch_bounds__(kExpWarps * 32)
 exp_kernel(bf_param_tables prm, int rounds, const uint32_t* __restrict__ offsets,
            const uint32_t* __restrict__ list, const uint32_t* __restrict__ member_mask,
-           int64_t star_begin, int64_t entry_base, const double* __restrict__ weights,
-           const double* __restrict__ part_wsum, double* __restrict__ exp_vals) {
+           int64_t star_begin, int64_t n_stars, int64_t entry_base,
+           const double* __restrict__ weights, const double* __restrict__ part_wsum,
+           double* __restrict__ exp_vals) {
   extern __shared__ __align__(16) double exp_smem[];  // [kExpWarps][nq] + [kExpWarps]
   double* red = exp_smem;
   double* wred = exp_smem + kExpWarps * prm.n_q;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int nq = prm.n_q;
-  const int64_t s = star_begin + blockIdx.x;
+  for (int64_t sb = blockIdx.x; sb < n_stars; sb += gridDim.x) {
+  const int64_t s = star_begin + sb;
   const uint32_t e0 = offsets[s * BF_SELECT_SPLIT];
   const uint32_t e1 = offsets[(s + 1) * BF_SELECT_SPLIT];
   for (int r = 0; r < rounds; ++r) {
@@ -171,6 +177,8 @@ exp_kernel(bf_param_tables prm, int rounds, const uint32_t* __restrict__ offsets
     exp_vals[s * nq + k] = wtot > 0.0 ? prm.q_lin[2 * k] + prm.q_lin[2 * k + 1] * (e / wtot)
                                       : __longlong_as_double(0x7ff8000000000000LL);
   }
+  __syncthreads();  // red / wred are reused by the next star
+  }
 }
 
 // ---------------------------------------------------------------------------------------
@@ -219,7 +227,7 @@ hist_kernel(bf_param_tables prm, int rounds, const double* __restrict__ pmax,
 
   double* hist = smem_d;
   double* wbuf_all = hist + harea;
-  double* red = wbuf_all + nw * BF_GROUP;
+  double* red = wbuf_all + nw * kStageDoubles;
   long long* redj = reinterpret_cast<long long*>(red + 2 * nw);
   uint32_t* sscan = reinterpret_cast<uint32_t*>(redj + nw);
 
@@ -232,7 +240,7 @@ hist_kernel(bf_param_tables prm, int rounds, const double* __restrict__ pmax,
   const uint32_t e0 = offsets[s * BF_SELECT_SPLIT];
   const uint32_t e1 = offsets[(s + 1) * BF_SELECT_SPLIT];
   double* myhist = hist + warp * hist_per_warp + lane;
-  double* wbuf = wbuf_all + warp * BF_GROUP;
+  double* wbuf = wbuf_all + warp * kStageDoubles;
 
   for (int r = 0; r < rounds; ++r) {
     const int k = r * 32 + lane;
@@ -242,7 +250,10 @@ hist_kernel(bf_param_tables prm, int rounds, const double* __restrict__ pmax,
     uint32_t e = e0 + warp;
     EntryRows cur, nxt;
     // three-deep software pipeline: list entry (group id + membership words) two groups
-    // ahead, bin rows + weights one group ahead, accumulation on the current group
+    // ahead, bin rows + weights one group ahead, accumulation on the current group.
+    // (Deeper register-ring prefetching and a forwarding read-modify-write pipeline were
+    // measured: no gain at 200 bins, a loss at 50 bins where the extra registers cost a
+    // resident block -- the kernel is bound by single-warp issue, see DESIGN.md.)
     uint32_t g1 = 0, a1 = 0, b1 = 0, g2 = 0, a2 = 0, b2 = 0;
     if (e < e1) {
       g1 = list[e];
@@ -388,7 +399,8 @@ hist_kernel(bf_param_tables prm, int rounds, const double* __restrict__ pmax,
 
 }  // namespace bf
 
-extern "C" int bf_exact_accumulate(const bf_exact_grid* grid, const bf_param_tables* params,
+// phases: 1 = exact weights + expectations, 2 = histograms / percentiles, 3 = both
+static int accumulate_impl(int phases, const bf_exact_grid* grid, const bf_param_tables* params,
                                    int64_t star_begin, int64_t n_stars, const double* flux64,
                                    const double* pmax, double threshold, const uint32_t* offsets,
                                    const uint32_t* list,
@@ -426,6 +438,7 @@ extern "C" int bf_exact_accumulate(const bf_exact_grid* grid, const bf_param_tab
   int dev = 0;
   BF_CUDA_TRY(cudaGetDevice(&dev));
   static int smem_limit[64] = {};
+  static int sm_count[64] = {};
   if (dev >= 64) {
     set_error("bf_exact_accumulate: device ordinal %d not supported", dev);
     return BF_ERR_UNSUPPORTED;
@@ -439,12 +452,14 @@ extern "C" int bf_exact_accumulate(const bf_exact_grid* grid, const bf_param_tab
                                      cudaSharedmemCarveoutMaxShared));
     BF_CUDA_TRY(cudaFuncSetAttribute(hist_kernel, cudaFuncAttributePreferredSharedMemoryCarveout,
                                      cudaSharedmemCarveoutMaxShared));
+    BF_CUDA_TRY(cudaDeviceGetAttribute(&sm_count[dev], cudaDevAttrMultiProcessorCount, dev));
     smem_limit[dev] = optin;
   }
-  if (n_entries > 0) {
+  if ((phases & 1) && n_entries > 0) {
     const int64_t blocks = (n_entries + kWeightWarps - 1) / kWeightWarps;
     BF_REQUIRE(blocks < (1LL << 31), "bf_exact_accumulate: too many list entries in one call");
-    exact_weights_kernel<<<static_cast<unsigned>(blocks), kWeightWarps * 32, 0, st>>>(
+    const int64_t cap = static_cast<int64_t>(sm_count[dev]) * kSideBlocksPerSm;
+    exact_weights_kernel<<<static_cast<unsigned>(blocks < cap ? blocks : cap), kWeightWarps * 32, 0, st>>>(
         *grid, n_stars, flux64, pmax, threshold, list, entry_star, entry_base, n_entries, *scratch,
         out->member_mask, out->member_prefix);
     BF_CHECK_LAUNCH("exact_weights_kernel");
@@ -471,22 +486,26 @@ extern "C" int bf_exact_accumulate(const bf_exact_grid* grid, const bf_param_tab
               params->max_bins, params->n_q, smem, budget);
     return BF_ERR_TOO_LARGE;
   }
-  hist_kernel<<<static_cast<unsigned>(n_stars), nw * 32, smem, st>>>(
-      *params, rounds, pmax, offsets, list, star_order, star_begin, entry_base, *scratch,
-      percentiles_host[0],
-      percentiles_host[1], percentiles_host[2], *out);
-  BF_CHECK_LAUNCH("hist_kernel");
+  if (phases & 2) {
+    hist_kernel<<<static_cast<unsigned>(n_stars), nw * 32, smem, st>>>(
+        *params, rounds, pmax, offsets, list, star_order, star_begin, entry_base, *scratch,
+        percentiles_host[0], percentiles_host[1], percentiles_host[2], *out);
+    BF_CHECK_LAUNCH("hist_kernel");
+  }
   if (timing) cudaEventRecord(tev[2], st);
   // The expectation kernel is bound by L2 bandwidth and the histogram kernel by shared-memory
   // latency, and together they fit on an SM; with an auxiliary stream they run side by side
   // (the histogram blocks are launched first so that they claim their shared memory).
   if (aux_stream) BF_CUDA_TRY(cudaStreamWaitEvent(sx, ev_weights[dev], 0));
   if (timing) cudaEventRecord(tev[3], sx);
-  exp_kernel<<<static_cast<unsigned>(n_stars), kExpWarps * 32,
-               (kExpWarps * params->n_q + kExpWarps) * sizeof(double), sx>>>(
-      *params, rounds, offsets, list, out->member_mask, star_begin, entry_base, scratch->weights,
-      scratch->part_wsum, out->exp_vals);
-  BF_CHECK_LAUNCH("exp_kernel");
+  if (phases & 1) {
+    const int64_t cap = static_cast<int64_t>(sm_count[dev]) * kSideBlocksPerSm;
+    exp_kernel<<<static_cast<unsigned>(n_stars < cap ? n_stars : cap), kExpWarps * 32,
+                 (kExpWarps * params->n_q + kExpWarps) * sizeof(double), sx>>>(
+        *params, rounds, offsets, list, out->member_mask, star_begin, n_stars, entry_base,
+        scratch->weights, scratch->part_wsum, out->exp_vals);
+    BF_CHECK_LAUNCH("exp_kernel");
+  }
   if (aux_stream) BF_CUDA_TRY(cudaEventRecord(ev_exp[dev], sx));
   if (aux_stream) BF_CUDA_TRY(cudaStreamWaitEvent(st, ev_exp[dev], 0));
   if (timing) {
@@ -504,4 +523,16 @@ extern "C" int bf_exact_accumulate(const bf_exact_grid* grid, const bf_param_tab
     for (auto& e : tev) cudaEventDestroy(e);
   }
   return BF_OK;
+}
+
+extern "C" int bf_exact_accumulate(const bf_exact_grid* grid, const bf_param_tables* params,
+                                   int64_t star_begin, int64_t n_stars, const double* flux64,
+                                   const double* pmax, double threshold, const uint32_t* offsets,
+                                   const uint32_t* list, const uint32_t* entry_star,
+                                   const int32_t* star_order, int64_t entry_base, int64_t n_entries,
+                                   const double* percentiles_host, const bf_accum_scratch* scratch,
+                                   const bf_star_outputs* out, void* stream, void* aux_stream) {
+  return accumulate_impl(3, grid, params, star_begin, n_stars, flux64, pmax, threshold, offsets, list,
+                         entry_star, star_order, entry_base, n_entries, percentiles_host, scratch,
+                         out, stream, aux_stream);
 }

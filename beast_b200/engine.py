@@ -334,6 +334,9 @@ class FitEngine:
                                o["chi2min_j"].data_ptr(), o["n_sparse"].data_ptr(),
                                o["exp_vals"].data_ptr(), o["pdf1d"].data_ptr(),
                                o["per_vals"].data_ptr(), mask.data_ptr(), prefix.data_ptr())
+            # (running the weights kernel of the next range beside the histogram kernel of this one
+            # was measured and is slower: the latency-bound histogram kernel stalls once the
+            # memory-bound kernels saturate L2 -- see DESIGN.md)
             for a0, b0 in cuts:
                 base, cnt = int(off_host[a0]), int(off_host[b0] - off_host[a0])
                 with self._timed("accumulate"):

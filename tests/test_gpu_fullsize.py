@@ -1,0 +1,89 @@
+"""BASELINE.json sizes (C2: 4,000,000 models x 6 bands) on the GPU: size-independent
+properties on 1536 stars plus a direct oracle comparison on a handful of them."""
+import warnings
+
+import numpy as np
+import pytest
+
+from tests import util
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def c2():
+    from beast_b200 import synth
+    from beast_b200.engine import FitEngine
+    from beast_b200.gridprep import FitSetup
+    from oracle import fit_oracle as fo
+
+    g = synth.make_sedgrid("C2", seed=1234)
+    nz = synth.make_noisemodel(g)
+    obs = synth.make_observations(g, nz, 1536, seed=99, with_coords=False)
+    keys = fo.default_keys(g)
+    with warnings.catch_warnings():
+        warnings.simplefilter("ignore")
+        setup = FitSetup(g, nz, list(keys), max_nbins=200)
+    eng = FitEngine(setup)
+    res = eng.fit(obs.fluxes, threshold=-10.0, sparse=500, lnp_rng="device", seed=7)
+    return g, nz, obs, keys, setup, eng, res
+
+
+def test_full_size_properties(c2):
+    g, nz, obs, keys, setup, eng, res = c2
+    ns = len(obs)
+    assert setup.n_models == 4_000_000 and setup.n_q == 32
+    assert np.all(res.Pmax_j >= 0) and np.all(res.Pmax_j < setup.n_models)
+    assert np.all(res.n_sparse >= 1)
+    # total_log_norm = Pmax + ln(sum of weights), weights in (e^-10, 1], the best model has weight 1
+    dlt = res.total_log_norm - res.Pmax
+    assert np.all(dlt >= -1e-12) and np.all(dlt <= np.log(res.n_sparse.astype(float)) + 1e-9)
+    # every parameter's pdf is a normalised histogram of the same weights
+    for k in range(setup.n_q):
+        a, b = setup.bin_off[k], setup.bin_off[k + 1]
+        row = res.pdf1d[:, a:b]
+        assert np.all(row >= 0)
+        np.testing.assert_allclose(row.sum(axis=1), 1.0, rtol=0, atol=1e-9)
+        # percentiles are ordered and inside the bin range
+        per = res.per_vals[:, k, :]
+        assert np.all(np.diff(per, axis=1) >= -1e-12 * (1 + np.abs(per[:, :2])))
+        lo, hi = setup.bin_val[a:b].min(), setup.bin_val[a:b].max()
+        assert np.all(per >= lo - 1e-9 * abs(lo)) and np.all(per <= hi + 1e-9 * abs(hi))
+        # the expectation lies inside the parameter's range
+        col = setup.qcols[k][setup.g0_indxs]
+        span = col.max() - col.min()
+        assert np.all(res.exp_vals[:, k] >= col.min() - 1e-9 * span - 1e-300)
+        assert np.all(res.exp_vals[:, k] <= col.max() + 1e-9 * span + 1e-300)
+    # chi2min belongs to a member: it cannot beat the best chi2 of the arg-max by construction only
+    assert np.all(res.chi2min >= 0) and np.all(res.chi2min_j >= 0)
+    # sparse records: at most lnp_npts per star, distinct, lnp within the threshold of Pmax
+    cnt = np.diff(res.sparse_off)
+    np.testing.assert_array_equal(cnt, np.minimum(res.n_sparse, 500))
+    star = np.repeat(np.arange(ns), cnt)
+    assert np.all(res.sparse_lnp - res.Pmax[star].astype(np.float32) <= 1e-3)
+    assert np.all(res.sparse_lnp - res.Pmax[star].astype(np.float32) > -10.0 - 1e-3)
+    for e in range(0, ns, 97):
+        seg = res.sparse_j[res.sparse_off[e]:res.sparse_off[e + 1]]
+        assert len(np.unique(seg)) == len(seg)
+    # a second run is bit-identical (fixed summation order everywhere)
+    again = eng.fit(obs.fluxes, threshold=-10.0, sparse=500, lnp_rng="device", seed=7)
+    for name in ("Pmax", "total_log_norm", "pdf1d", "exp_vals", "per_vals", "sparse_j"):
+        np.testing.assert_array_equal(getattr(res, name), getattr(again, name), err_msg=name)
+
+
+def test_full_size_against_oracle_on_a_few_stars(c2):
+    from oracle import fit_oracle as fo
+
+    g, nz, obs, keys, setup, eng, res = c2
+    pick = [0, 1, 511, 777, 1200, 1535]
+    ost = fo.OracleSetup(g, nz, keys, max_nbins=200)
+    want = fo.fit_all(obs.fluxes[pick], ost, -10.0, fast=True)
+
+    class Sub:
+        pass
+
+    sub = Sub()
+    for name in ("Pmax", "Pmax_j", "total_log_norm", "chi2min", "chi2min_j", "exp_vals", "pdf1d", "per_vals"):
+        setattr(sub, name, getattr(res, name)[pick])
+    util.compare_to_reference(setup, sub, want)
+    np.testing.assert_array_equal(res.n_sparse[pick], [len(s[0]) for s in want["sparse"]])
