@@ -408,6 +408,8 @@ class FitEngine:
             raise ValueError("fluxes must have shape (n_stars, %d)" % s.nb)
         bs = min(batch or self.max_batch, self.max_batch)
         pair_len = int(s.pair_off[-1]) if (want_pdf2d and s.pair_off is not None) else 0
+        if pair_len:  # 2D PDFs are dense per star: keep one batch of them within ~16 GB of HBM
+            bs = int(max(1, min(bs, (16 << 30) // (pair_len * 8))))
         cap = ns * int(sparse) if (sparse is not None and sparse != "all") else 0
         key = (ns, pair_len, cap)
         res = self._result_cache.get(key) if reuse_buffers else None

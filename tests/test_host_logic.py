@@ -131,3 +131,27 @@ def test_golden_fixture_inputs_are_self_contained():
     g, nz, obs, args, ref = util.load_golden("tiny_thr10_pdf2d")
     assert len(g) == 1920 and obs.fluxes.shape == (16, 6) and args["threshold"] == -10.0
     assert (g["weight"] == 0).sum() > 0
+
+
+def test_merging_stat_tables(tmp_path):
+    # beast/tools/merge_beast_stats.py:12-71
+    from beast_b200.merge import merge_stats_files
+
+    filt = {"filternames": np.array(["F1", "F2"]), "wavelengths": np.array([1.0, 2.0])}
+    names = []
+    for i, n in enumerate((3, 2)):
+        cols = {"Name": np.array(["s%d_%d" % (i, j) for j in range(n)]), "Pmax": np.arange(n) + 10.0 * i,
+                "Pmax_indx": np.arange(n) + 100 * i}
+        p = str(tmp_path / ("proj_sd0-1_sub%d_stats.fits" % i))
+        fitsio.write_table_file(p, [cols, filt])
+        names.append(p)
+    n = merge_stats_files(names, str(tmp_path / "merged"))
+    assert n == 5
+    hd = fitsio.read_fits(str(tmp_path / "merged_stats.fits"))
+    tab = hd[1][1]
+    assert list(tab["Name"]) == ["s0_0", "s0_1", "s0_2", "s1_0", "s1_1"]
+    np.testing.assert_array_equal(tab["Pmax"], [0.0, 1.0, 2.0, 10.0, 11.0])
+    assert list(tab["reorder_tag"]) == ["sd0-1_sub0"] * 3 + ["sd0-1_sub1"] * 2
+    assert list(hd[2][1]["filternames"]) == ["F1", "F2"]
+    merge_stats_files(names, str(tmp_path / "tagged"), reorder_tag_list=["a", "b"])
+    assert list(fitsio.read_fits(str(tmp_path / "tagged_stats.fits"))[1][1]["reorder_tag"]) == ["a"] * 3 + ["b"] * 2
