@@ -200,13 +200,15 @@ __device__ __forceinline__ void load_entry(const bf_param_tables& prm, const dou
   const double* wp = weights + (static_cast<int64_t>(e) - entry_base) * BF_GROUP;
   r.w0 = __ldg(wp + lane);
   r.w1 = __ldg(wp + 32 + lane);
-  const int64_t ch0 = static_cast<int64_t>(g) * (BF_GROUP / BF_CHUNK);
+  // row of chunk c of this group = base + c * (n_q * 8) bytes: one 64-bit product per group
+  const uint8_t* base = prm.bin_tab +
+      (static_cast<size_t>(g) * (BF_GROUP / BF_CHUNK) * prm.n_q + k) * BF_CHUNK;
+  const uint32_t stride = static_cast<uint32_t>(prm.n_q) * BF_CHUNK;
 #pragma unroll
   for (int c = 0; c < BF_GROUP / BF_CHUNK; ++c) {
     const uint32_t byte = ((c < 4 ? m0 : m1) >> (8 * (c & 3))) & 0xffu;
     if (byte != 0) {  // warp-uniform: chunks without a member are never read
-      const size_t row = (static_cast<size_t>(ch0 + c) * prm.n_q + k) * BF_CHUNK;
-      const uint2 bb = __ldg(reinterpret_cast<const uint2*>(prm.bin_tab + row));
+      const uint2 bb = __ldg(reinterpret_cast<const uint2*>(base + c * stride));
       r.bits[c] = static_cast<unsigned long long>(bb.x) | (static_cast<unsigned long long>(bb.y) << 32);
     }
   }
@@ -289,11 +291,9 @@ hist_kernel(bf_param_tables prm, int rounds, const double* __restrict__ pmax,
 #pragma unroll
           for (int i = 0; i < BF_CHUNK; ++i) {
             if ((byte >> i) & 1u) {  // warp-uniform
-              const double w = wbuf[c * BF_CHUNK + i];
-              if (live) {
-                const int b = static_cast<int>((cur.bits[c] >> (8 * i)) & 0xffull);
-                hr[b * 32] += w;
-              }
+              // lanes beyond n_q own a column too (never read back), so no lane test is needed
+              const int b = static_cast<int>((cur.bits[c] >> (8 * i)) & 0xffull);
+              hr[b * 32] += wbuf[c * BF_CHUNK + i];
             }
           }
         }
