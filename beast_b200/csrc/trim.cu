@@ -24,9 +24,9 @@ trim_flags_kernel(int nb, int64_t n_models, const double* __restrict__ seds,
                   const double* __restrict__ hi, uint32_t* __restrict__ pattern,
                   uint32_t* __restrict__ hist) {
   const int64_t m = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x;
-  if (m >= n_models) return;
+  const bool valid = m < n_models;
   uint32_t p = kTrimComplete;
-  for (int b = 0; b < nb; ++b) {
+  for (int b = 0; valid && b < nb; ++b) {
     const int64_t i = m * nb + b;
     if (!(compl_[i] > 0.0)) p &= ~kTrimComplete;
     const double val = __dadd_rn(seds[i], bias[i]);
@@ -34,9 +34,11 @@ trim_flags_kernel(int nb, int64_t n_models, const double* __restrict__ seds,
     const double down = __dsub_rn(val, w), up = __dadd_rn(val, w);
     if (up >= lo[b] && down <= hi[b]) p |= 1u << b;
   }
-  pattern[m] = p;
-  const uint32_t bin = (p & 0xffffu) | ((p & kTrimComplete) ? (1u << nb) : 0u);
-  atomicAdd(hist + bin, 1u);
+  if (valid) pattern[m] = p;
+  // few distinct patterns exist, so neighbouring models mostly share one: count per warp first
+  const uint32_t bin = valid ? ((p & 0xffffu) | ((p & kTrimComplete) ? (1u << nb) : 0u)) : 0xffffffffu;
+  const uint32_t peers = __match_any_sync(0xffffffffu, bin);
+  if (valid && (threadIdx.x & 31) == __ffs(peers) - 1) atomicAdd(hist + bin, __popc(peers));
 }
 
 __global__ void __launch_bounds__(256)

@@ -49,6 +49,7 @@ def parse_args():
     ap.add_argument("--stars", type=int, default=None, help="override stars per GPU")
     ap.add_argument("--max-nbins", type=int, default=MAX_NBINS)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--pdf2d", action="store_true", help="also build 2D PDFs for Av, M_ini, logT (config C4)")
     ap.add_argument("--cpu-stars-per-core", type=int, default=2)
     return ap.parse_args()
 
@@ -195,7 +196,7 @@ def workload_config(args, nm, stars):
     return {"workload": CONFIGS[args.config][2], "config": args.config, "models": nm,
             "bands": 8 if args.config == "C4" else 6, "stars_per_gpu": stars,
             "threshold": THRESHOLD, "max_nbins": args.max_nbins, "lnp_npts": LNP_NPTS,
-            "outputs": "stats+pdf1d+sparse lnP", "parallelism": "stars sharded, grid replicated",
+            "outputs": "stats+pdf1d+sparse lnP" + ("+pdf2d" if args.pdf2d else ""), "parallelism": "stars sharded, grid replicated",
             "l2": "inputs larger than L2 (grid tiles + exact arrays + parameter tables > 126 MB)"}
 
 
@@ -219,12 +220,15 @@ def run_ours(args, rank, world, local_rank):
     keys = [k for k in g.keys() if k not in
             "osl keep weight grid_weight prior_weight fullgrid_idx stage specgrid_indx phase eep".split()]
     t0 = time.perf_counter()
-    setup = FitSetup(g, nz, keys, max_nbins=args.max_nbins)
+    p2d = ["Av", "M_ini", "logT"] if args.pdf2d else None
+    setup = FitSetup(g, nz, keys, max_nbins=args.max_nbins, pdf2d_param_list=p2d, make_pdf2d=args.pdf2d)
     eng = FitEngine(setup, device=dev, gmin_budget_bytes=24 << 30)
     setup_s = time.perf_counter() - t0
     nm = setup.n_models
     fluxes = np.ascontiguousarray(obs.fluxes)
     bs = eng.max_batch
+    if args.pdf2d:  # 2D PDFs are dense per star: same bound as FitEngine.fit
+        bs = int(max(1, min(bs, (16 << 30) // (int(setup.pair_off[-1]) * 8))))
     batches = [(a, min(stars, a + bs)) for a in range(0, stars, bs)]
     d_flux = [torch.from_numpy(fluxes[a:b]).to(dev) for a, b in batches]
     pinned = torch.from_numpy(fluxes).pin_memory()
@@ -236,11 +240,12 @@ def run_ours(args, rank, world, local_rank):
 
     def step_resident():
         for (a, b), df in zip(batches, d_flux):
-            eng.fit_batch(df, THRESHOLD, sparse=LNP_NPTS, lnp_rng="device", seed=1, star_base=a)
+            eng.fit_batch(df, THRESHOLD, sparse=LNP_NPTS, lnp_rng="device", seed=1, star_base=a,
+                          want_pdf2d=args.pdf2d)
 
     def step_e2e():
         return eng.fit(pinned.numpy(), THRESHOLD, sparse=LNP_NPTS, lnp_rng="device", seed=1,
-                       reuse_buffers=True)
+                       reuse_buffers=True, want_pdf2d=args.pdf2d)
 
     # ---- device-resident throughput ------------------------------------------------
     sampler = ClockSampler(local_rank)  # started before the warm-up: the first NVML queries stall
