@@ -21,7 +21,6 @@
 
 namespace bf {
 
-constexpr int kMaxRounds = BF_MAX_PARAMS / 32;
 constexpr int kWeightWarps = 8;
 constexpr int kStageDoubles = BF_GROUP;  // per-warp staging: the current group's weights
 constexpr int kSideBlocksPerSm = 64;  // grid cap of the grid-stride kernels, in blocks per SM
@@ -106,7 +105,7 @@ struct HistSmem {
 // ---------------------------------------------------------------------------------------
 // exp_kernel: sum_m w_m * q_k[m] for every parameter (fit.py:743), lane <-> parameter.
 // No shared-memory state, so many warps stay resident and hide the row-load latency.
-// Writes the raw sums; hist_kernel divides by the weight sum.
+// Also sums the per-group weight partials, so it writes the finished expectations.
 // ---------------------------------------------------------------------------------------
 constexpr int kExpWarps = 8;
 
@@ -399,15 +398,13 @@ hist_kernel(bf_param_tables prm, int rounds, const double* __restrict__ pmax,
 
 }  // namespace bf
 
-// phases: 1 = exact weights + expectations, 2 = histograms / percentiles, 3 = both
-static int accumulate_impl(int phases, const bf_exact_grid* grid, const bf_param_tables* params,
+extern "C" int bf_exact_accumulate(const bf_exact_grid* grid, const bf_param_tables* params,
                                    int64_t star_begin, int64_t n_stars, const double* flux64,
                                    const double* pmax, double threshold, const uint32_t* offsets,
-                                   const uint32_t* list,
-                                   const uint32_t* entry_star, const int32_t* star_order,
-                                   int64_t entry_base, int64_t n_entries, const double* percentiles_host,
-                                   const bf_accum_scratch* scratch, const bf_star_outputs* out,
-                                   void* stream, void* aux_stream) {
+                                   const uint32_t* list, const uint32_t* entry_star,
+                                   const int32_t* star_order, int64_t entry_base, int64_t n_entries,
+                                   const double* percentiles_host, const bf_accum_scratch* scratch,
+                                   const bf_star_outputs* out, void* stream, void* aux_stream) {
   using namespace bf;
   BF_REQUIRE(grid && params && out && scratch && percentiles_host, "bf_exact_accumulate: null struct");
   BF_REQUIRE(grid->nb >= 1 && grid->nb <= BF_MAX_BANDS, "bf_exact_accumulate: bad band count");
@@ -455,7 +452,7 @@ static int accumulate_impl(int phases, const bf_exact_grid* grid, const bf_param
     BF_CUDA_TRY(cudaDeviceGetAttribute(&sm_count[dev], cudaDevAttrMultiProcessorCount, dev));
     smem_limit[dev] = optin;
   }
-  if ((phases & 1) && n_entries > 0) {
+  if (n_entries > 0) {
     const int64_t blocks = (n_entries + kWeightWarps - 1) / kWeightWarps;
     BF_REQUIRE(blocks < (1LL << 31), "bf_exact_accumulate: too many list entries in one call");
     const int64_t cap = static_cast<int64_t>(sm_count[dev]) * kSideBlocksPerSm;
@@ -486,7 +483,7 @@ static int accumulate_impl(int phases, const bf_exact_grid* grid, const bf_param
               params->max_bins, params->n_q, smem, budget);
     return BF_ERR_TOO_LARGE;
   }
-  if (phases & 2) {
+  {
     hist_kernel<<<static_cast<unsigned>(n_stars), nw * 32, smem, st>>>(
         *params, rounds, pmax, offsets, list, star_order, star_begin, entry_base, *scratch,
         percentiles_host[0], percentiles_host[1], percentiles_host[2], *out);
@@ -498,7 +495,7 @@ static int accumulate_impl(int phases, const bf_exact_grid* grid, const bf_param
   // (the histogram blocks are launched first so that they claim their shared memory).
   if (aux_stream) BF_CUDA_TRY(cudaStreamWaitEvent(sx, ev_weights[dev], 0));
   if (timing) cudaEventRecord(tev[3], sx);
-  if (phases & 1) {
+  {
     const int64_t cap = static_cast<int64_t>(sm_count[dev]) * kSideBlocksPerSm;
     exp_kernel<<<static_cast<unsigned>(n_stars < cap ? n_stars : cap), kExpWarps * 32,
                  (kExpWarps * params->n_q + kExpWarps) * sizeof(double), sx>>>(
@@ -523,16 +520,4 @@ static int accumulate_impl(int phases, const bf_exact_grid* grid, const bf_param
     for (auto& e : tev) cudaEventDestroy(e);
   }
   return BF_OK;
-}
-
-extern "C" int bf_exact_accumulate(const bf_exact_grid* grid, const bf_param_tables* params,
-                                   int64_t star_begin, int64_t n_stars, const double* flux64,
-                                   const double* pmax, double threshold, const uint32_t* offsets,
-                                   const uint32_t* list, const uint32_t* entry_star,
-                                   const int32_t* star_order, int64_t entry_base, int64_t n_entries,
-                                   const double* percentiles_host, const bf_accum_scratch* scratch,
-                                   const bf_star_outputs* out, void* stream, void* aux_stream) {
-  return accumulate_impl(3, grid, params, star_begin, n_stars, flux64, pmax, threshold, offsets, list,
-                         entry_star, star_order, entry_base, n_entries, percentiles_host, scratch,
-                         out, stream, aux_stream);
 }

@@ -12,10 +12,15 @@ __device__ __forceinline__ void exact_lnp(const bf_exact_grid& g, const double* 
                                           double& lnp, double& chi2) {
   double acc = 0.0;
   if (g.cov_off == nullptr) {
+    const double* pm = g.msb + j;  // walk the band-major arrays: one pointer add per band
+    const double* pv = g.ivar + j;
+#pragma unroll 2
     for (int b = 0; b < g.nb; ++b) {
-      const double d = __dsub_rn(sflux[b], g.msb[static_cast<int64_t>(b) * g.ld_model + j]);
+      const double d = __dsub_rn(sflux[b], __ldg(pm));
       const double dd = __dmul_rn(d, d);
-      acc = __dadd_rn(acc, __dmul_rn(dd, g.ivar[static_cast<int64_t>(b) * g.ld_model + j]));
+      acc = __dadd_rn(acc, __dmul_rn(dd, __ldg(pv)));
+      pm += g.ld_model;
+      pv += g.ld_model;
     }
   } else {
     // N_covar_chi2 (likelihood.py:88-106): diagonal terms, then for each k the packed

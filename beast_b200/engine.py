@@ -21,8 +21,6 @@ from . import _cabi
 from ._cabi import (GROUP, SELECT_SPLIT, STAR_BLOCK, AccumScratch, ExactGrid, ParamTables,
                     StarOutputs)
 
-_INF_BITS = 0x7F800000
-
 
 def _torch():
     import torch
@@ -347,7 +345,6 @@ class FitEngine:
                                C.c_void_p(self._aux_stream.cuda_stream))
                 self.launches += 3
             o["n_groups_selected"] = off_star[1:] - off_star[:-1]
-            o["n_sparse"] = o["n_sparse"]
 
             if want_pdf2d and self.d_pair_bin is not None:
                 row = int(s.pair_off[-1])
