@@ -51,6 +51,8 @@ class ParamTables(C.Structure):
         ("q_lin", c_void_p),
         ("bin_off", c_void_p),
         ("bin_val", c_void_p),
+        ("q_const", c_void_p),
+        ("bin_q", c_void_p),
     ]
 
 

@@ -126,7 +126,9 @@ exp_kernel(bf_param_tables prm, int rounds, const uint32_t* __restrict__ offsets
   const uint32_t e1 = offsets[(s + 1) * BF_SELECT_SPLIT];
   for (int r = 0; r < rounds; ++r) {
     const int k = r * 32 + lane;
-    const bool live = k < nq;
+    // parameters whose expectation comes from the histogram are not read here
+    const bool live = k < nq && !(prm.q_const && prm.q_const[k]);
+    if (!__any_sync(0xffffffffu, live)) continue;
     const int kk = live ? k : 0;
     double eacc = 0.0;
     for (uint32_t e = e0 + warp; e < e1; e += kExpWarps) {
@@ -139,20 +141,22 @@ exp_kernel(bf_param_tables prm, int rounds, const uint32_t* __restrict__ offsets
       for (int c = 0; c < BF_GROUP / BF_CHUNK; ++c) {
         const uint32_t byte = ((c < 4 ? m0 : m1) >> (8 * (c & 3))) & 0xffu;
         if (byte == 0) continue;
-        const size_t row = (static_cast<size_t>(ch0 + c) * nq + kk) * BF_CHUNK;
-        const int4* qp = reinterpret_cast<const int4*>(prm.q_tab + row);
         const double2* wq = reinterpret_cast<const double2*>(wp + c * BF_CHUNK);
-        const int4 qa = __ldg(qp), qb = __ldg(qp + 1);
         const double2 w01 = __ldg(wq), w23 = __ldg(wq + 1), w45 = __ldg(wq + 2), w67 = __ldg(wq + 3);
-        // non-members carry weight 0
-        eacc += w01.x * static_cast<double>(qa.x);
-        eacc += w01.y * static_cast<double>(qa.y);
-        eacc += w23.x * static_cast<double>(qa.z);
-        eacc += w23.y * static_cast<double>(qa.w);
-        eacc += w45.x * static_cast<double>(qb.x);
-        eacc += w45.y * static_cast<double>(qb.y);
-        eacc += w67.x * static_cast<double>(qb.z);
-        eacc += w67.y * static_cast<double>(qb.w);
+        if (live) {  // idle lanes touch no row: a row is one 32-byte sector
+          const size_t row = (static_cast<size_t>(ch0 + c) * nq + kk) * BF_CHUNK;
+          const int4* qp = reinterpret_cast<const int4*>(prm.q_tab + row);
+          const int4 qa = __ldg(qp), qb = __ldg(qp + 1);
+          // non-members carry weight 0
+          eacc += w01.x * static_cast<double>(qa.x);
+          eacc += w01.y * static_cast<double>(qa.y);
+          eacc += w23.x * static_cast<double>(qa.z);
+          eacc += w23.y * static_cast<double>(qa.w);
+          eacc += w45.x * static_cast<double>(qb.x);
+          eacc += w45.y * static_cast<double>(qb.y);
+          eacc += w67.x * static_cast<double>(qb.z);
+          eacc += w67.y * static_cast<double>(qb.w);
+        }
       }
     }
     if (live) red[warp * nq + k] = eacc;
@@ -169,6 +173,7 @@ exp_kernel(bf_param_tables prm, int rounds, const uint32_t* __restrict__ offsets
 #pragma unroll
   for (int w = 0; w < kExpWarps; ++w) wtot += wred[w];
   for (int k = threadIdx.x; k < nq; k += blockDim.x) {
+    if (prm.q_const && prm.q_const[k]) continue;  // written by the histogram kernel
     double e = 0.0;
 #pragma unroll
     for (int w = 0; w < kExpWarps; ++w) e += red[w * nq + k];
@@ -191,9 +196,11 @@ struct EntryRows {
 
 // rows of a group whose list entry (group id g, membership words) is already in registers:
 // no load here depends on another load
+template <bool MASKED = false>
 __device__ __forceinline__ void load_entry(const bf_param_tables& prm, const double* weights,
                                            int64_t entry_base, uint32_t e, uint32_t g, uint32_t m0,
-                                           uint32_t m1, int k, int lane, EntryRows& r) {
+                                           uint32_t m1, int k, int lane, EntryRows& r,
+                                           uint32_t lane_mask = 0xffffffffu) {
   r.m0 = m0;
   r.m1 = m1;
   const double* wp = weights + (static_cast<int64_t>(e) - entry_base) * BF_GROUP;
@@ -207,10 +214,123 @@ __device__ __forceinline__ void load_entry(const bf_param_tables& prm, const dou
   for (int c = 0; c < BF_GROUP / BF_CHUNK; ++c) {
     const uint32_t byte = ((c < 4 ? m0 : m1) >> (8 * (c & 3))) & 0xffu;
     if (byte != 0) {  // warp-uniform: chunks without a member are never read
-      const uint2 bb = __ldg(reinterpret_cast<const uint2*>(base + c * stride));
+      uint2 bb = __ldg(reinterpret_cast<const uint2*>(base + c * stride));
+      if (MASKED) {  // lanes without a parameter see bin 0 everywhere
+        bb.x &= lane_mask;
+        bb.y &= lane_mask;
+      }
       r.bits[c] = static_cast<unsigned long long>(bb.x) | (static_cast<unsigned long long>(bb.y) << 32);
     }
   }
+}
+
+// expectation of a parameter whose bins each hold one value: q_mid + sum_b H_b (q_b - q_mid) / sum w
+// (fit.py:743 regrouped by bin; bin_q holds q_b - q_mid, q_mid = q_lin[2k], so that a
+// single-valued parameter comes out exactly); eq holds this lane's part of the sum
+__device__ __forceinline__ void store_bin_expectation(double eq, double wtot, bool empty,
+                                                      double q_mid, double* dst, int lane) {
+#pragma unroll
+  for (int d = 16; d > 0; d >>= 1) eq += __shfl_xor_sync(0xffffffffu, eq, d);
+  if (lane == 0) *dst = empty ? __longlong_as_double(0x7ff8000000000000LL) : q_mid + eq / wtot;
+}
+
+// per-star reductions over the group partials, fixed order: weight sum (returned), chi2
+// minimum and its model (fit.py:689, 725-726), total_log_norm (fit.py:731)
+__device__ __forceinline__ double star_totals(uint32_t e0, uint32_t e1, int64_t entry_base,
+                                              const bf_accum_scratch& sc, double M, int64_t s,
+                                              double* red, long long* redj,
+                                              const bf_star_outputs& out) {
+  const int nw = blockDim.x >> 5;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  double wpart = 0.0, cpart = 1.7976931348623157e308;
+  long long cj = -1;
+  for (uint32_t e = e0 + threadIdx.x; e < e1; e += blockDim.x) {
+    const int64_t slot = static_cast<int64_t>(e) - entry_base;
+    wpart += sc.part_wsum[slot];
+    const long long oj = sc.part_chi2_j[slot];
+    const double oc = sc.part_chi2[slot];
+    if (oj >= 0 && (cj < 0 || oc < cpart || (oc == cpart && oj < cj))) {
+      cpart = oc;
+      cj = oj;
+    }
+  }
+#pragma unroll
+  for (int d = 16; d > 0; d >>= 1) {
+    wpart += __shfl_xor_sync(0xffffffffu, wpart, d);
+    const double oc = __shfl_xor_sync(0xffffffffu, cpart, d);
+    const long long oj = __shfl_xor_sync(0xffffffffu, cj, d);
+    if (oj >= 0 && (cj < 0 || oc < cpart || (oc == cpart && oj < cj))) {
+      cpart = oc;
+      cj = oj;
+    }
+  }
+  if (lane == 0) {
+    red[warp] = wpart;
+    red[nw + warp] = cpart;
+    redj[warp] = cj;
+  }
+  __syncthreads();
+  double wtot = 0.0;
+  for (int w = 0; w < nw; ++w) wtot += red[w];
+  const bool empty = !(wtot > 0.0);
+  const double qnan = __longlong_as_double(0x7ff8000000000000LL);
+  if (threadIdx.x == 0) {
+    double c = 1.7976931348623157e308;
+    long long bj = -1;
+    for (int w = 0; w < nw; ++w) {
+      if (redj[w] >= 0 && (bj < 0 || red[nw + w] < c || (red[nw + w] == c && redj[w] < bj))) {
+        c = red[nw + w];
+        bj = redj[w];
+      }
+    }
+    out.total_log_norm[s] = empty ? qnan : M + log(wtot);
+    out.chi2min[s] = empty ? qnan : c;
+    out.chi2min_j[s] = bj;
+  }
+  return wtot;
+}
+
+// percentiles of the finished pdfs (one warp per parameter, fit_metrics/common.py:112-121)
+// and the exclusive prefix of the per-group member counts over this star's list
+__device__ __forceinline__ void star_percentiles_and_prefix(const bf_param_tables& prm, int64_t s,
+                                                            uint32_t e0, uint32_t e1, double p0,
+                                                            double p1, double p2, double* cdf_area,
+                                                            uint32_t* sscan,
+                                                            const bf_star_outputs& out) {
+  const int nw = blockDim.x >> 5;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int nq = prm.n_q, tb = prm.total_bins;
+  double* cdf = cdf_area + warp * kMaxBinsPerParam;
+  for (int kq = warp; kq < nq; kq += nw) {
+    const int b0 = prm.bin_off[kq];
+    const int nbk = prm.bin_off[kq + 1] - b0;
+    warp_percentiles(out.pdf1d + s * tb + b0, prm.bin_val + b0, nbk, cdf, p0, p1, p2,
+                     out.per_vals + (s * nq + kq) * 3, lane);
+  }
+
+  // ---- per-group member counts -> exclusive prefix over this star's list -----------------
+  uint32_t carry = 0;
+  for (uint32_t base = e0; base < e1; base += blockDim.x) {
+    const uint32_t e = base + threadIdx.x;
+    const uint32_t v = e < e1 ? out.member_prefix[e] : 0u;
+    uint32_t inc = v;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+      const uint32_t t = __shfl_up_sync(0xffffffffu, inc, d);
+      if (lane >= d) inc += t;
+    }
+    __syncthreads();
+    if (lane == 31) sscan[warp] = inc;
+    __syncthreads();
+    uint32_t woff = 0, tot = 0;
+    for (int w = 0; w < nw; ++w) {
+      if (w < warp) woff += sscan[w];
+      tot += sscan[w];
+    }
+    if (e < e1) out.member_prefix[e] = carry + woff + inc - v;
+    carry += tot;
+  }
+  if (threadIdx.x == 0) out.n_sparse[s] = carry;
 }
 
 __global__ void __launch_bounds__(512, 1)
@@ -302,52 +422,8 @@ hist_kernel(bf_param_tables prm, int rounds, const double* __restrict__ pmax,
     }
   }
 
-  // ---- per-star reductions over the group partials, fixed order ------------------------
-  double wpart = 0.0, cpart = 1.7976931348623157e308;
-  long long cj = -1;
-  for (uint32_t e = e0 + threadIdx.x; e < e1; e += blockDim.x) {
-    const int64_t slot = static_cast<int64_t>(e) - entry_base;
-    wpart += sc.part_wsum[slot];
-    const long long oj = sc.part_chi2_j[slot];
-    const double oc = sc.part_chi2[slot];
-    if (oj >= 0 && (cj < 0 || oc < cpart || (oc == cpart && oj < cj))) {
-      cpart = oc;
-      cj = oj;
-    }
-  }
-#pragma unroll
-  for (int d = 16; d > 0; d >>= 1) {
-    wpart += __shfl_xor_sync(0xffffffffu, wpart, d);
-    const double oc = __shfl_xor_sync(0xffffffffu, cpart, d);
-    const long long oj = __shfl_xor_sync(0xffffffffu, cj, d);
-    if (oj >= 0 && (cj < 0 || oc < cpart || (oc == cpart && oj < cj))) {
-      cpart = oc;
-      cj = oj;
-    }
-  }
-  if (lane == 0) {
-    red[warp] = wpart;
-    red[nw + warp] = cpart;
-    redj[warp] = cj;
-  }
-  __syncthreads();
-  double wtot = 0.0;
-  for (int w = 0; w < nw; ++w) wtot += red[w];
+  const double wtot = star_totals(e0, e1, entry_base, sc, M, s, red, redj, out);
   const bool empty = !(wtot > 0.0);
-  const double qnan = __longlong_as_double(0x7ff8000000000000LL);
-  if (threadIdx.x == 0) {
-    double c = 1.7976931348623157e308;
-    long long bj = -1;
-    for (int w = 0; w < nw; ++w) {
-      if (redj[w] >= 0 && (bj < 0 || red[nw + w] < c || (red[nw + w] == c && redj[w] < bj))) {
-        c = red[nw + w];
-        bj = redj[w];
-      }
-    }
-    out.total_log_norm[s] = empty ? qnan : M + log(wtot);
-    out.chi2min[s] = empty ? qnan : c;
-    out.chi2min_j[s] = bj;
-  }
 
   // ---- merge private histograms (warp order), normalise --------------------------------
   const double inv = empty ? 0.0 : 1.0 / wtot;
@@ -356,44 +432,273 @@ hist_kernel(bf_param_tables prm, int rounds, const double* __restrict__ pmax,
     const int nbk = prm.bin_off[kq + 1] - b0;
     const size_t col = static_cast<size_t>(kq >> 5) * mb * 32 + (kq & 31);
     double* row = out.pdf1d + s * tb + b0;
+    const bool from_bins = prm.q_const && prm.q_const[kq];
+    double eq = 0.0;
     for (int b = lane; b < nbk; b += 32) {
       double v = 0.0;
       for (int w = 0; w < nw; ++w) v += hist[w * hist_per_warp + col + static_cast<size_t>(b) * 32];
       row[b] = v * inv;
+      if (from_bins) eq += v * prm.bin_q[b0 + b];
     }
+    if (from_bins)
+      store_bin_expectation(eq, wtot, empty, prm.q_lin[2 * kq], out.exp_vals + s * nq + kq, lane);
   }
   __syncthreads();  // histograms are consumed: their memory becomes the percentile scratch
-  double* cdf = hist + warp * kMaxBinsPerParam;
-  for (int kq = warp; kq < nq; kq += nw) {
-    const int b0 = prm.bin_off[kq];
-    const int nbk = prm.bin_off[kq + 1] - b0;
-    warp_percentiles(out.pdf1d + s * tb + b0, prm.bin_val + b0, nbk, cdf, p0, p1, p2,
-                     out.per_vals + (s * nq + kq) * 3, lane);
+  star_percentiles_and_prefix(prm, s, e0, e1, p0, p1, p2, hist, sscan, out);
+}
+
+// ---------------------------------------------------------------------------------------
+// hist_window_kernel: the histogram kernel for wide bin tables.  A star's members fall in a
+// narrow range of bins of most parameters, so the private histograms only need the occupied
+// range [min bin, max bin] of every parameter.  A first walk over the star's bin rows finds
+// the ranges (16-bit SIMD min/max, no shared-memory traffic); the private copies are then
+// sized by the ranges (see the layout step) instead of 32 x max_bins doubles per warp, and
+// as many of the block's 16 warps as fit work on the star (4 with the full-width layout at
+// 200 bins).
+// Shared memory (doubles): hist [hist_doubles] | wbuf [16][64] | red, redj, scan | int
+// tables wmin, wmax, plane, lparam, lcol [rounds*32] | tmpw [32] | misc [4].
+// ---------------------------------------------------------------------------------------
+constexpr int kWindowWarps = 16;
+
+struct WindowSmem {
+  static __host__ __device__ size_t bytes(int hist_doubles, int rounds) {
+    return (static_cast<size_t>(hist_doubles) + kWindowWarps * kStageDoubles + 3 * kWindowWarps + 8) *
+               sizeof(double) +
+           (5 * static_cast<size_t>(rounds) * 32 + 32 + 4) * sizeof(int);
+  }
+};
+
+// The accumulation loop of hist_window_kernel for one warp and one round of 32 parameters:
+// groups e, e + step, ... of the star; col[bin * STRIDE] is this lane's histogram column.
+// Same three-deep software pipeline as hist_kernel.
+template <int STRIDE>
+__device__ __forceinline__ void accumulate_columns(const bf_param_tables& prm, const double* weights,
+                                                   int64_t entry_base, const uint32_t* __restrict__ list,
+                                                   const uint32_t* __restrict__ member_mask, uint32_t e,
+                                                   uint32_t e1, uint32_t step, int kk, uint32_t lmask,
+                                                   int lane, double* col, double* wbuf) {
+  // 32-bit shared-window address of the column: the update below is written with explicit
+  // ld.shared / st.shared so that the compiler neither rebuilds the base per member nor
+  // orders the (distinct) weight loads behind the histogram stores
+  const uint32_t col_s = static_cast<uint32_t>(__cvta_generic_to_shared(col));
+  EntryRows cur, nxt;
+  uint32_t g1 = 0, a1 = 0, b1 = 0, g2 = 0, a2 = 0, b2 = 0;
+  if (e < e1) {
+    g1 = list[e];
+    a1 = member_mask[static_cast<size_t>(e) * kWordsPerGroup];
+    b1 = member_mask[static_cast<size_t>(e) * kWordsPerGroup + 1];
+    load_entry<true>(prm, weights, entry_base, e, g1, a1, b1, kk, lane, nxt, lmask);
+    if (e + step < e1) {
+      g2 = list[e + step];
+      a2 = member_mask[static_cast<size_t>(e + step) * kWordsPerGroup];
+      b2 = member_mask[static_cast<size_t>(e + step) * kWordsPerGroup + 1];
+    }
+  }
+  while (e < e1) {
+    cur = nxt;
+    const uint32_t en = e + step;
+    if (en < e1) {
+      load_entry<true>(prm, weights, entry_base, en, g2, a2, b2, kk, lane, nxt, lmask);
+      const uint32_t en2 = en + step;
+      if (en2 < e1) {
+        g2 = list[en2];
+        a2 = member_mask[static_cast<size_t>(en2) * kWordsPerGroup];
+        b2 = member_mask[static_cast<size_t>(en2) * kWordsPerGroup + 1];
+      }
+    }
+    if ((cur.m0 | cur.m1) != 0) {
+      wbuf[lane] = cur.w0;
+      wbuf[32 + lane] = cur.w1;
+      __syncwarp();
+#pragma unroll
+      for (int c = 0; c < BF_GROUP / BF_CHUNK; ++c) {
+        const uint32_t byte = ((c < 4 ? cur.m0 : cur.m1) >> (8 * (c & 3))) & 0xffu;
+        if (byte == 0) continue;
+#pragma unroll
+        for (int i = 0; i < BF_CHUNK; ++i) {
+          if ((byte >> i) & 1u) {  // warp-uniform
+            const uint32_t b = static_cast<uint32_t>((cur.bits[c] >> (8 * i)) & 0xffull);
+            const uint32_t addr = col_s + b * (STRIDE * 8);
+            double h;
+            asm volatile("ld.shared.f64 %0, [%1];" : "=d"(h) : "r"(addr));
+            h += wbuf[c * BF_CHUNK + i];
+            asm volatile("st.shared.f64 [%0], %1;" ::"r"(addr), "d"(h));
+          }
+        }
+      }
+      __syncwarp();
+    }
+    e = en;
+  }
+}
+
+__global__ void __launch_bounds__(kWindowWarps * 32, 1)
+hist_window_kernel(bf_param_tables prm, int rounds, int hist_doubles,
+                   const double* __restrict__ pmax, const uint32_t* __restrict__ offsets,
+                   const uint32_t* __restrict__ list, const int32_t* __restrict__ star_order,
+                   int64_t star_begin, int64_t entry_base, bf_accum_scratch sc, double p0,
+                   double p1, double p2, bf_star_outputs out) {
+  extern __shared__ __align__(16) double smem_d[];
+  constexpr int NW = kWindowWarps;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int nq = prm.n_q, tb = prm.total_bins;
+  const int npad = rounds * 32;
+
+  double* hist = smem_d;
+  double* wbuf_all = hist + hist_doubles;
+  double* red = wbuf_all + NW * kStageDoubles;
+  long long* redj = reinterpret_cast<long long*>(red + 2 * NW);
+  uint32_t* sscan = reinterpret_cast<uint32_t*>(redj + NW);
+  int* wmin = reinterpret_cast<int*>(red + 3 * NW + 8);
+  int* wmax = wmin + npad;
+  int* plane = wmax + npad;    // lane that works on parameter k (within its round of 32)
+  int* lparam = plane + npad;  // parameter of a lane, -1: none
+  int* lcol = lparam + npad;   // a lane's column: offset of (absolute) bin 0 within a copy
+  int* tmpw = lcol + npad;     // [32] range widths by lane
+  int* misc = tmpw + 32;       // [0] doubles per private copy, [1] warps that get one
+
+  const int64_t s =
+      star_begin + (star_order ? star_order[blockIdx.x] : static_cast<int64_t>(blockIdx.x));
+  for (int i = threadIdx.x; i < npad; i += blockDim.x) {
+    wmin[i] = 255;
+    wmax[i] = 0;
+  }
+  __syncthreads();
+
+  const double M = pmax[s];
+  const uint32_t e0 = offsets[s * BF_SELECT_SPLIT];
+  const uint32_t e1 = offsets[(s + 1) * BF_SELECT_SPLIT];
+  const uint32_t stride = static_cast<uint32_t>(nq) * BF_CHUNK;
+
+  // ---- pass 1: occupied bin range of every parameter ------------------------------------
+  for (int r = 0; r < rounds; ++r) {
+    const int k = r * 32 + lane;
+    const bool live = k < nq;
+    const int kk = live ? k : 0;
+    uint32_t mn2 = 0x00ff00ffu, mx2 = 0;
+    uint32_t e = e0 + warp;
+    uint32_t g1 = 0, a1 = 0, b1 = 0;
+    if (e < e1) {
+      g1 = list[e];
+      a1 = out.member_mask[static_cast<size_t>(e) * kWordsPerGroup];
+      b1 = out.member_mask[static_cast<size_t>(e) * kWordsPerGroup + 1];
+    }
+    while (e < e1) {
+      const uint32_t g = g1, m0 = a1, m1 = b1;
+      const uint32_t en = e + NW;
+      if (en < e1) {
+        g1 = list[en];
+        a1 = out.member_mask[static_cast<size_t>(en) * kWordsPerGroup];
+        b1 = out.member_mask[static_cast<size_t>(en) * kWordsPerGroup + 1];
+      }
+      if ((m0 | m1) != 0) {
+        const uint8_t* base = prm.bin_tab +
+            (static_cast<size_t>(g) * (BF_GROUP / BF_CHUNK) * nq + kk) * BF_CHUNK;
+#pragma unroll
+        for (int c = 0; c < BF_GROUP / BF_CHUNK; ++c) {
+          const uint32_t byte = ((c < 4 ? m0 : m1) >> (8 * (c & 3))) & 0xffu;
+          if (byte == 0) continue;
+          const uint2 bb = __ldg(reinterpret_cast<const uint2*>(base + c * stride));
+          // every model of a chunk with a member counts (a superset of the members' range
+          // is all that is needed): bytes -> two 16-bit lanes, native 3-input SIMD min/max
+          const uint32_t xe = __byte_perm(bb.x, 0, 0x4240), xo = __byte_perm(bb.x, 0, 0x4341);
+          const uint32_t ye = __byte_perm(bb.y, 0, 0x4240), yo = __byte_perm(bb.y, 0, 0x4341);
+          mn2 = __vimin3_u16x2(__vimin3_u16x2(mn2, xe, xo), ye, yo);
+          mx2 = __vimax3_u16x2(__vimax3_u16x2(mx2, xe, xo), ye, yo);
+        }
+      }
+      e = en;
+    }
+    const int mn = min(mn2 & 0xffffu, mn2 >> 16);
+    const int mx = max(mx2 & 0xffffu, mx2 >> 16);
+    if (live) {
+      atomicMin(wmin + k, mn);
+      atomicMax(wmax + k, mx);
+    }
+  }
+  __syncthreads();
+
+  // ---- lay out a private copy --------------------------------------------------------------
+  // 16 stacks of doubles, interleaved (stack j holds slots j, j+16, j+32, ...).  Lanes are
+  // re-assigned to parameters by range width: lanes 0..15 take the 16 widest ranges in
+  // decreasing order, lanes 16..31 the others in increasing order, and lane 16+j stacks its
+  // range on top of lane j's.  A half-warp always touches 16 different stacks, so the 64-bit
+  // accesses are conflict free whatever the bins are, and the copy holds
+  // 16 * max_j (width_j + width_{31-j}) doubles -- close to the sum of the widths.
+  // Lanes without a parameter get a one-bin range of their own.
+  if (warp == 0) {
+    int rows = 0;
+    for (int r = 0; r < rounds; ++r) {
+      const int k = r * 32 + lane;
+      const bool occupied = k < nq && wmin[k] <= wmax[k];
+      const int mn = occupied ? wmin[k] : 0;
+      const int w = occupied ? wmax[k] - wmin[k] + 1 : 1;
+      int rank = 0;
+#pragma unroll
+      for (int j = 0; j < 32; ++j) {
+        const int wj = __shfl_sync(0xffffffffu, w, j);
+        rank += (wj > w || (wj == w && j < lane)) ? 1 : 0;
+      }
+      const int slot = rank < 16 ? rank : 47 - rank;
+      tmpw[slot] = w;
+      __syncwarp();
+      const int below = slot >= 16 ? tmpw[slot - 16] : 0;
+      const int depth = __reduce_max_sync(0xffffffffu, lane < 16 ? tmpw[lane] + tmpw[lane + 16] : 0);
+      __syncwarp();
+      lparam[r * 32 + slot] = k < nq ? k : -1;
+      lcol[r * 32 + slot] = (rows + below - mn) * 16 + (slot & 15);
+      plane[k] = slot;
+      rows += depth;
+    }
+    if (lane == 0) {
+      const int fit = hist_doubles / (rows * 16);
+      misc[0] = rows * 16;
+      misc[1] = fit < NW ? fit : NW;
+    }
+  }
+  __syncthreads();
+  const int copy = misc[0], nwe = misc[1];
+  for (int i = threadIdx.x; i < nwe * copy; i += blockDim.x) hist[i] = 0.0;
+  __syncthreads();
+
+  // ---- pass 2: accumulate, warps 0..nwe-1 share the star's groups -------------------------
+  if (warp < nwe) {
+    double* wbuf = wbuf_all + warp * kStageDoubles;
+    for (int r = 0; r < rounds; ++r) {
+      const int k = lparam[r * 32 + lane];
+      const bool live = k >= 0;  // the others read bin 0 everywhere and own a one-bin range
+      accumulate_columns<16>(prm, sc.weights, entry_base, list, out.member_mask, e0 + warp, e1, nwe,
+                             live ? k : 0, live ? 0xffffffffu : 0u, lane,
+                             hist + warp * copy + lcol[r * 32 + lane], wbuf);
+    }
   }
 
-  // ---- per-group member counts -> exclusive prefix over this star's list -----------------
-  uint32_t carry = 0;
-  for (uint32_t base = e0; base < e1; base += blockDim.x) {
-    const uint32_t e = base + threadIdx.x;
-    const uint32_t v = e < e1 ? out.member_prefix[e] : 0u;
-    uint32_t inc = v;
-#pragma unroll
-    for (int d = 1; d < 32; d <<= 1) {
-      const uint32_t t = __shfl_up_sync(0xffffffffu, inc, d);
-      if (lane >= d) inc += t;
+  const double wtot = star_totals(e0, e1, entry_base, sc, M, s, red, redj, out);
+  const bool empty = !(wtot > 0.0);
+
+  // ---- merge the private copies (warp order), normalise; bins outside the range are 0 -----
+  const double inv = empty ? 0.0 : 1.0 / wtot;
+  for (int kq = warp; kq < nq; kq += NW) {
+    const int b0 = prm.bin_off[kq];
+    const int nbk = prm.bin_off[kq + 1] - b0;
+    const int mn = wmin[kq];
+    const int width = wmax[kq] >= mn ? wmax[kq] - mn + 1 : 0;
+    const double* src = hist + lcol[(kq & ~31) + plane[kq]];
+    double* row = out.pdf1d + s * tb + b0;
+    const bool from_bins = prm.q_const && prm.q_const[kq];
+    double eq = 0.0;
+    for (int b = lane; b < nbk; b += 32) {
+      double v = 0.0;
+      if (b >= mn && b < mn + width)
+        for (int w = 0; w < nwe; ++w) v += src[w * copy + b * 16];
+      row[b] = v * inv;
+      if (from_bins) eq += v * prm.bin_q[b0 + b];
     }
-    __syncthreads();
-    if (lane == 31) sscan[warp] = inc;
-    __syncthreads();
-    uint32_t woff = 0, tot = 0;
-    for (int w = 0; w < nw; ++w) {
-      if (w < warp) woff += sscan[w];
-      tot += sscan[w];
-    }
-    if (e < e1) out.member_prefix[e] = carry + woff + inc - v;
-    carry += tot;
+    if (from_bins)
+      store_bin_expectation(eq, wtot, empty, prm.q_lin[2 * kq], out.exp_vals + s * nq + kq, lane);
   }
-  if (threadIdx.x == 0) out.n_sparse[s] = carry;
+  __syncthreads();  // histograms are consumed: their memory becomes the percentile scratch
+  star_percentiles_and_prefix(prm, s, e0, e1, p0, p1, p2, hist, sscan, out);
 }
 
 }  // namespace bf
@@ -449,6 +754,9 @@ extern "C" int bf_exact_accumulate(const bf_exact_grid* grid, const bf_param_tab
                                      cudaSharedmemCarveoutMaxShared));
     BF_CUDA_TRY(cudaFuncSetAttribute(hist_kernel, cudaFuncAttributePreferredSharedMemoryCarveout,
                                      cudaSharedmemCarveoutMaxShared));
+    BF_CUDA_TRY(cudaFuncSetAttribute(hist_window_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, optin));
+    BF_CUDA_TRY(cudaFuncSetAttribute(hist_window_kernel, cudaFuncAttributePreferredSharedMemoryCarveout,
+                                     cudaSharedmemCarveoutMaxShared));
     BF_CUDA_TRY(cudaDeviceGetAttribute(&sm_count[dev], cudaDevAttrMultiProcessorCount, dev));
     smem_limit[dev] = optin;
   }
@@ -483,7 +791,25 @@ extern "C" int bf_exact_accumulate(const bf_exact_grid* grid, const bf_param_tab
               params->max_bins, params->n_q, smem, budget);
     return BF_ERR_TOO_LARGE;
   }
-  {
+  // wide bin tables leave the full-width layout few warps: use the windowed kernel there
+  // (BF_HIST=full|window overrides the choice, for measurements and tests)
+  const char* hist_env = getenv("BF_HIST");
+  const size_t wbytes_total = budget - 16384;  // leave room for resident exp_kernel blocks
+  const int hist_doubles = static_cast<int>(
+      (wbytes_total - WindowSmem::bytes(0, rounds)) / sizeof(double)) & ~1;
+  // worst case of one private copy: every range as wide as the widest bin table
+  const bool window_fits = hist_doubles >= 32 * params->max_bins * rounds &&
+                           hist_doubles >= kWindowWarps * kMaxBinsPerParam;
+  bool use_window = window_fits && nw < 8;
+  if (hist_env && hist_env[0] == 'f') use_window = false;
+  if (hist_env && hist_env[0] == 'w') use_window = window_fits;
+  if (use_window) {
+    hist_window_kernel<<<static_cast<unsigned>(n_stars), kWindowWarps * 32,
+                         WindowSmem::bytes(hist_doubles, rounds), st>>>(
+        *params, rounds, hist_doubles, pmax, offsets, list, star_order, star_begin, entry_base,
+        *scratch, percentiles_host[0], percentiles_host[1], percentiles_host[2], *out);
+    BF_CHECK_LAUNCH("hist_window_kernel");
+  } else {
     hist_kernel<<<static_cast<unsigned>(n_stars), nw * 32, smem, st>>>(
         *params, rounds, pmax, offsets, list, star_order, star_begin, entry_base, *scratch,
         percentiles_host[0], percentiles_host[1], percentiles_host[2], *out);
@@ -515,8 +841,9 @@ extern "C" int bf_exact_accumulate(const bf_exact_grid* grid, const bf_param_tab
     cudaEventElapsedTime(&x, tev[3], tev[4]);
     cudaEventElapsedTime(&tot, tev[0], tev[4]);
     fprintf(stderr, "[bf timing] stars=%lld entries=%lld weights=%.2f ms hist=%.2f ms exp=%.2f ms "
-            "(exp end - start of call = %.2f ms, hist warps=%d)\n",
-            static_cast<long long>(n_stars), static_cast<long long>(n_entries), w, h, x, tot, nw);
+            "(exp end - start of call = %.2f ms, hist warps=%d%s)\n",
+            static_cast<long long>(n_stars), static_cast<long long>(n_entries), w, h, x, tot,
+            use_window ? kWindowWarps : nw, use_window ? " windowed" : "");
     for (auto& e : tev) cudaEventDestroy(e);
   }
   return BF_OK;

@@ -107,6 +107,7 @@ class FitEngine:
             self.d_bin_tab, self.d_q_tab = up(s.bin_tab), up(s.q_tab)
             self.d_bin_off, self.d_bin_val = up(s.bin_off), up(s.bin_val)
             self.d_q_lin = up(s.q_lin)
+            self.d_q_const, self.d_bin_q = up(s.q_const), up(s.bin_q)
             self.d_inv_scale = up((1.0 / s.band_scale).astype(np.float64))
             if s.pair_bin is not None:
                 self.d_pair_bin, self.d_pair_off = up(s.pair_bin), up(s.pair_off)
@@ -117,8 +118,8 @@ class FitEngine:
                               self.d_cov_off.data_ptr() if self.d_cov_off is not None else None)
         self.params = ParamTables(s.n_q, s.total_bins, s.max_bins, self.d_bin_tab.data_ptr(),
                                   self.d_q_tab.data_ptr(), self.d_q_lin.data_ptr(),
-                                  self.d_bin_off.data_ptr(),
-                                  self.d_bin_val.data_ptr())
+                                  self.d_bin_off.data_ptr(), self.d_bin_val.data_ptr(),
+                                  self.d_q_const.data_ptr(), self.d_bin_q.data_ptr())
         per_star = s.n_groups * 4
         mb = max(STAR_BLOCK, (gmin_budget_bytes // per_star) // STAR_BLOCK * STAR_BLOCK)
         mb = min(mb, ((2**31 - 1) // max(s.n_groups, 1)) // STAR_BLOCK * STAR_BLOCK, 32768 * STAR_BLOCK)

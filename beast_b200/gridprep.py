@@ -292,6 +292,11 @@ class FitSetup:
         # range: q = q_lin[k,0] + q_lin[k,1] * fix, |rounding| <= range * 2^-33
         qtab = np.zeros((nq, nmp), dtype=np.int32)
         self.q_lin = np.zeros((nq, 2), dtype=np.float64)
+        # parameters whose bins each hold a single value (grid axes in unique-value bins): the
+        # expectation sum regroups by bin, sum_m w_m q_m = sum_b (sum_{m in b} w_m) q_b, so it is
+        # taken from the histogram and the per-model table is not read for them
+        self.q_const = np.zeros(nq, dtype=np.uint8)
+        self.bin_q = np.zeros(self.total_bins, dtype=np.float64)
         for k in range(nq):
             btab[k, :nm] = self.bins[k].bin_num[g0]
             col = self.qcols[k][g0]
@@ -300,6 +305,13 @@ class FitSetup:
             self.q_lin[k] = (0.5 * (lo + hi), scale)
             if scale > 0:
                 qtab[k, :nm] = np.rint((col - self.q_lin[k, 0]) / scale).astype(np.int64).astype(np.int32)
+            rep = np.zeros(self.bins[k].nbins, dtype=np.float64)
+            rep[btab[k, :nm]] = col
+            if np.array_equal(rep[btab[k, :nm]], col):
+                self.q_const[k] = 1
+                occupied = np.zeros(self.bins[k].nbins, dtype=bool)
+                occupied[btab[k, :nm]] = True
+                self.bin_q[self.bin_off[k]:self.bin_off[k + 1]] = np.where(occupied, rep - self.q_lin[k, 0], 0.0)
         self.bin_tab = np.ascontiguousarray(btab.reshape(nq, nch, CHUNK).transpose(1, 0, 2))
         self.q_tab = np.ascontiguousarray(qtab.reshape(nq, nch, CHUNK).transpose(1, 0, 2))
         if self.pairs:

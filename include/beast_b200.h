@@ -176,6 +176,13 @@ int bf_exact_max(const bf_exact_grid* grid, int64_t n_stars, int64_t ld_star,
  *   q_lin   [n_q][2] double              offset and scale of that encoding
  *   bin_off [n_q+1] int32                start of parameter k's bins in a star's pdf row
  *   bin_val [bin_off[n_q]] double        bin centres (pdf1d.bin_vals)
+ *   q_const [n_q] uint8, may be NULL     1: all models of a bin of parameter k share one value
+ *                                        (grid axes, unique-value bins).  Its expectation is then
+ *                                        q_lin[2k] + sum_b pdf_b * bin_q_b, taken from the
+ *                                        histogram, and q_tab is not read for it (the same
+ *                                        sum, regrouped by bin)
+ *   bin_q   [bin_off[n_q]] double        that shared value minus q_lin[2k], per bin (read
+ *                                        where q_const is 1)
  * ------------------------------------------------------------------------- */
 typedef struct {
   int n_q;
@@ -186,6 +193,8 @@ typedef struct {
   const double* q_lin;
   const int32_t* bin_off;
   const double* bin_val;
+  const uint8_t* q_const;
+  const double* bin_q;
 } bf_param_tables;
 
 typedef struct {

@@ -102,3 +102,23 @@ def test_numpy_subsample_follows_reference_stream():
         rindx = np.random.choice(indx, size=npts, replace=False) if npts < len(indx) else indx
         sa, sb = sub.sparse_off[e], sub.sparse_off[e + 1]
         np.testing.assert_array_equal(sub.sparse_j[sa:sb], full.sparse_j[fa:fb][rindx])
+
+
+@pytest.mark.parametrize("layout", ["full", "window"])
+def test_histogram_layouts_agree_with_the_oracle(layout, monkeypatch):
+    """200-bin tables: the full-width histogram kernel and the windowed kernel both give the
+    oracle's pdfs, percentiles and expectations (BF_HIST is read at every call of
+    bf_exact_accumulate; the golden cases run whichever kernel the bin tables select)."""
+    from beast_b200 import synth
+    from oracle import fit_oracle as fo
+
+    monkeypatch.setenv("BF_HIST", layout)
+    g, nz, obs = synth.make_config("C1", nstars=40, seed=5)
+    keys = fo.default_keys(g)
+    ost = fo.OracleSetup(g, nz, keys, max_nbins=200)
+    want = fo.fit_all(obs.fluxes, ost, threshold=-10.0, fast=True)
+    args = dict(keys=keys, max_nbins=200, pdf2d_param_list=None, do_not_normalize=False)
+    setup, eng = _engine(g, nz, args)
+    assert setup.q_const.any() and not setup.q_const.all()  # both expectation paths are used
+    res = eng.fit(obs.fluxes, threshold=-10.0, sparse="all")
+    util.compare_to_reference(setup, res, want)
