@@ -514,15 +514,33 @@ __device__ __forceinline__ void accumulate_columns(const bf_param_tables& prm, c
       for (int c = 0; c < BF_GROUP / BF_CHUNK; ++c) {
         const uint32_t byte = ((c < 4 ? cur.m0 : cur.m1) >> (8 * (c & 3))) & 0xffu;
         if (byte == 0) continue;
+        // All 8 models of the chunk are added, four at a time: non-members carry weight 0 and
+        // their bins lie inside the ranges too (pass 1 looked at whole chunks).  The four
+        // loads are issued together; a model that shares its bin with earlier ones of the
+        // four takes their weights along (s_j below, computed while the loads are in flight),
+        // so the stores, issued in order, leave the complete sum whichever comes last.
 #pragma unroll
-        for (int i = 0; i < BF_CHUNK; ++i) {
-          if ((byte >> i) & 1u) {  // warp-uniform
-            const uint32_t b = static_cast<uint32_t>((cur.bits[c] >> (8 * i)) & 0xffull);
-            const uint32_t addr = col_s + b * (STRIDE * 8);
-            double h;
-            asm volatile("ld.shared.f64 %0, [%1];" : "=d"(h) : "r"(addr));
-            h += wbuf[c * BF_CHUNK + i];
-            asm volatile("st.shared.f64 [%0], %1;" ::"r"(addr), "d"(h));
+        for (int i0 = 0; i0 < BF_CHUNK; i0 += 4) {
+          uint32_t a[4];
+          double h[4], sw[4];
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            const uint32_t b = static_cast<uint32_t>((cur.bits[c] >> (8 * (i0 + j))) & 0xffull);
+            a[j] = col_s + b * (STRIDE * 8);
+          }
+#pragma unroll
+          for (int j = 0; j < 4; ++j) asm volatile("ld.shared.f64 %0, [%1];" : "=d"(h[j]) : "r"(a[j]));
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            sw[j] = wbuf[c * BF_CHUNK + i0 + j];
+#pragma unroll
+            for (int i = 0; i < j; ++i)
+              if (a[i] == a[j]) sw[j] += wbuf[c * BF_CHUNK + i0 + i];
+          }
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            h[j] += sw[j];
+            asm volatile("st.shared.f64 [%0], %1;" ::"r"(a[j]), "d"(h[j]));
           }
         }
       }
@@ -771,6 +789,7 @@ extern "C" int bf_exact_accumulate(const bf_exact_grid* grid, const bf_param_tab
   }
   if (timing) cudaEventRecord(tev[1], st);
   const int rounds = (params->n_q + 31) / 32;
+  if (timing && getenv("BF_TIMING")[0] == '2') aux_stream = nullptr;  // serial: each kernel alone
   cudaStream_t sx = aux_stream ? static_cast<cudaStream_t>(aux_stream) : st;
   static cudaEvent_t ev_weights[64] = {}, ev_exp[64] = {};
   if (aux_stream) {  // the weights are ready at this point of `stream`

@@ -336,12 +336,16 @@ class FitEngine:
             # (running the weights kernel of the next range beside the histogram kernel of this one
             # was measured and is slower: the latency-bound histogram kernel stalls once the
             # memory-bound kernels saturate L2 -- see DESIGN.md)
+            n_listed = off_star[1:] - off_star[:-1]
             for a0, b0 in cuts:
                 base, cnt = int(off_host[a0]), int(off_host[b0] - off_host[a0])
+                # one block per star in the histogram kernel: longest lists first, so that the
+                # last blocks of the launch are short ones
+                order = torch.argsort(n_listed[a0:b0], descending=True, stable=True).to(torch.int32)
                 with self._timed("accumulate"):
                     _cabi.call("bf_exact_accumulate", C.byref(self.grid), C.byref(self.params),
                                a0, b0 - a0, _ptr(d_flux), _ptr(pmax), float(threshold),
-                               _ptr(offsets), _ptr(lst), _ptr(entry_star), None, base, cnt,
+                               _ptr(offsets), _ptr(lst), _ptr(entry_star), _ptr(order), base, cnt,
                                pct, C.byref(scr), C.byref(outs), st,
                                C.c_void_p(self._aux_stream.cuda_stream))
                 self.launches += 3
