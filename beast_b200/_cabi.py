@@ -62,6 +62,7 @@ class AccumScratch(C.Structure):
         ("part_wsum", c_void_p),
         ("part_chi2", c_void_p),
         ("part_chi2_j", c_void_p),
+        ("star_flags", c_void_p),
     ]
 
 

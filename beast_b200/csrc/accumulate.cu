@@ -114,13 +114,14 @@ exp_kernel(bf_param_tables prm, int rounds, const uint32_t* __restrict__ offsets
            const uint32_t* __restrict__ list, const uint32_t* __restrict__ member_mask,
            int64_t star_begin, int64_t n_stars, int64_t entry_base,
            const double* __restrict__ weights, const double* __restrict__ part_wsum,
-           double* __restrict__ exp_vals) {
+           const int32_t* __restrict__ star_flags, double* __restrict__ exp_vals) {
   extern __shared__ __align__(16) double exp_smem[];  // [kExpWarps][nq] + [kExpWarps]
   double* red = exp_smem;
   double* wred = exp_smem + kExpWarps * prm.n_q;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int nq = prm.n_q;
   for (int64_t sb = blockIdx.x; sb < n_stars; sb += gridDim.x) {
+  if (star_flags && star_flags[sb]) continue;  // done by the histogram kernel
   const int64_t s = star_begin + sb;
   const uint32_t e0 = offsets[s * BF_SELECT_SPLIT];
   const uint32_t e1 = offsets[(s + 1) * BF_SELECT_SPLIT];
@@ -459,11 +460,12 @@ hist_kernel(bf_param_tables prm, int rounds, const double* __restrict__ pmax,
 // tables wmin, wmax, plane, lparam, lcol [rounds*32] | tmpw [32] | misc [4].
 // ---------------------------------------------------------------------------------------
 constexpr int kWindowWarps = 16;
+constexpr int kMinExpWarps = 6;  // idle warps from which a block does the expectation sums itself
 
 struct WindowSmem {
   static __host__ __device__ size_t bytes(int hist_doubles, int rounds) {
-    return (static_cast<size_t>(hist_doubles) + kWindowWarps * kStageDoubles + 3 * kWindowWarps + 8) *
-               sizeof(double) +
+    return (static_cast<size_t>(hist_doubles) + kWindowWarps * kStageDoubles + 3 * kWindowWarps + 8 +
+            static_cast<size_t>(kWindowWarps) * rounds * 32) * sizeof(double) +
            (5 * static_cast<size_t>(rounds) * 32 + 32 + 4) * sizeof(int);
   }
 };
@@ -550,6 +552,78 @@ __device__ __forceinline__ void accumulate_columns(const bf_param_tables& prm, c
   }
 }
 
+// Expectation sums of one warp inside hist_window_kernel: sum_m w_m * fix_m for every
+// parameter that is not taken from the histogram (fit.py:743), lane <-> parameter, over the
+// groups e, e + step, ... of the star.  The rows of half a group are requested together.
+__device__ __forceinline__ void expectation_rows(const bf_param_tables& prm, int rounds,
+                                                 const double* __restrict__ weights,
+                                                 int64_t entry_base, const uint32_t* __restrict__ list,
+                                                 const uint32_t* __restrict__ member_mask,
+                                                 uint32_t e_first, uint32_t e1, uint32_t step,
+                                                 int lane, double* epart_w) {
+  const int nq = prm.n_q;
+  for (int r = 0; r < rounds; ++r) {
+    const int k = r * 32 + lane;
+    const bool live = k < nq && !(prm.q_const && prm.q_const[k]);
+    if (!__any_sync(0xffffffffu, live)) continue;
+    const int kk = live ? k : 0;
+    double eacc = 0.0;
+    uint32_t e = e_first;
+    uint32_t g1 = 0, a1 = 0, b1 = 0;
+    if (e < e1) {
+      g1 = list[e];
+      a1 = member_mask[static_cast<size_t>(e) * kWordsPerGroup];
+      b1 = member_mask[static_cast<size_t>(e) * kWordsPerGroup + 1];
+    }
+    while (e < e1) {
+      const uint32_t g = g1, m0 = a1, m1 = b1;
+      const uint32_t en = e + step;
+      if (en < e1) {
+        g1 = list[en];
+        a1 = member_mask[static_cast<size_t>(en) * kWordsPerGroup];
+        b1 = member_mask[static_cast<size_t>(en) * kWordsPerGroup + 1];
+      }
+      const double* wp = weights + (static_cast<int64_t>(e) - entry_base) * BF_GROUP;
+      const int32_t* qbase =
+          prm.q_tab + (static_cast<size_t>(g) * (BF_GROUP / BF_CHUNK) * nq + kk) * BF_CHUNK;
+#pragma unroll
+      for (int h = 0; h < 2; ++h) {
+        const uint32_t mw = h ? m1 : m0;
+        if (mw == 0) continue;  // warp-uniform
+        int4 qa[4], qb[4];
+#pragma unroll
+        for (int c = 0; c < 4; ++c) {
+          qa[c] = make_int4(0, 0, 0, 0);
+          qb[c] = make_int4(0, 0, 0, 0);
+          if (((mw >> (8 * c)) & 0xffu) != 0 && live) {  // idle lanes touch no row
+            const int4* qp = reinterpret_cast<const int4*>(
+                qbase + static_cast<size_t>(h * 4 + c) * nq * BF_CHUNK);
+            qa[c] = __ldg(qp);
+            qb[c] = __ldg(qp + 1);
+          }
+        }
+#pragma unroll
+        for (int c = 0; c < 4; ++c) {
+          if (((mw >> (8 * c)) & 0xffu) == 0) continue;
+          const double2* wq = reinterpret_cast<const double2*>(wp + (h * 4 + c) * BF_CHUNK);
+          const double2 w01 = __ldg(wq), w23 = __ldg(wq + 1), w45 = __ldg(wq + 2), w67 = __ldg(wq + 3);
+          // non-members carry weight 0
+          eacc += w01.x * static_cast<double>(qa[c].x);
+          eacc += w01.y * static_cast<double>(qa[c].y);
+          eacc += w23.x * static_cast<double>(qa[c].z);
+          eacc += w23.y * static_cast<double>(qa[c].w);
+          eacc += w45.x * static_cast<double>(qb[c].x);
+          eacc += w45.y * static_cast<double>(qb[c].y);
+          eacc += w67.x * static_cast<double>(qb[c].z);
+          eacc += w67.y * static_cast<double>(qb[c].w);
+        }
+      }
+      e = en;
+    }
+    if (live) epart_w[k] = eacc;
+  }
+}
+
 __global__ void __launch_bounds__(kWindowWarps * 32, 1)
 hist_window_kernel(bf_param_tables prm, int rounds, int hist_doubles,
                    const double* __restrict__ pmax, const uint32_t* __restrict__ offsets,
@@ -567,7 +641,8 @@ hist_window_kernel(bf_param_tables prm, int rounds, int hist_doubles,
   double* red = wbuf_all + NW * kStageDoubles;
   long long* redj = reinterpret_cast<long long*>(red + 2 * NW);
   uint32_t* sscan = reinterpret_cast<uint32_t*>(redj + NW);
-  int* wmin = reinterpret_cast<int*>(red + 3 * NW + 8);
+  double* epart = red + 3 * NW + 8;  // [NW][npad] expectation sums of the warps that do them
+  int* wmin = reinterpret_cast<int*>(epart + NW * npad);
   int* wmax = wmin + npad;
   int* plane = wmax + npad;    // lane that works on parameter k (within its round of 32)
   int* lparam = plane + npad;  // parameter of a lane, -1: none
@@ -676,6 +751,11 @@ hist_window_kernel(bf_param_tables prm, int rounds, int hist_doubles,
   }
   __syncthreads();
   const int copy = misc[0], nwe = misc[1];
+  // A star with broad ranges leaves warps without a private copy: from kMinExpWarps on they
+  // take the star's expectation sums, and the expectation kernel skips the star.
+  const int n_exp = NW - nwe;
+  const bool exp_here = sc.star_flags != nullptr && n_exp >= kMinExpWarps;
+  if (threadIdx.x == 0 && sc.star_flags) sc.star_flags[s - star_begin] = exp_here ? 1 : 0;
   for (int i = threadIdx.x; i < nwe * copy; i += blockDim.x) hist[i] = 0.0;
   __syncthreads();
 
@@ -689,10 +769,23 @@ hist_window_kernel(bf_param_tables prm, int rounds, int hist_doubles,
                              live ? k : 0, live ? 0xffffffffu : 0u, lane,
                              hist + warp * copy + lcol[r * 32 + lane], wbuf);
     }
+  } else if (exp_here) {
+    expectation_rows(prm, rounds, sc.weights, entry_base, list, out.member_mask,
+                     e0 + (warp - nwe), e1, n_exp, lane, epart + (warp - nwe) * npad);
   }
 
   const double wtot = star_totals(e0, e1, entry_base, sc, M, s, red, redj, out);
   const bool empty = !(wtot > 0.0);
+  if (exp_here) {
+    // q = q_lin[2k] + q_lin[2k+1] * fix  ->  Exp = offset + scale * sum(w fix) / sum(w)
+    for (int k = threadIdx.x; k < nq; k += blockDim.x) {
+      if (prm.q_const && prm.q_const[k]) continue;  // written with the merged histogram below
+      double e = 0.0;
+      for (int w = 0; w < n_exp; ++w) e += epart[w * npad + k];
+      out.exp_vals[s * nq + k] = empty ? __longlong_as_double(0x7ff8000000000000LL)
+                                       : prm.q_lin[2 * k] + prm.q_lin[2 * k + 1] * (e / wtot);
+    }
+  }
 
   // ---- merge the private copies (warp order), normalise; bins outside the range are 0 -----
   const double inv = empty ? 0.0 : 1.0 / wtot;
@@ -789,16 +882,6 @@ extern "C" int bf_exact_accumulate(const bf_exact_grid* grid, const bf_param_tab
   }
   if (timing) cudaEventRecord(tev[1], st);
   const int rounds = (params->n_q + 31) / 32;
-  if (timing && getenv("BF_TIMING")[0] == '2') aux_stream = nullptr;  // serial: each kernel alone
-  cudaStream_t sx = aux_stream ? static_cast<cudaStream_t>(aux_stream) : st;
-  static cudaEvent_t ev_weights[64] = {}, ev_exp[64] = {};
-  if (aux_stream) {  // the weights are ready at this point of `stream`
-    if (!ev_weights[dev]) {
-      BF_CUDA_TRY(cudaEventCreateWithFlags(&ev_weights[dev], cudaEventDisableTiming));
-      BF_CUDA_TRY(cudaEventCreateWithFlags(&ev_exp[dev], cudaEventDisableTiming));
-    }
-    BF_CUDA_TRY(cudaEventRecord(ev_weights[dev], st));
-  }
   // widest block whose private histograms fit; two resident blocks per SM when they are small
   const size_t budget = static_cast<size_t>(smem_limit[dev]);
   int nw = 16;
@@ -813,7 +896,7 @@ extern "C" int bf_exact_accumulate(const bf_exact_grid* grid, const bf_param_tab
   // wide bin tables leave the full-width layout few warps: use the windowed kernel there
   // (BF_HIST=full|window overrides the choice, for measurements and tests)
   const char* hist_env = getenv("BF_HIST");
-  const size_t wbytes_total = budget - 16384;  // leave room for resident exp_kernel blocks
+  const size_t wbytes_total = budget - 1024;
   const int hist_doubles = static_cast<int>(
       (wbytes_total - WindowSmem::bytes(0, rounds)) / sizeof(double)) & ~1;
   // worst case of one private copy: every range as wide as the widest bin table
@@ -822,6 +905,18 @@ extern "C" int bf_exact_accumulate(const bf_exact_grid* grid, const bf_param_tab
   bool use_window = window_fits && nw < 8;
   if (hist_env && hist_env[0] == 'f') use_window = false;
   if (hist_env && hist_env[0] == 'w') use_window = window_fits;
+  if (timing && getenv("BF_TIMING")[0] == '2') aux_stream = nullptr;  // serial: each kernel alone
+  // the windowed kernel tells the expectation kernel which stars it has done: same stream
+  if (use_window) aux_stream = nullptr;
+  cudaStream_t sx = aux_stream ? static_cast<cudaStream_t>(aux_stream) : st;
+  static cudaEvent_t ev_weights[64] = {}, ev_exp[64] = {};
+  if (aux_stream) {  // the weights are ready at this point of `stream`
+    if (!ev_weights[dev]) {
+      BF_CUDA_TRY(cudaEventCreateWithFlags(&ev_weights[dev], cudaEventDisableTiming));
+      BF_CUDA_TRY(cudaEventCreateWithFlags(&ev_exp[dev], cudaEventDisableTiming));
+    }
+    BF_CUDA_TRY(cudaEventRecord(ev_weights[dev], st));
+  }
   if (use_window) {
     hist_window_kernel<<<static_cast<unsigned>(n_stars), kWindowWarps * 32,
                          WindowSmem::bytes(hist_doubles, rounds), st>>>(
@@ -845,7 +940,8 @@ extern "C" int bf_exact_accumulate(const bf_exact_grid* grid, const bf_param_tab
     exp_kernel<<<static_cast<unsigned>(n_stars < cap ? n_stars : cap), kExpWarps * 32,
                  (kExpWarps * params->n_q + kExpWarps) * sizeof(double), sx>>>(
         *params, rounds, offsets, list, out->member_mask, star_begin, n_stars, entry_base,
-        scratch->weights, scratch->part_wsum, out->exp_vals);
+        scratch->weights, scratch->part_wsum, use_window ? scratch->star_flags : nullptr,
+        out->exp_vals);
     BF_CHECK_LAUNCH("exp_kernel");
   }
   if (aux_stream) BF_CUDA_TRY(cudaEventRecord(ev_exp[dev], sx));

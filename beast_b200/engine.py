@@ -328,7 +328,9 @@ class FitEngine:
             p_w = torch.empty(max(nmax, 1), dtype=torch.float64, device=dev)
             p_c = torch.empty(max(nmax, 1), dtype=torch.float64, device=dev)
             p_j = torch.empty(max(nmax, 1), dtype=torch.int64, device=dev)
-            scr = AccumScratch(w_scr.data_ptr(), p_w.data_ptr(), p_c.data_ptr(), p_j.data_ptr())
+            flags = torch.empty(max(b - a for a, b in cuts), dtype=torch.int32, device=dev)
+            scr = AccumScratch(w_scr.data_ptr(), p_w.data_ptr(), p_c.data_ptr(), p_j.data_ptr(),
+                               flags.data_ptr())
             outs = StarOutputs(o["total_log_norm"].data_ptr(), o["chi2min"].data_ptr(),
                                o["chi2min_j"].data_ptr(), o["n_sparse"].data_ptr(),
                                o["exp_vals"].data_ptr(), o["pdf1d"].data_ptr(),

@@ -216,6 +216,9 @@ typedef struct {
   double* part_wsum;    /* [n_entries] sum of the group's weights                        */
   double* part_chi2;    /* [n_entries] smallest member chi2 of the group                 */
   int64_t* part_chi2_j; /* [n_entries] its model index (-1: no member)                   */
+  int32_t* star_flags;  /* [n_stars] or NULL.  Set by the histogram kernel: 1 = it has also
+                           written this star's expectations (warps without a private
+                           histogram did the sums), so the expectation kernel skips the star */
 } bf_accum_scratch;
 
 /* Sparse pass: exact sparse set, weights, normalisation, chi2min, expectations, 1D PDFs
