@@ -552,6 +552,26 @@ __device__ __forceinline__ void accumulate_columns(const bf_param_tables& prm, c
   }
 }
 
+// bin rows of a listed group for pass 1 of hist_window_kernel (no weights)
+struct BinRows {
+  uint32_t m0, m1;
+  uint2 b[BF_GROUP / BF_CHUNK];
+};
+
+__device__ __forceinline__ void load_bin_rows(const bf_param_tables& prm, uint32_t g, uint32_t m0,
+                                              uint32_t m1, int k, BinRows& r) {
+  r.m0 = m0;
+  r.m1 = m1;
+  const uint8_t* base = prm.bin_tab +
+      (static_cast<size_t>(g) * (BF_GROUP / BF_CHUNK) * prm.n_q + k) * BF_CHUNK;
+  const uint32_t stride = static_cast<uint32_t>(prm.n_q) * BF_CHUNK;
+#pragma unroll
+  for (int c = 0; c < BF_GROUP / BF_CHUNK; ++c) {
+    const uint32_t byte = ((c < 4 ? m0 : m1) >> (8 * (c & 3))) & 0xffu;
+    if (byte != 0) r.b[c] = __ldg(reinterpret_cast<const uint2*>(base + c * stride));
+  }
+}
+
 // Expectation sums of one warp inside hist_window_kernel: sum_m w_m * fix_m for every
 // parameter that is not taken from the histogram (fit.py:743), lane <-> parameter, over the
 // groups e, e + step, ... of the star.  The rows of half a group are requested together.
@@ -661,7 +681,6 @@ hist_window_kernel(bf_param_tables prm, int rounds, int hist_doubles,
   const double M = pmax[s];
   const uint32_t e0 = offsets[s * BF_SELECT_SPLIT];
   const uint32_t e1 = offsets[(s + 1) * BF_SELECT_SPLIT];
-  const uint32_t stride = static_cast<uint32_t>(nq) * BF_CHUNK;
 
   // ---- pass 1: occupied bin range of every parameter ------------------------------------
   for (int r = 0; r < rounds; ++r) {
@@ -670,35 +689,42 @@ hist_window_kernel(bf_param_tables prm, int rounds, int hist_doubles,
     const int kk = live ? k : 0;
     uint32_t mn2 = 0x00ff00ffu, mx2 = 0;
     uint32_t e = e0 + warp;
-    uint32_t g1 = 0, a1 = 0, b1 = 0;
+    // same three-deep pipeline as the accumulation: list entry two groups ahead, bin rows one
+    BinRows cur, nxt;
+    uint32_t g2 = 0, a2 = 0, b2 = 0;
+    nxt.m0 = nxt.m1 = 0;
     if (e < e1) {
-      g1 = list[e];
-      a1 = out.member_mask[static_cast<size_t>(e) * kWordsPerGroup];
-      b1 = out.member_mask[static_cast<size_t>(e) * kWordsPerGroup + 1];
+      load_bin_rows(prm, list[e], out.member_mask[static_cast<size_t>(e) * kWordsPerGroup],
+                    out.member_mask[static_cast<size_t>(e) * kWordsPerGroup + 1], kk, nxt);
+      if (e + NW < e1) {
+        g2 = list[e + NW];
+        a2 = out.member_mask[static_cast<size_t>(e + NW) * kWordsPerGroup];
+        b2 = out.member_mask[static_cast<size_t>(e + NW) * kWordsPerGroup + 1];
+      }
     }
     while (e < e1) {
-      const uint32_t g = g1, m0 = a1, m1 = b1;
+      cur = nxt;
       const uint32_t en = e + NW;
       if (en < e1) {
-        g1 = list[en];
-        a1 = out.member_mask[static_cast<size_t>(en) * kWordsPerGroup];
-        b1 = out.member_mask[static_cast<size_t>(en) * kWordsPerGroup + 1];
-      }
-      if ((m0 | m1) != 0) {
-        const uint8_t* base = prm.bin_tab +
-            (static_cast<size_t>(g) * (BF_GROUP / BF_CHUNK) * nq + kk) * BF_CHUNK;
-#pragma unroll
-        for (int c = 0; c < BF_GROUP / BF_CHUNK; ++c) {
-          const uint32_t byte = ((c < 4 ? m0 : m1) >> (8 * (c & 3))) & 0xffu;
-          if (byte == 0) continue;
-          const uint2 bb = __ldg(reinterpret_cast<const uint2*>(base + c * stride));
-          // every model of a chunk with a member counts (a superset of the members' range
-          // is all that is needed): bytes -> two 16-bit lanes, native 3-input SIMD min/max
-          const uint32_t xe = __byte_perm(bb.x, 0, 0x4240), xo = __byte_perm(bb.x, 0, 0x4341);
-          const uint32_t ye = __byte_perm(bb.y, 0, 0x4240), yo = __byte_perm(bb.y, 0, 0x4341);
-          mn2 = __vimin3_u16x2(__vimin3_u16x2(mn2, xe, xo), ye, yo);
-          mx2 = __vimax3_u16x2(__vimax3_u16x2(mx2, xe, xo), ye, yo);
+        load_bin_rows(prm, g2, a2, b2, kk, nxt);
+        const uint32_t en2 = en + NW;
+        if (en2 < e1) {
+          g2 = list[en2];
+          a2 = out.member_mask[static_cast<size_t>(en2) * kWordsPerGroup];
+          b2 = out.member_mask[static_cast<size_t>(en2) * kWordsPerGroup + 1];
         }
+      }
+#pragma unroll
+      for (int c = 0; c < BF_GROUP / BF_CHUNK; ++c) {
+        const uint32_t byte = ((c < 4 ? cur.m0 : cur.m1) >> (8 * (c & 3))) & 0xffu;
+        if (byte == 0) continue;
+        // every model of a chunk with a member counts (a superset of the members' range
+        // is all that is needed): bytes -> two 16-bit lanes, native 3-input SIMD min/max
+        const uint2 bb = cur.b[c];
+        const uint32_t xe = __byte_perm(bb.x, 0, 0x4240), xo = __byte_perm(bb.x, 0, 0x4341);
+        const uint32_t ye = __byte_perm(bb.y, 0, 0x4240), yo = __byte_perm(bb.y, 0, 0x4341);
+        mn2 = __vimin3_u16x2(__vimin3_u16x2(mn2, xe, xo), ye, yo);
+        mx2 = __vimax3_u16x2(__vimax3_u16x2(mx2, xe, xo), ye, yo);
       }
       e = en;
     }
