@@ -225,16 +225,22 @@ typedef struct {
  * and p16/p50/p84 (fit.py:670-755) for stars [star_begin, star_begin + n_stars) of the
  * batch-wide arrays passed in.
  * Three launches: (1) one warp per listed group evaluates the exact lnP of its 64 models and
- * stores membership bits, weights and per-group partial sums; (2) one block per star sums
- * w*q into the expectations; (3) one block per star builds the histograms and percentiles.
+ * stores membership bits, weights and per-group partial sums; (2) one block per star builds the
+ * histograms and percentiles -- with full-width private histograms per warp, or, for wide bin
+ * tables (200 bins), with histograms sized by the star's occupied bin ranges, in which case
+ * warps left without a histogram also sum the star's expectations; (3) one block per star sums
+ * w*q into the expectations of the stars and parameters not yet done.  Results do not depend
+ * on which histogram kernel runs beyond the summation order (tests/test_gpu_fullsize.py).
  * entry_star : [list length] star index of every list position (from bf_select_fill).
- * star_order : optional [n_stars] int32 permutation; block i works on star star_order[i]
- *              (callers sort by arg-min group so that concurrent blocks share L2 lines).
+ * star_order : optional [n_stars] int32 permutation of 0..n_stars-1; block i of the histogram
+ *              kernel works on star star_begin + star_order[i] (callers put the stars with the
+ *              longest lists first, so that the last blocks of the launch are short).
  * entry_base / n_entries : list range of those stars,
  *              [offsets[star_begin*SPLIT], offsets[(star_begin+n_stars)*SPLIT]), covered by `scratch`.
  * percentiles_host : [3] host doubles in percent.
- * aux_stream : optional second stream; when given, the expectation kernel runs on it next to
- *              the histogram kernel (ordered by events; `stream` has joined it on return). */
+ * aux_stream : optional second stream; when given and the full-width histogram kernel is used,
+ *              the expectation kernel runs on it next to the histogram kernel (ordered by
+ *              events; `stream` has joined it on return). */
 int bf_exact_accumulate(const bf_exact_grid* grid, const bf_param_tables* params,
                         int64_t star_begin, int64_t n_stars, const double* flux64, const double* pmax,
                         double threshold, const uint32_t* offsets, const uint32_t* list,
