@@ -43,6 +43,29 @@ __device__ __forceinline__ void exact_lnp(const bf_exact_grid& g, const double* 
   lnp = __dadd_rn(__dsub_rn(-g.lnq[j], __dmul_rn(0.5, acc)), g.lnw[j]);
 }
 
+// Diagonal likelihood with the band count known at compile time: the loads of all bands are
+// independent of the arithmetic, so the compiler issues them together (same operation order as
+// exact_lnp, bit-identical results).
+template <int NB>
+__device__ __forceinline__ void exact_lnp_fixed(const bf_exact_grid& g, const double* sflux, int64_t j,
+                                                double& lnp, double& chi2) {
+  double m[NB], v[NB];
+#pragma unroll
+  for (int b = 0; b < NB; ++b) {
+    m[b] = __ldg(g.msb + static_cast<int64_t>(b) * g.ld_model + j);
+    v[b] = __ldg(g.ivar + static_cast<int64_t>(b) * g.ld_model + j);
+  }
+  const double lq = __ldg(g.lnq + j), lw = __ldg(g.lnw + j);
+  double acc = 0.0;
+#pragma unroll
+  for (int b = 0; b < NB; ++b) {
+    const double d = __dsub_rn(sflux[b], m[b]);
+    acc = __dadd_rn(acc, __dmul_rn(__dmul_rn(d, d), v[b]));
+  }
+  chi2 = acc;
+  lnp = __dadd_rn(__dsub_rn(-lq, __dmul_rn(0.5, acc)), lw);
+}
+
 __device__ __forceinline__ bool is_finite(double x) { return fabs(x) <= 1.7976931348623157e308; }
 
 }  // namespace bf
