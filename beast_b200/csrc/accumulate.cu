@@ -576,7 +576,7 @@ __device__ __forceinline__ void load_bin_rows(const bf_param_tables& prm, uint32
 
 // Expectation sums of one warp inside hist_window_kernel: sum_m w_m * fix_m for every
 // parameter that is not taken from the histogram (fit.py:743), lane <-> parameter, over the
-// groups e, e + step, ... of the star.  The rows of half a group are requested together.
+// groups e, e + step, ... of the star.  The rows of a group are requested together.
 __device__ __forceinline__ void expectation_rows(const bf_param_tables& prm, int rounds,
                                                  const double* __restrict__ weights,
                                                  int64_t entry_base, const uint32_t* __restrict__ list,
@@ -608,26 +608,23 @@ __device__ __forceinline__ void expectation_rows(const bf_param_tables& prm, int
       const double* wp = weights + (static_cast<int64_t>(e) - entry_base) * BF_GROUP;
       const int32_t* qbase =
           prm.q_tab + (static_cast<size_t>(g) * (BF_GROUP / BF_CHUNK) * nq + kk) * BF_CHUNK;
+      if ((m0 | m1) != 0) {  // warp-uniform
+        // the rows of all chunks with a member are requested before the first one is used
+        int4 qa[8], qb[8];
 #pragma unroll
-      for (int h = 0; h < 2; ++h) {
-        const uint32_t mw = h ? m1 : m0;
-        if (mw == 0) continue;  // warp-uniform
-        int4 qa[4], qb[4];
-#pragma unroll
-        for (int c = 0; c < 4; ++c) {
+        for (int c = 0; c < 8; ++c) {
           qa[c] = make_int4(0, 0, 0, 0);
           qb[c] = make_int4(0, 0, 0, 0);
-          if (((mw >> (8 * c)) & 0xffu) != 0 && live) {  // idle lanes touch no row
-            const int4* qp = reinterpret_cast<const int4*>(
-                qbase + static_cast<size_t>(h * 4 + c) * nq * BF_CHUNK);
+          if ((((c < 4 ? m0 : m1) >> (8 * (c & 3))) & 0xffu) != 0 && live) {  // idle lanes touch no row
+            const int4* qp = reinterpret_cast<const int4*>(qbase + static_cast<size_t>(c) * nq * BF_CHUNK);
             qa[c] = __ldg(qp);
             qb[c] = __ldg(qp + 1);
           }
         }
 #pragma unroll
-        for (int c = 0; c < 4; ++c) {
-          if (((mw >> (8 * c)) & 0xffu) == 0) continue;
-          const double2* wq = reinterpret_cast<const double2*>(wp + (h * 4 + c) * BF_CHUNK);
+        for (int c = 0; c < 8; ++c) {
+          if ((((c < 4 ? m0 : m1) >> (8 * (c & 3))) & 0xffu) == 0) continue;
+          const double2* wq = reinterpret_cast<const double2*>(wp + c * BF_CHUNK);
           const double2 w01 = __ldg(wq), w23 = __ldg(wq + 1), w45 = __ldg(wq + 2), w67 = __ldg(wq + 3);
           // non-members carry weight 0
           eacc += w01.x * static_cast<double>(qa[c].x);
