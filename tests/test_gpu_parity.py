@@ -122,3 +122,16 @@ def test_histogram_layouts_agree_with_the_oracle(layout, monkeypatch):
     assert setup.q_const.any() and not setup.q_const.all()  # both expectation paths are used
     res = eng.fit(obs.fluxes, threshold=-10.0, sparse="all")
     util.compare_to_reference(setup, res, want)
+
+
+def test_weights_kernel_instantiations_are_bit_identical(monkeypatch):
+    """the per-band-count weights kernel (all loads of a model in flight at once) performs the
+    same operations in the same order as the runtime-band-count one: every output bit agrees"""
+    g, nz, obs, args, ref = util.load_golden("small_thr10")
+    setup, eng = _engine(g, nz, args)
+    a = eng.fit(obs.fluxes, threshold=args["threshold"], sparse="all")
+    monkeypatch.setenv("BF_WEIGHTS_GENERIC", "1")
+    b = eng.fit(obs.fluxes, threshold=args["threshold"], sparse="all")
+    for name in ("Pmax", "Pmax_j", "total_log_norm", "chi2min", "chi2min_j", "n_sparse", "pdf1d",
+                 "exp_vals", "per_vals", "sparse_j", "sparse_lnp", "sparse_chi2"):
+        np.testing.assert_array_equal(getattr(a, name), getattr(b, name), err_msg=name)
