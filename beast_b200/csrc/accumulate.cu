@@ -468,7 +468,7 @@ struct WindowSmem {
   static __host__ __device__ size_t bytes(int hist_doubles, int rounds) {
     return (static_cast<size_t>(hist_doubles) + kWindowWarps * kStageDoubles + 3 * kWindowWarps + 8 +
             static_cast<size_t>(kWindowWarps) * rounds * 32) * sizeof(double) +
-           (5 * static_cast<size_t>(rounds) * 32 + 32 + 4) * sizeof(int);
+           (5 * static_cast<size_t>(rounds) * 32 + 32 + 16) * sizeof(int);
   }
 };
 
@@ -667,7 +667,8 @@ hist_window_kernel(bf_param_tables prm, int rounds, int hist_doubles,
   int* lparam = plane + npad;  // parameter of a lane, -1: none
   int* lcol = lparam + npad;   // a lane's column: offset of (absolute) bin 0 within a copy
   int* tmpw = lcol + npad;     // [32] range widths by lane
-  int* misc = tmpw + 32;       // [0] doubles per private copy, [1] warps that get one
+  int* misc = tmpw + 32;       // [0] doubles of one copy of every round, [1] copies per round,
+                               // [4+r] doubles of a copy of round r, [8+r] the same summed over earlier rounds
 
   const int64_t s =
       star_begin + (star_order ? star_order[blockIdx.x] : static_cast<int64_t>(blockIdx.x));
@@ -744,8 +745,10 @@ hist_window_kernel(bf_param_tables prm, int rounds, int hist_doubles,
   // accesses are conflict free whatever the bins are, and the copy holds
   // 16 * max_j (width_j + width_{31-j}) doubles -- close to the sum of the widths.
   // Lanes without a parameter get a one-bin range of their own.
+  // With more than 32 parameters every round of 32 gets its own copies and its own warps
+  // (n per round), so that a warp walks the star's groups once.
   if (warp == 0) {
-    int rows = 0;
+    int total = 0;
     for (int r = 0; r < rounds; ++r) {
       const int k = r * 32 + lane;
       const bool occupied = k < nq && wmin[k] <= wmax[k];
@@ -764,36 +767,46 @@ hist_window_kernel(bf_param_tables prm, int rounds, int hist_doubles,
       const int depth = __reduce_max_sync(0xffffffffu, lane < 16 ? tmpw[lane] + tmpw[lane + 16] : 0);
       __syncwarp();
       lparam[r * 32 + slot] = k < nq ? k : -1;
-      lcol[r * 32 + slot] = (rows + below - mn) * 16 + (slot & 15);
+      lcol[r * 32 + slot] = (below - mn) * 16 + (slot & 15);
       plane[k] = slot;
-      rows += depth;
+      if (lane == 0) {
+        misc[4 + r] = depth * 16;
+        misc[8 + r] = total;
+      }
+      total += depth * 16;
     }
     if (lane == 0) {
-      const int fit = hist_doubles / (rows * 16);
-      misc[0] = rows * 16;
-      misc[1] = fit < NW ? fit : NW;
+      const int fit = hist_doubles / total, most = NW / rounds;
+      int n = fit < most ? fit : most;
+      // several rounds make the expectation kernel expensive (it walks the star once per
+      // round): rather give up a copy or two per round and keep kMinExpWarps warps for the
+      // expectation sums in this block
+      const int n_in = (NW - kMinExpWarps) / rounds;
+      if (rounds > 1 && sc.star_flags != nullptr && n > n_in && n < 2 * n_in) n = n_in;
+      misc[0] = total;
+      misc[1] = n;
     }
   }
   __syncthreads();
-  const int copy = misc[0], nwe = misc[1];
+  const int copy = misc[0], npr = misc[1];  // doubles of one copy of every round, copies per round
+  const int nwe = npr * rounds;             // warps that accumulate
   // A star with broad ranges leaves warps without a private copy: from kMinExpWarps on they
   // take the star's expectation sums, and the expectation kernel skips the star.
   const int n_exp = NW - nwe;
   const bool exp_here = sc.star_flags != nullptr && n_exp >= kMinExpWarps;
   if (threadIdx.x == 0 && sc.star_flags) sc.star_flags[s - star_begin] = exp_here ? 1 : 0;
-  for (int i = threadIdx.x; i < nwe * copy; i += blockDim.x) hist[i] = 0.0;
+  for (int i = threadIdx.x; i < npr * copy; i += blockDim.x) hist[i] = 0.0;
   __syncthreads();
 
-  // ---- pass 2: accumulate, warps 0..nwe-1 share the star's groups -------------------------
+  // ---- pass 2: accumulate; warp w works on round w / npr, copy w % npr -----------------------
   if (warp < nwe) {
-    double* wbuf = wbuf_all + warp * kStageDoubles;
-    for (int r = 0; r < rounds; ++r) {
-      const int k = lparam[r * 32 + lane];
-      const bool live = k >= 0;  // the others read bin 0 everywhere and own a one-bin range
-      accumulate_columns<16>(prm, sc.weights, entry_base, list, out.member_mask, e0 + warp, e1, nwe,
-                             live ? k : 0, live ? 0xffffffffu : 0u, lane,
-                             hist + warp * copy + lcol[r * 32 + lane], wbuf);
-    }
+    const int r = warp / npr, i = warp - r * npr;
+    const int k = lparam[r * 32 + lane];
+    const bool live = k >= 0;  // the others read bin 0 everywhere and own a one-bin range
+    accumulate_columns<16>(prm, sc.weights, entry_base, list, out.member_mask, e0 + i, e1, npr,
+                           live ? k : 0, live ? 0xffffffffu : 0u, lane,
+                           hist + npr * misc[8 + r] + i * misc[4 + r] + lcol[r * 32 + lane],
+                           wbuf_all + warp * kStageDoubles);
   } else if (exp_here) {
     expectation_rows(prm, rounds, sc.weights, entry_base, list, out.member_mask,
                      e0 + (warp - nwe), e1, n_exp, lane, epart + (warp - nwe) * npad);
@@ -819,14 +832,15 @@ hist_window_kernel(bf_param_tables prm, int rounds, int hist_doubles,
     const int nbk = prm.bin_off[kq + 1] - b0;
     const int mn = wmin[kq];
     const int width = wmax[kq] >= mn ? wmax[kq] - mn + 1 : 0;
-    const double* src = hist + lcol[(kq & ~31) + plane[kq]];
+    const int copy_r = misc[4 + (kq >> 5)];
+    const double* src = hist + npr * misc[8 + (kq >> 5)] + lcol[(kq & ~31) + plane[kq]];
     double* row = out.pdf1d + s * tb + b0;
     const bool from_bins = prm.q_const && prm.q_const[kq];
     double eq = 0.0;
     for (int b = lane; b < nbk; b += 32) {
       double v = 0.0;
       if (b >= mn && b < mn + width)
-        for (int w = 0; w < nwe; ++w) v += src[w * copy + b * 16];
+        for (int w = 0; w < npr; ++w) v += src[w * copy_r + b * 16];
       row[b] = v * inv;
       if (from_bins) eq += v * prm.bin_q[b0 + b];
     }
