@@ -461,12 +461,12 @@ hist_kernel(bf_param_tables prm, int rounds, const double* __restrict__ pmax,
 // Shared memory (doubles): hist [hist_doubles] | wbuf [16][64] | red, redj, scan | int
 // tables wmin, wmax, plane, lparam, lcol [rounds*32] | tmpw [32] | misc [4].
 // ---------------------------------------------------------------------------------------
-constexpr int kWindowWarps = 16;
+constexpr int kWindowWarps = 20;
 constexpr int kMinExpWarps = 8;  // idle warps from which a block does the expectation sums itself
 
 struct WindowSmem {
   static __host__ __device__ size_t bytes(int hist_doubles, int rounds) {
-    return (static_cast<size_t>(hist_doubles) + kWindowWarps * kStageDoubles + 3 * kWindowWarps + 8 +
+    return (static_cast<size_t>(hist_doubles) + kWindowWarps * kStageDoubles + 4 * kWindowWarps +
             static_cast<size_t>(kWindowWarps) * rounds * 32) * sizeof(double) +
            (5 * static_cast<size_t>(rounds) * 32 + 32 + 16) * sizeof(int);
   }
@@ -660,7 +660,7 @@ hist_window_kernel(bf_param_tables prm, int rounds, int hist_doubles,
   double* red = wbuf_all + NW * kStageDoubles;
   long long* redj = reinterpret_cast<long long*>(red + 2 * NW);
   uint32_t* sscan = reinterpret_cast<uint32_t*>(redj + NW);
-  double* epart = red + 3 * NW + 8;  // [NW][npad] expectation sums of the warps that do them
+  double* epart = red + 4 * NW;  // [NW][npad] expectation sums of the warps that do them
   int* wmin = reinterpret_cast<int*>(epart + NW * npad);
   int* wmax = wmin + npad;
   int* plane = wmax + npad;    // lane that works on parameter k (within its round of 32)
