@@ -462,7 +462,7 @@ hist_kernel(bf_param_tables prm, int rounds, const double* __restrict__ pmax,
 // tables wmin, wmax, plane, lparam, lcol [rounds*32] | tmpw [32] | misc [4].
 // ---------------------------------------------------------------------------------------
 constexpr int kWindowWarps = 20;
-constexpr int kMinExpWarps = 8;  // idle warps from which a block does the expectation sums itself
+constexpr int kMinExpWarps = 10;  // idle warps from which a block does the expectation sums itself
 
 struct WindowSmem {
   static __host__ __device__ size_t bytes(int hist_doubles, int rounds) {
