@@ -66,6 +66,38 @@ def test_device_layouts(small):
     assert st.err_a > 0 and st.err_b > 0
 
 
+def test_bin_constant_parameters_regroup_the_expectation(small):
+    """parameters whose bins each hold one value: sum_m w_m q_m = sum_b (sum_{m in b} w_m) q_b, the
+    identity behind taking their expectation from the histogram (fit.py:743 vs pdf1d.py:142-147)"""
+    g, nz, obs = small
+    keys = fo.default_keys(g)
+    with pytest.warns(UserWarning, match="zero weight"):
+        st = FitSetup(g, nz, list(keys), max_nbins=6)
+    assert st.q_const.any() and not st.q_const.all()
+    rng = np.random.default_rng(5)
+    idx = np.sort(rng.choice(st.n_models, size=40, replace=False))
+    w = rng.random(40)
+    for k in range(st.n_q):
+        col = st.qcols[k][st.g0_indxs]
+        bn = st.bins[k].bin_num[st.g0_indxs]
+        a, b = st.bin_off[k], st.bin_off[k + 1]
+        if st.q_const[k]:
+            # every model of a bin carries the bin's value (stored relative to the mid value) ...
+            np.testing.assert_allclose(st.q_lin[k, 0] + st.bin_q[a:b][bn], col, rtol=4e-16, atol=0)
+            # ... so the histogram gives the expectation
+            hist = np.bincount(bn[idx], weights=w, minlength=b - a)
+            got = st.q_lin[k, 0] + float(hist @ st.bin_q[a:b]) / w.sum()
+            want = fo.expectation(col[idx], weights=w)
+            assert abs(got - want) <= 1e-12 * max(1.0, abs(want))
+        else:
+            per_bin = [np.ptp(col[bn == v]) for v in np.unique(bn)]
+            assert max(per_bin) > 0  # some bin mixes values: the per-model table is needed
+    # a single-valued parameter comes out exactly
+    single = [k for k in range(st.n_q) if st.bins[k].nbins == 1]
+    for k in single:
+        assert st.q_const[k] and st.bin_q[st.bin_off[k]] == 0.0
+
+
 def test_error_conventions(small):
     g, nz, obs = small
     bad = dict(nz)
