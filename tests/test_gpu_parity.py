@@ -124,6 +124,26 @@ def test_histogram_layouts_agree_with_the_oracle(layout, monkeypatch):
     util.compare_to_reference(setup, res, want)
 
 
+def test_full_width_kernel_at_100_bins(monkeypatch):
+    """100-bin tables leave the full-width histogram kernel 8 warps: it then adds four models at a
+    time (as the windowed kernel does); BF_HIST_SERIAL selects the one-member-at-a-time loop"""
+    from beast_b200 import synth
+    from oracle import fit_oracle as fo
+
+    g, nz, obs = synth.make_config("C1", nstars=24, seed=9)
+    keys = fo.default_keys(g)
+    want = fo.fit_all(obs.fluxes, fo.OracleSetup(g, nz, keys, max_nbins=100), threshold=-10.0, fast=True)
+    args = dict(keys=keys, max_nbins=100, pdf2d_param_list=None, do_not_normalize=False)
+    monkeypatch.setenv("BF_HIST", "full")
+    setup, eng = _engine(g, nz, args)
+    res = eng.fit(obs.fluxes, threshold=-10.0, sparse="all")
+    util.compare_to_reference(setup, res, want)
+    monkeypatch.setenv("BF_HIST_SERIAL", "1")
+    res2 = eng.fit(obs.fluxes, threshold=-10.0, sparse="all")
+    util.compare_to_reference(setup, res2, want)
+    np.testing.assert_allclose(res.pdf1d, res2.pdf1d, rtol=1e-12, atol=1e-300)
+
+
 def test_weights_kernel_instantiations_are_bit_identical(monkeypatch):
     """the per-band-count weights kernel (all loads of a model in flight at once) performs the
     same operations in the same order as the runtime-band-count one: every output bit agrees"""
