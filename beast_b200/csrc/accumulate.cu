@@ -1,18 +1,24 @@
 // The sparse pass (K4), three launches.
 //
-// (1) exact_weights_kernel -- one warp per listed group, lane <-> model: exact lnP,
+// (1) exact_weights_kernel<NB> -- one warp per listed group, lane <-> model: exact lnP,
 //     membership (lnp - max > threshold, beast/fitting/fit.py:670), weight exp(lnp - max)
-//     (fit.py:685), per-group weight sum and chi2 minimum (fit.py:689, 725-726).  Perfectly
-//     load balanced and latency tolerant (tens of thousands of independent warps).
-// (2) hist_kernel -- one block per star, lane <-> parameter: every 8-model chunk that has
-//     a member is one coalesced row read (8 bin bytes per lane);
-//     each lane adds the members' weights into its own column of a per-warp private
-//     histogram laid out [bin][lane] (bank = lane: conflict free, no atomics, fixed summation
-//     order, bit-reproducible).  The next group's rows are fetched while the current one is
-//     processed.  exp_kernel does the same walk for sum w*q (fit.py:743) without any
-//     shared-memory state, so it runs at full occupancy.  Private
-//     histograms are merged in warp order, normalised by the weight sum (fit.py:690), and
-//     one warp per parameter turns the pdf into p16/p50/p84 (fit_metrics/common.py:112-121).
+//     (fit.py:685), per-group weight sum and chi2 minimum (fit.py:689, 725-726).  Tens of
+//     thousands of independent warps; the kernel waits on HBM, so the band count is a
+//     template parameter and all rows of a model are requested before the first is used.
+// (2) the histograms, one block per star, lane <-> parameter: every 8-model chunk that has
+//     a member is one coalesced row read (8 bin bytes per lane); each lane adds the weights
+//     into its own column of a per-warp private histogram (no atomics, fixed summation
+//     order, bit-reproducible); private histograms are merged in warp order, normalised by
+//     the weight sum (fit.py:690), and one warp per parameter turns the pdf into
+//     p16/p50/p84 (fit_metrics/common.py:112-121).  Two kernels:
+//       hist_kernel         full-width columns [bin][lane] (bank = lane), as many warps as fit
+//                           (16 at 50 bins, 4 at 200);
+//       hist_window_kernel  for wide bin tables: columns sized by the star's occupied bin
+//                           ranges, up to 20 warps, models added four at a time; warps left
+//                           without a histogram do the star's expectation sums.
+// (3) exp_kernel -- sum w*q (fit.py:743) for the stars and parameters the histogram kernel
+//     has not covered: no shared-memory state, full occupancy.  Parameters whose bins each
+//     hold a single value get their expectation from the histogram instead.
 
 #include <cstdlib>
 
