@@ -319,6 +319,10 @@ def run_ours(args, rank, world, local_rank):
         "dense_ms_per_launch": dense_ms, "flop_per_star_model": flop_per_eval,
         "hbm_gbs_peak": peaks.get("hbm_gbs"),
         "stage_ms_per_step": {k: v / args.steps for k, v in stage_tot.items()},
+        # where the step goes: the sparse pass (exact weights, histograms, expectations) is the
+        # longest stage; its kernels are bound by HBM latency and the L1/shared data pipe
+        # (profiles/r01_exact_weights_ncu.md, profiles/r01_hist_window_ncu.md)
+        "stage_share_of_step": {k: (v / args.steps) / ms_step for k, v in stage_tot.items()},
     }
 
     # ---- the step before the fit: trim_models flags pass, HBM-bound (fitting/trim_grid.py) -----
