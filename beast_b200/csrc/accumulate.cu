@@ -493,9 +493,9 @@ hist_kernel(bf_param_tables prm, int rounds, const double* __restrict__ pmax,
 // range [min bin, max bin] of every parameter.  A first walk over the star's bin rows finds
 // the ranges (16-bit SIMD min/max, no shared-memory traffic); the private copies are then
 // sized by the ranges (see the layout step) instead of 32 x max_bins doubles per warp, and
-// as many of the block's 16 warps as fit work on the star (4 with the full-width layout at
+// as many of the block's 20 warps as fit work on the star (4 with the full-width layout at
 // 200 bins).
-// Shared memory (doubles): hist [hist_doubles] | wbuf [16][64] | red, redj, scan | int
+// Shared memory (doubles): hist [hist_doubles] | wbuf [20][64] | red, redj, scan | epart | int
 // tables wmin, wmax, plane, lparam, lcol [rounds*32] | tmpw [32] | misc [4].
 // ---------------------------------------------------------------------------------------
 constexpr int kWindowWarps = 20;
