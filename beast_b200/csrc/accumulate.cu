@@ -496,7 +496,7 @@ hist_kernel(bf_param_tables prm, int rounds, const double* __restrict__ pmax,
 // as many of the block's 20 warps as fit work on the star (4 with the full-width layout at
 // 200 bins).
 // Shared memory (doubles): hist [hist_doubles] | wbuf [20][64] | red, redj, scan | epart | int
-// tables wmin, wmax, plane, lparam, lcol [rounds*32] | tmpw [32] | misc [4].
+// tables wmin, wmax, plane, lparam, lcol [rounds*32] | tmpw [32] | misc [16].
 // ---------------------------------------------------------------------------------------
 constexpr int kWindowWarps = 20;
 constexpr int kMinExpWarps = 10;  // idle warps from which a block does the expectation sums itself
