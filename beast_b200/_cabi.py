@@ -110,6 +110,8 @@ PROTOTYPES = {
                                    c_void_p, c_void_p]),
     "bf_sparse_sample_ranks": (C.c_int, [i64, c_void_p, c_void_p, C.c_uint64, i64, c_void_p,
                                          c_void_p]),
+    "bf_pdf2d_from_weights": (C.c_int, [i64, C.c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p,
+                                        c_void_p, c_void_p, c_void_p, i64, i64, c_void_p, c_void_p]),
     "bf_pdf2d_accumulate": (C.c_int, [C.POINTER(ExactGrid), C.c_int, c_void_p, c_void_p, i64,
                                       c_void_p, c_void_p, c_void_p, C.c_double, c_void_p,
                                       c_void_p, c_void_p, c_void_p]),

@@ -140,7 +140,65 @@ pdf2d_kernel(bf_exact_grid grid, int n_pairs, const int32_t* __restrict__ pair_b
   }
 }
 
+// Same sums from the weights the sparse pass has just left in its scratch (exp(lnP - Pmax) of the
+// members, membership bits): no model is evaluated again.  One warp per listed group.
+__global__ void __launch_bounds__(kPdf2dWarps * 32)
+pdf2d_weights_kernel(int64_t ld_model, int n_pairs, const int32_t* __restrict__ pair_bin,
+                     const int64_t* __restrict__ pair_off, const double* __restrict__ pmax,
+                     const double* __restrict__ tln, const uint32_t* __restrict__ list,
+                     const uint32_t* __restrict__ entry_star, const uint32_t* __restrict__ member_mask,
+                     const double* __restrict__ weights, int64_t entry_base, int64_t n_entries,
+                     double* __restrict__ pdf2d) {
+  const int lane = threadIdx.x & 31;
+  const int64_t row_len = pair_off[n_pairs];
+  for (int64_t slot = static_cast<int64_t>(blockIdx.x) * kPdf2dWarps + (threadIdx.x >> 5);
+       slot < n_entries; slot += static_cast<int64_t>(gridDim.x) * kPdf2dWarps) {
+    const uint32_t e = static_cast<uint32_t>(entry_base + slot);
+    const uint32_t m0 = member_mask[static_cast<size_t>(e) * kWordsPerGroup];
+    const uint32_t m1 = member_mask[static_cast<size_t>(e) * kWordsPerGroup + 1];
+    if ((m0 | m1) == 0) continue;
+    const int64_t s = entry_star[e];
+    // weights are relative to Pmax; 1 / (sum of weights) = exp(Pmax - total_log_norm) (fit.py:716)
+    const double inv = exp(pmax[s] - tln[s]);
+    double* row = pdf2d + s * row_len;
+    const int64_t j0 = static_cast<int64_t>(list[e]) * BF_GROUP;
+#pragma unroll
+    for (int h = 0; h < kWordsPerGroup; ++h) {
+      if (!(((h ? m1 : m0) >> lane) & 1u)) continue;
+      const int64_t j = j0 + h * 32 + lane;
+      const double w = weights[slot * BF_GROUP + h * 32 + lane] * inv;
+      for (int p = 0; p < n_pairs; ++p) {
+        const int32_t b = pair_bin[static_cast<int64_t>(p) * ld_model + j];
+        if (b >= 0) atomicAdd(row + pair_off[p] + b, w);
+      }
+    }
+  }
+}
+
 }  // namespace bf
+
+extern "C" int bf_pdf2d_from_weights(int64_t ld_model, int n_pairs, const int32_t* pair_bin,
+                                     const int64_t* pair_off, const double* pmax,
+                                     const double* total_log_norm, const uint32_t* list,
+                                     const uint32_t* entry_star, const uint32_t* member_mask,
+                                     const double* weights, int64_t entry_base, int64_t n_entries,
+                                     double* pdf2d, void* stream) {
+  using namespace bf;
+  BF_REQUIRE(n_pairs >= 1 && ld_model > 0, "bf_pdf2d_from_weights: bad sizes");
+  BF_REQUIRE(entry_base >= 0 && n_entries >= 0, "bf_pdf2d_from_weights: bad entry range");
+  BF_REQUIRE(pair_bin && pair_off && pmax && total_log_norm && list && entry_star && member_mask &&
+                 weights && pdf2d,
+             "bf_pdf2d_from_weights: null pointer");
+  if (n_entries == 0) return BF_OK;
+  const int64_t blocks = (n_entries + kPdf2dWarps - 1) / kPdf2dWarps;
+  const int64_t cap = 148LL * 64;
+  pdf2d_weights_kernel<<<static_cast<unsigned>(blocks < cap ? blocks : cap), kPdf2dWarps * 32, 0,
+                         static_cast<cudaStream_t>(stream)>>>(
+      ld_model, n_pairs, pair_bin, pair_off, pmax, total_log_norm, list, entry_star, member_mask,
+      weights, entry_base, n_entries, pdf2d);
+  BF_CHECK_LAUNCH("pdf2d_weights_kernel");
+  return BF_OK;
+}
 
 extern "C" int bf_sparse_gather(const bf_exact_grid* grid, int64_t n_stars, const double* flux64,
                                 const uint32_t* offsets, const uint32_t* list,

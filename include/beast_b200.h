@@ -276,6 +276,18 @@ int bf_pdf2d_accumulate(const bf_exact_grid* grid, int n_pairs, const int32_t* p
                         const uint32_t* offsets, const uint32_t* list, double* pdf2d,
                         void* stream);
 
+/* The same 2D PDFs from what bf_exact_accumulate has just left behind for the list range
+ * [entry_base, entry_base + n_entries): the members' weights exp(lnP - Pmax) in
+ * scratch->weights, the membership bits, and total_log_norm (1 / sum of weights =
+ * exp(Pmax - total_log_norm), fit.py:716).  No model is evaluated again, so this is the call
+ * to use right after each bf_exact_accumulate; bf_pdf2d_accumulate needs neither scratch nor
+ * masks.  pdf2d rows of the stars concerned must be zero before their first range. */
+int bf_pdf2d_from_weights(int64_t ld_model, int n_pairs, const int32_t* pair_bin,
+                          const int64_t* pair_off, const double* pmax, const double* total_log_norm,
+                          const uint32_t* list, const uint32_t* entry_star,
+                          const uint32_t* member_mask, const double* weights, int64_t entry_base,
+                          int64_t n_entries, double* pdf2d, void* stream);
+
 /* ---------------------------------------------------------------------------
  * Subgrid merge (tools/subgridding_tools.py:392-527), device part.  Each rank holds the
  * results of its own subgrid for the same stars; after the caller all-gathers
