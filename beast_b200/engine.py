@@ -342,6 +342,7 @@ class FitEngine:
             pdf2d = None
             if want_pdf2d and self.d_pair_bin is not None:
                 pdf2d = torch.zeros((n, int(s.pair_off[-1])), dtype=torch.float64, device=dev)
+            reeval = pdf2d is not None and getattr(self, "pdf2d_reevaluate", False)
             for a0, b0 in cuts:
                 base, cnt = int(off_host[a0]), int(off_host[b0] - off_host[a0])
                 # one block per star in the histogram kernel: longest lists first, so that the
@@ -354,7 +355,7 @@ class FitEngine:
                                pct, C.byref(scr), C.byref(outs), st,
                                C.c_void_p(self._aux_stream.cuda_stream))
                 self.launches += 3
-                if pdf2d is not None and cnt:
+                if pdf2d is not None and cnt and not reeval:
                     # 2D PDFs of this range from the weights still in the scratch (fit.py:758-762)
                     with self._timed("pdf2d"):
                         _cabi.call("bf_pdf2d_from_weights", s.ld_model, len(s.pairs),
@@ -363,6 +364,12 @@ class FitEngine:
                                    _ptr(w_scr), base, cnt, _ptr(pdf2d), st)
                     self.launches += 1
             o["n_groups_selected"] = off_star[1:] - off_star[:-1]
+            if reeval:  # the stand-alone entry point: evaluates the listed models again (tests)
+                _cabi.call("bf_pdf2d_accumulate", C.byref(self.grid), len(s.pairs),
+                           _ptr(self.d_pair_bin), _ptr(self.d_pair_off), n, _ptr(d_flux),
+                           _ptr(pmax), _ptr(o["total_log_norm"]), float(threshold),
+                           _ptr(offsets), _ptr(lst), _ptr(pdf2d), st)
+                self.launches += 1
             if pdf2d is not None:
                 o["pdf2d"] = pdf2d
 

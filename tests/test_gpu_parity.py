@@ -155,3 +155,15 @@ def test_weights_kernel_instantiations_are_bit_identical(monkeypatch):
     for name in ("Pmax", "Pmax_j", "total_log_norm", "chi2min", "chi2min_j", "n_sparse", "pdf1d",
                  "exp_vals", "per_vals", "sparse_j", "sparse_lnp", "sparse_chi2"):
         np.testing.assert_array_equal(getattr(a, name), getattr(b, name), err_msg=name)
+
+
+def test_pdf2d_entry_points_agree():
+    """bf_pdf2d_from_weights (weights left by the sparse pass) and bf_pdf2d_accumulate (models
+    evaluated again) build the same 2D PDFs; both match the reference's (golden case)"""
+    g, nz, obs, args, ref = util.load_golden("tiny_thr10_pdf2d")
+    setup, eng = _engine(g, nz, args)
+    a = eng.fit(obs.fluxes, threshold=args["threshold"], want_pdf2d=True, sparse="all")
+    eng.pdf2d_reevaluate = True
+    b = eng.fit(obs.fluxes, threshold=args["threshold"], want_pdf2d=True, sparse="all")
+    util.compare_to_reference(setup, b, ref, n_pdf2d=len(setup.pairs))
+    np.testing.assert_allclose(a.pdf2d, b.pdf2d, rtol=1e-12, atol=1e-300)
