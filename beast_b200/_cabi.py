@@ -53,6 +53,16 @@ class ParamTables(C.Structure):
         ("bin_val", c_void_p),
         ("q_const", c_void_p),
         ("bin_q", c_void_p),
+        ("n_fast", C.c_int),
+        ("n_slow", C.c_int),
+        ("fast_pad", C.c_int),
+        ("slow_pad", C.c_int),
+        ("fast_k", c_void_p),
+        ("slow_k", c_void_p),
+        ("fast_bin", c_void_p),
+        ("fast_q", c_void_p),
+        ("slow_bin", c_void_p),
+        ("slow_q", c_void_p),
     ]
 
 
@@ -63,6 +73,8 @@ class AccumScratch(C.Structure):
         ("part_chi2", c_void_p),
         ("part_chi2_j", c_void_p),
         ("star_flags", c_void_p),
+        ("group_order", c_void_p),
+        ("chunk_refs", c_void_p),
     ]
 
 
@@ -97,6 +109,8 @@ PROTOTYPES = {
     "bf_scan_scratch_elems": (i64, [i64]),
     "bf_exclusive_scan_u32": (C.c_int, [i64, c_void_p, c_void_p, c_void_p, c_void_p]),
     "bf_exclusive_scan_u32_noalloc": (C.c_int, [i64, c_void_p, c_void_p, c_void_p]),
+    "bf_group_order_work_elems": (i64, [i64]),
+    "bf_group_order": (C.c_int, [i64, c_void_p, i64, i64, c_void_p, c_void_p, c_void_p]),
     "bf_exact_max": (C.c_int, [C.POINTER(ExactGrid), i64, i64, c_void_p, c_void_p, c_void_p,
                                C.c_float, C.c_float, c_void_p, c_void_p, c_void_p, c_void_p,
                                c_void_p]),

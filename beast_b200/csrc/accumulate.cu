@@ -22,8 +22,7 @@
 
 #include <cstdlib>
 
-#include "exact.cuh"
-#include "percentile.cuh"
+#include "accum_common.cuh"
 
 namespace bf {
 
@@ -231,115 +230,6 @@ __device__ __forceinline__ void load_entry(const bf_param_tables& prm, const dou
       r.bits[c] = static_cast<unsigned long long>(bb.x) | (static_cast<unsigned long long>(bb.y) << 32);
     }
   }
-}
-
-// expectation of a parameter whose bins each hold one value: q_mid + sum_b H_b (q_b - q_mid) / sum w
-// (fit.py:743 regrouped by bin; bin_q holds q_b - q_mid, q_mid = q_lin[2k], so that a
-// single-valued parameter comes out exactly); eq holds this lane's part of the sum
-__device__ __forceinline__ void store_bin_expectation(double eq, double wtot, bool empty,
-                                                      double q_mid, double* dst, int lane) {
-#pragma unroll
-  for (int d = 16; d > 0; d >>= 1) eq += __shfl_xor_sync(0xffffffffu, eq, d);
-  if (lane == 0) *dst = empty ? __longlong_as_double(0x7ff8000000000000LL) : q_mid + eq / wtot;
-}
-
-// per-star reductions over the group partials, fixed order: weight sum (returned), chi2
-// minimum and its model (fit.py:689, 725-726), total_log_norm (fit.py:731)
-__device__ __forceinline__ double star_totals(uint32_t e0, uint32_t e1, int64_t entry_base,
-                                              const bf_accum_scratch& sc, double M, int64_t s,
-                                              double* red, long long* redj,
-                                              const bf_star_outputs& out) {
-  const int nw = blockDim.x >> 5;
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  double wpart = 0.0, cpart = 1.7976931348623157e308;
-  long long cj = -1;
-  for (uint32_t e = e0 + threadIdx.x; e < e1; e += blockDim.x) {
-    const int64_t slot = static_cast<int64_t>(e) - entry_base;
-    wpart += sc.part_wsum[slot];
-    const long long oj = sc.part_chi2_j[slot];
-    const double oc = sc.part_chi2[slot];
-    if (oj >= 0 && (cj < 0 || oc < cpart || (oc == cpart && oj < cj))) {
-      cpart = oc;
-      cj = oj;
-    }
-  }
-#pragma unroll
-  for (int d = 16; d > 0; d >>= 1) {
-    wpart += __shfl_xor_sync(0xffffffffu, wpart, d);
-    const double oc = __shfl_xor_sync(0xffffffffu, cpart, d);
-    const long long oj = __shfl_xor_sync(0xffffffffu, cj, d);
-    if (oj >= 0 && (cj < 0 || oc < cpart || (oc == cpart && oj < cj))) {
-      cpart = oc;
-      cj = oj;
-    }
-  }
-  if (lane == 0) {
-    red[warp] = wpart;
-    red[nw + warp] = cpart;
-    redj[warp] = cj;
-  }
-  __syncthreads();
-  double wtot = 0.0;
-  for (int w = 0; w < nw; ++w) wtot += red[w];
-  const bool empty = !(wtot > 0.0);
-  const double qnan = __longlong_as_double(0x7ff8000000000000LL);
-  if (threadIdx.x == 0) {
-    double c = 1.7976931348623157e308;
-    long long bj = -1;
-    for (int w = 0; w < nw; ++w) {
-      if (redj[w] >= 0 && (bj < 0 || red[nw + w] < c || (red[nw + w] == c && redj[w] < bj))) {
-        c = red[nw + w];
-        bj = redj[w];
-      }
-    }
-    out.total_log_norm[s] = empty ? qnan : M + log(wtot);
-    out.chi2min[s] = empty ? qnan : c;
-    out.chi2min_j[s] = bj;
-  }
-  return wtot;
-}
-
-// percentiles of the finished pdfs (one warp per parameter, fit_metrics/common.py:112-121)
-// and the exclusive prefix of the per-group member counts over this star's list
-__device__ __forceinline__ void star_percentiles_and_prefix(const bf_param_tables& prm, int64_t s,
-                                                            uint32_t e0, uint32_t e1, double p0,
-                                                            double p1, double p2, double* cdf_area,
-                                                            uint32_t* sscan,
-                                                            const bf_star_outputs& out) {
-  const int nw = blockDim.x >> 5;
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int nq = prm.n_q, tb = prm.total_bins;
-  double* cdf = cdf_area + warp * kMaxBinsPerParam;
-  for (int kq = warp; kq < nq; kq += nw) {
-    const int b0 = prm.bin_off[kq];
-    const int nbk = prm.bin_off[kq + 1] - b0;
-    warp_percentiles(out.pdf1d + s * tb + b0, prm.bin_val + b0, nbk, cdf, p0, p1, p2,
-                     out.per_vals + (s * nq + kq) * 3, lane);
-  }
-
-  // ---- per-group member counts -> exclusive prefix over this star's list -----------------
-  uint32_t carry = 0;
-  for (uint32_t base = e0; base < e1; base += blockDim.x) {
-    const uint32_t e = base + threadIdx.x;
-    const uint32_t v = e < e1 ? out.member_prefix[e] : 0u;
-    uint32_t inc = v;
-#pragma unroll
-    for (int d = 1; d < 32; d <<= 1) {
-      const uint32_t t = __shfl_up_sync(0xffffffffu, inc, d);
-      if (lane >= d) inc += t;
-    }
-    __syncthreads();
-    if (lane == 31) sscan[warp] = inc;
-    __syncthreads();
-    uint32_t woff = 0, tot = 0;
-    for (int w = 0; w < nw; ++w) {
-      if (w < warp) woff += sscan[w];
-      tot += sscan[w];
-    }
-    if (e < e1) out.member_prefix[e] = carry + woff + inc - v;
-    carry += tot;
-  }
-  if (threadIdx.x == 0) out.n_sparse[s] = carry;
 }
 
 template <bool BATCH>
@@ -959,6 +849,17 @@ extern "C" int bf_exact_accumulate(const bf_exact_grid* grid, const bf_param_tab
     // 1.4x faster than the runtime loop); full covariance and > 12 bands take the generic one
     int nbk = grid->cov_off == nullptr && grid->nb <= 12 ? grid->nb : 0;
     if (getenv("BF_WEIGHTS_GENERIC")) nbk = 0;  // measurements
+    // with the list positions ordered by group the rows of a group are fetched once for all
+    // its stars (BF_WEIGHTS=star keeps the star-ordered kernel, for measurements and tests)
+    const char* wenv = getenv("BF_WEIGHTS");
+    // (two models' rows per lane: up to 8 bands fit the register file without spills)
+    const bool grouped = scratch->group_order != nullptr && nbk > 0 && nbk <= 8 &&
+                         !(wenv && wenv[0] == 's');
+    if (grouped) {
+      const int rc = launch_weights_grouped(*grid, flux64, pmax, threshold, list, entry_star,
+                                            entry_base, n_entries, *scratch, *out, sm_count[dev], st);
+      if (rc != BF_OK) return rc;
+    } else {
 #define BF_WEIGHTS_CASE(N)                                                                      \
   case N:                                                                                       \
     exact_weights_kernel<N><<<wgrid, kWeightWarps * 32, 0, st>>>(                               \
@@ -974,6 +875,7 @@ extern "C" int bf_exact_accumulate(const bf_exact_grid* grid, const bf_param_tab
     }
 #undef BF_WEIGHTS_CASE
     BF_CHECK_LAUNCH("exact_weights_kernel");
+    }
   }
   if (timing) cudaEventRecord(tev[1], st);
   const int rounds = (params->n_q + 31) / 32;
@@ -1003,6 +905,31 @@ extern "C" int bf_exact_accumulate(const bf_exact_grid* grid, const bf_param_tab
   bool use_window = window_fits && nw < 8;
   if (hist_env && hist_env[0] == 'f') use_window = false;
   if (hist_env && hist_env[0] == 'w') use_window = window_fits;
+  // the class-split kernel needs the class tables, room for the chunk lists and, like the
+  // windowed kernel, one worst-case private copy per class; it does every expectation itself
+  const bool use_split = scratch->chunk_refs != nullptr && split_hist_supported(*params, budget) &&
+                         !(hist_env && (hist_env[0] == 'f' || hist_env[0] == 'w'));
+  if (use_split) {
+    const int rc = launch_split_hist(*params, pmax, offsets, list, star_order, star_begin, n_stars,
+                                     entry_base, *scratch, percentiles_host[0], percentiles_host[1],
+                                     percentiles_host[2], *out, budget, st);
+    if (rc != BF_OK) return rc;
+    if (timing) {
+      cudaEventRecord(tev[2], st);
+      cudaStreamSynchronize(st);
+      float w = 0, h = 0;
+      cudaEventElapsedTime(&w, tev[0], tev[1]);
+      cudaEventElapsedTime(&h, tev[1], tev[2]);
+      fprintf(stderr, "[bf timing] stars=%lld entries=%lld weights=%.2f ms (%s) split hist=%.2f ms\n",
+              static_cast<long long>(n_stars), static_cast<long long>(n_entries), w,
+              scratch->group_order ? "grouped" : "by star", h);
+      for (auto& e : tev) cudaEventDestroy(e);
+    }
+    return BF_OK;
+  }
+  BF_REQUIRE(params->bin_tab && params->q_tab,
+             "bf_exact_accumulate: the per-model tables bin_tab / q_tab are needed (no class split "
+             "usable for this call)");
   if (timing && getenv("BF_TIMING")[0] == '2') aux_stream = nullptr;  // serial: each kernel alone
   // the windowed kernel tells the expectation kernel which stars it has done: same stream
   if (use_window) aux_stream = nullptr;

@@ -1,0 +1,741 @@
+// The split sparse pass: the two kernels bf_exact_accumulate prefers when the caller supplies
+// what they need (scratch->group_order, scratch->chunk_refs, the class tables of bf_param_tables).
+//
+// (A) exact_weights_grouped_kernel<NB> -- the same arithmetic and the same outputs as
+//     exact_weights_kernel (beast/fitting/fit.py:670, 685, 689, 725-726), but the list positions
+//     are visited in group order (bf_group_order).  A warp keeps the FP64 rows of a group's 64
+//     models in registers and serves every star of its stretch of the order with them: about a
+//     thousand stars of a batch list the same group, so the 7 KB of rows come out of HBM once
+//     per stretch instead of once per (star, group).
+//
+// (B) split_hist_kernel -- histograms, percentiles and expectations (fit.py:732-755), one block
+//     per star.  Parameters come in two classes (gridprep.FitSetup._class_split):
+//       fast: one shared-memory update and one expectation term per model.  With <= 16 fast
+//             parameters a warp works on two chunks at a time (half-warp <-> chunk, lane <->
+//             parameter), so every update instruction has all 32 lanes busy;
+//       slow: one value per chunk -> one update and one expectation term per chunk, with the
+//             chunk's weight sum, i.e. an eighth of the work.
+//     The block first writes the list of the star's chunks that hold a member (chunk id + place
+//     of its 8 weights), finds every parameter's occupied bin range over those chunks, lays out
+//     private histogram copies sized by the ranges (16 interleaved stacks, conflict free for
+//     64-bit accesses, as in hist_window_kernel), and then fast warps and slow warps walk the
+//     chunk list.  Sums are in fixed order: results are bit-reproducible.
+
+#include <cstdlib>
+
+#include "accum_common.cuh"
+
+namespace bf {
+
+// =========================================================================================
+// bf_group_order: counting sort of list positions by group id
+// =========================================================================================
+__global__ void __launch_bounds__(256)
+group_count_kernel(const uint32_t* __restrict__ list, int64_t entry_base, int64_t n_entries,
+                   uint32_t* __restrict__ counts) {
+  for (int64_t i = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x; i < n_entries;
+       i += static_cast<int64_t>(gridDim.x) * blockDim.x)
+    atomicAdd(counts + list[entry_base + i], 1u);
+}
+
+__global__ void __launch_bounds__(256)
+group_scatter_kernel(const uint32_t* __restrict__ list, int64_t entry_base, int64_t n_entries,
+                     const uint32_t* __restrict__ goff, uint32_t* __restrict__ cursor,
+                     uint32_t* __restrict__ order) {
+  for (int64_t i = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x; i < n_entries;
+       i += static_cast<int64_t>(gridDim.x) * blockDim.x) {
+    const uint32_t g = list[entry_base + i];
+    const uint32_t pos = atomicAdd(cursor + g, 1u);
+    order[goff[g] + pos] = static_cast<uint32_t>(entry_base + i);
+  }
+}
+
+// =========================================================================================
+// (A) group-ordered exact weights
+// =========================================================================================
+constexpr int kGroupedWarps = 8;
+constexpr int kOrderStretch = 128;  // positions of the group order one warp walks in one go
+
+// first index of the smallest chi2 among the member lanes (chi2 >= 0: its bit pattern orders
+// like the value, so two 32-bit warp reductions find the minimum); returns false if no member
+__device__ __forceinline__ bool warp_min_chi2(bool member, double chi2, int lane, double& cmin,
+                                              int& cl) {
+  const unsigned long long u = static_cast<unsigned long long>(__double_as_longlong(chi2));
+  const uint32_t hi = member ? static_cast<uint32_t>(u >> 32) : 0xffffffffu;
+  const uint32_t mh = __reduce_min_sync(0xffffffffu, hi);
+  const bool c1 = member && hi == mh;
+  const uint32_t lo = c1 ? static_cast<uint32_t>(u) : 0xffffffffu;
+  const uint32_t ml = __reduce_min_sync(0xffffffffu, lo);
+  const uint32_t who = __ballot_sync(0xffffffffu, c1 && lo == ml);
+  if (who == 0) return false;
+  cl = __ffs(who) - 1;
+  cmin = __longlong_as_double(static_cast<long long>((static_cast<unsigned long long>(mh) << 32) | ml));
+  return true;
+}
+
+template <int NB>
+__global__ void __launch_bounds__(kGroupedWarps * 32, 2)
+exact_weights_grouped_kernel(bf_exact_grid grid, const double* __restrict__ flux64,
+                             const double* __restrict__ pmax, double threshold,
+                             const uint32_t* __restrict__ list,
+                             const uint32_t* __restrict__ entry_star,
+                             const uint32_t* __restrict__ order, int64_t entry_base,
+                             int64_t n_entries, bf_accum_scratch sc,
+                             uint32_t* __restrict__ member_mask,
+                             uint32_t* __restrict__ member_prefix) {
+  const int lane = threadIdx.x & 31;
+  const int64_t n_stretch = (n_entries + kOrderStretch - 1) / kOrderStretch;
+  for (int64_t st = static_cast<int64_t>(blockIdx.x) * kGroupedWarps + (threadIdx.x >> 5);
+       st < n_stretch; st += static_cast<int64_t>(gridDim.x) * kGroupedWarps) {
+    const int64_t i0 = st * kOrderStretch;
+    const int64_t i1 = i0 + kOrderStretch < n_entries ? i0 + kOrderStretch : n_entries;
+    uint32_t cur_g = 0xffffffffu;
+    double m0[NB], v0[NB], m1[NB], v1[NB];
+    double lq0 = 0.0, lw0 = 0.0, lq1 = 0.0, lw1 = 0.0;
+    bool ok0 = false, ok1 = false;
+    int64_t j0 = 0;
+    for (int64_t blk = i0; blk < i1; blk += 32) {
+      const int cnt = static_cast<int>(i1 - blk < 32 ? i1 - blk : 32);
+      // every lane fetches the description of one list position of this block of 32
+      uint32_t my_e = 0, my_s = 0, my_g = 0;
+      double my_M = 0.0;
+      if (lane < cnt) {
+        my_e = order[blk + lane];
+        my_s = entry_star[my_e];
+        my_g = list[my_e];
+        my_M = pmax[my_s];
+      }
+      for (int t = 0; t < cnt; ++t) {
+        const uint32_t e = __shfl_sync(0xffffffffu, my_e, t);
+        const uint32_t s = __shfl_sync(0xffffffffu, my_s, t);
+        const uint32_t g = __shfl_sync(0xffffffffu, my_g, t);
+        const double M = __shfl_sync(0xffffffffu, my_M, t);
+        double f[NB];
+        const double* sflux = flux64 + static_cast<int64_t>(s) * NB;
+#pragma unroll
+        for (int b = 0; b < NB; ++b) f[b] = __ldg(sflux + b);
+        if (g != cur_g) {  // warp-uniform: the rows of the next group
+          cur_g = g;
+          j0 = static_cast<int64_t>(g) * BF_GROUP + lane;
+          ok0 = j0 < grid.n_models;
+          ok1 = j0 + 32 < grid.n_models;
+#pragma unroll
+          for (int b = 0; b < NB; ++b) {
+            m0[b] = __ldg(grid.msb + static_cast<int64_t>(b) * grid.ld_model + j0);
+            v0[b] = __ldg(grid.ivar + static_cast<int64_t>(b) * grid.ld_model + j0);
+            m1[b] = __ldg(grid.msb + static_cast<int64_t>(b) * grid.ld_model + j0 + 32);
+            v1[b] = __ldg(grid.ivar + static_cast<int64_t>(b) * grid.ld_model + j0 + 32);
+          }
+          lq0 = __ldg(grid.lnq + j0);
+          lw0 = __ldg(grid.lnw + j0);
+          lq1 = __ldg(grid.lnq + j0 + 32);
+          lw1 = __ldg(grid.lnw + j0 + 32);
+        }
+        // the reference's operation order (likelihood.py:47-55, 149-165; fit.py:668), as in
+        // exact_lnp_fixed
+        double a0 = 0.0, a1 = 0.0;
+#pragma unroll
+        for (int b = 0; b < NB; ++b) {
+          const double d0 = __dsub_rn(f[b], m0[b]);
+          const double d1 = __dsub_rn(f[b], m1[b]);
+          a0 = __dadd_rn(a0, __dmul_rn(__dmul_rn(d0, d0), v0[b]));
+          a1 = __dadd_rn(a1, __dmul_rn(__dmul_rn(d1, d1), v1[b]));
+        }
+        const double lnp0 = __dadd_rn(__dsub_rn(-lq0, __dmul_rn(0.5, a0)), lw0);
+        const double lnp1 = __dadd_rn(__dsub_rn(-lq1, __dmul_rn(0.5, a1)), lw1);
+        const bool mem0 = ok0 && (lnp0 - M) > threshold;  // NaN compares false (fit.py:670)
+        const bool mem1 = ok1 && (lnp1 - M) > threshold;
+        const uint32_t mw0 = __ballot_sync(0xffffffffu, mem0);
+        const uint32_t mw1 = __ballot_sync(0xffffffffu, mem1);
+        double w0 = 0.0, w1 = 0.0;
+        if (mw0 | mw1) {
+          if (mem0) w0 = exp(lnp0 - M);
+          if (mem1) w1 = exp(lnp1 - M);
+        }
+        const int64_t slot = static_cast<int64_t>(e) - entry_base;
+        sc.weights[slot * BF_GROUP + lane] = w0;
+        sc.weights[slot * BF_GROUP + 32 + lane] = w1;
+        // group partials: weight sum in the order of exact_weights_kernel (word 0 then word 1
+        // per lane, then the butterfly), chi2 minimum with the lowest index on ties
+        double wsum = w0 + w1;
+#pragma unroll
+        for (int d = 16; d > 0; d >>= 1) wsum += __shfl_xor_sync(0xffffffffu, wsum, d);
+        double c0 = 0.0, c1 = 0.0;
+        int l0 = 0, l1 = 0;
+        const bool h0 = warp_min_chi2(mem0, a0, lane, c0, l0);
+        const bool h1 = warp_min_chi2(mem1, a1, lane, c1, l1);
+        if (lane == 0) {
+          double cm = 1.7976931348623157e308;
+          long long cj = -1;
+          if (h0) {
+            cm = c0;
+            cj = static_cast<long long>(g) * BF_GROUP + l0;
+          }
+          if (h1 && (!h0 || c1 < cm)) {
+            cm = c1;
+            cj = static_cast<long long>(g) * BF_GROUP + 32 + l1;
+          }
+          *reinterpret_cast<uint2*>(member_mask + static_cast<size_t>(e) * kWordsPerGroup) =
+              make_uint2(mw0, mw1);
+          sc.part_wsum[slot] = wsum;
+          sc.part_chi2[slot] = cm;
+          sc.part_chi2_j[slot] = cj;
+          member_prefix[e] = __popc(mw0) + __popc(mw1);
+        }
+      }
+    }
+  }
+}
+
+int launch_weights_grouped(const bf_exact_grid& grid, const double* flux64, const double* pmax,
+                           double threshold, const uint32_t* list, const uint32_t* entry_star,
+                           int64_t entry_base, int64_t n_entries, const bf_accum_scratch& sc,
+                           const bf_star_outputs& out, int sm_count, cudaStream_t st) {
+  const int64_t n_stretch = (n_entries + kOrderStretch - 1) / kOrderStretch;
+  const int64_t blocks = (n_stretch + kGroupedWarps - 1) / kGroupedWarps;
+  const int64_t cap = static_cast<int64_t>(sm_count) * 64;
+  const unsigned gridx = static_cast<unsigned>(blocks < cap ? blocks : cap);
+#define BF_GROUPED_CASE(N)                                                                    \
+  case N:                                                                                     \
+    exact_weights_grouped_kernel<N><<<gridx, kGroupedWarps * 32, 0, st>>>(                    \
+        grid, flux64, pmax, threshold, list, entry_star, sc.group_order, entry_base,          \
+        n_entries, sc, out.member_mask, out.member_prefix);                                   \
+    break;
+  switch (grid.nb) {
+    BF_GROUPED_CASE(1) BF_GROUPED_CASE(2) BF_GROUPED_CASE(3) BF_GROUPED_CASE(4)
+    BF_GROUPED_CASE(5) BF_GROUPED_CASE(6) BF_GROUPED_CASE(7) BF_GROUPED_CASE(8)
+    default:
+      set_error("exact_weights_grouped_kernel: %d bands not instantiated", grid.nb);
+      return BF_ERR_UNSUPPORTED;
+  }
+#undef BF_GROUPED_CASE
+  BF_CHECK_LAUNCH("exact_weights_grouped_kernel");
+  return BF_OK;
+}
+
+// =========================================================================================
+// (B) split histogram kernel
+// =========================================================================================
+constexpr int kSplitWarps = 20;
+
+// shared memory: hist [hist_doubles] | red [2 NW] | redj [NW] | sscan (NW u32, as NW/2 doubles)
+//   | epart [NW][32] | int tables (see kernel)
+constexpr int kSplitInts = 64 + 64 + 64 + 4 * 32 + 4 * 64 + 32 + 16;
+struct SplitSmem {
+  static __host__ __device__ size_t bytes(int hist_doubles) {
+    return (static_cast<size_t>(hist_doubles) + 4 * kSplitWarps + kSplitWarps * 32) * sizeof(double) +
+           kSplitInts * sizeof(int);
+  }
+};
+
+// lay out one private copy of a class: lane roles, columns and the copy size (in doubles).
+// SLOTS == 1: up to 32 parameters, one chunk per instruction (the hist_window_kernel layout);
+// SLOTS == 2: up to 16 parameters, lanes 0..15 <-> chunk slot 0 with the parameters in order of
+// decreasing range width, lanes 16..31 <-> chunk slot 1 in increasing order; lane 16+j stacks
+// its range on top of lane j's.  A half-warp always touches 16 different stacks.
+// wmin/wmax: ranges by class-local parameter; lparam/lcol by lane; plane[slot*32 + p] = lane.
+__device__ __forceinline__ int layout_class(int slots, int n, const int* wmin, const int* wmax,
+                                            int* lparam, int* lcol, int* plane, int* tmpw,
+                                            int lane) {
+  const int p = slots == 2 ? (lane & 15) : lane;
+  const int sl = slots == 2 ? (lane >> 4) : 0;
+  const bool valid = p < n;
+  const bool occupied = valid && wmin[p] <= wmax[p];
+  const int mn = occupied ? wmin[p] : 0;
+  const int w = occupied ? wmax[p] - wmin[p] + 1 : 1;
+  int rank = 0;
+  const int np = slots == 2 ? 16 : 32;
+  for (int j = 0; j < np; ++j) {
+    const int wj = __shfl_sync(0xffffffffu, w, j);
+    rank += (wj > w || (wj == w && j < p)) ? 1 : 0;
+  }
+  int target;
+  if (slots == 2) target = sl == 0 ? rank : 16 + (15 - rank);
+  else target = rank < 16 ? rank : 47 - rank;
+  tmpw[target] = w;
+  __syncwarp();
+  const int below = target >= 16 ? tmpw[target - 16] : 0;
+  const int depth = __reduce_max_sync(0xffffffffu, lane < 16 ? tmpw[lane] + tmpw[lane + 16] : 0);
+  __syncwarp();
+  lparam[target] = valid ? p : -1;
+  lcol[target] = (below - mn) * 16 + (target & 15);
+  plane[sl * 32 + p] = target;
+  return depth * 16;
+}
+
+struct FastRows {
+  uint2 bins;
+  int4 qa, qb;
+  double w[8];
+};
+
+// rows of one chunk for a fast lane.  ref = (chunk id, index of the chunk's 8 weights / 8)
+__device__ __forceinline__ void load_fast(const bf_param_tables& prm, const double* __restrict__ weights,
+                                          uint2 ref, bool valid, int kf, bool live, bool live_q,
+                                          FastRows& r) {
+  const double2* wp = reinterpret_cast<const double2*>(weights + static_cast<size_t>(ref.y) * BF_CHUNK);
+  double2 a = make_double2(0.0, 0.0), b = a, c = a, d = a;
+  if (valid) {
+    a = __ldg(wp);
+    b = __ldg(wp + 1);
+    c = __ldg(wp + 2);
+    d = __ldg(wp + 3);
+  }
+  r.w[0] = a.x; r.w[1] = a.y; r.w[2] = b.x; r.w[3] = b.y;
+  r.w[4] = c.x; r.w[5] = c.y; r.w[6] = d.x; r.w[7] = d.y;
+  r.bins = make_uint2(0u, 0u);
+  if (live)
+    r.bins = __ldg(reinterpret_cast<const uint2*>(
+        prm.fast_bin + (static_cast<size_t>(ref.x) * prm.fast_pad + kf) * BF_CHUNK));
+  r.qa = make_int4(0, 0, 0, 0);
+  r.qb = r.qa;
+  if (live_q) {
+    const int4* qp = reinterpret_cast<const int4*>(prm.fast_q) +
+                     static_cast<size_t>(ref.x) * 2 * prm.fast_pad + kf;
+    r.qa = __ldg(qp);
+    r.qb = __ldg(qp + prm.fast_pad);
+  }
+}
+
+// four updates of one lane's column at a time: four loads in flight, models that share a bin
+// take the earlier weights along, stores in order (see hist_window_kernel)
+__device__ __forceinline__ void add_four(uint32_t col_s, uint32_t b0, uint32_t b1, uint32_t b2,
+                                         uint32_t b3, double w0, double w1, double w2, double w3) {
+  const uint32_t a0 = col_s + b0 * 128u, a1 = col_s + b1 * 128u, a2 = col_s + b2 * 128u,
+                 a3 = col_s + b3 * 128u;
+  double h0, h1, h2, h3;
+  asm volatile("ld.shared.f64 %0, [%1];" : "=d"(h0) : "r"(a0));
+  asm volatile("ld.shared.f64 %0, [%1];" : "=d"(h1) : "r"(a1));
+  asm volatile("ld.shared.f64 %0, [%1];" : "=d"(h2) : "r"(a2));
+  asm volatile("ld.shared.f64 %0, [%1];" : "=d"(h3) : "r"(a3));
+  double s1 = w1, s2 = w2, s3 = w3;
+  if (a0 == a1) s1 += w0;
+  if (a0 == a2) s2 += w0;
+  if (a1 == a2) s2 += w1;
+  if (a0 == a3) s3 += w0;
+  if (a1 == a3) s3 += w1;
+  if (a2 == a3) s3 += w2;
+  h0 += w0;
+  h1 += s1;
+  h2 += s2;
+  h3 += s3;
+  asm volatile("st.shared.f64 [%0], %1;" ::"r"(a0), "d"(h0));
+  asm volatile("st.shared.f64 [%0], %1;" ::"r"(a1), "d"(h1));
+  asm volatile("st.shared.f64 [%0], %1;" ::"r"(a2), "d"(h2));
+  asm volatile("st.shared.f64 [%0], %1;" ::"r"(a3), "d"(h3));
+}
+
+// A fast warp: chunks first*SLOTS + h, then every nfw*SLOTS-th, of the star's member chunks.
+template <int SLOTS>
+__device__ __forceinline__ double fast_accumulate(const bf_param_tables& prm,
+                                                  const double* __restrict__ weights,
+                                                  const uint2* refs, uint32_t n_mc, uint32_t first,
+                                                  uint32_t nfw, int kf, bool live, bool live_q,
+                                                  int lane, double* col) {
+  const uint32_t h = SLOTS == 2 ? static_cast<uint32_t>(lane >> 4) : 0u;
+  const uint32_t step = nfw * SLOTS;
+  const uint32_t col_s = static_cast<uint32_t>(__cvta_generic_to_shared(col));
+  double eacc = 0.0;
+  uint32_t base = first * SLOTS;  // warp-uniform position of slot 0
+  if (base >= n_mc) return 0.0;
+  // software pipeline: chunk reference two steps ahead, rows one step ahead
+  FastRows cur, nxt;
+  uint32_t i = base + h;
+  bool v1 = i < n_mc;
+  uint2 r1 = refs[v1 ? i : n_mc - 1];
+  load_fast(prm, weights, r1, v1, kf, live, live_q, nxt);
+  bool v2 = false;
+  uint2 r2 = r1;
+  if (base + step < n_mc) {
+    v2 = i + step < n_mc;
+    r2 = refs[v2 ? i + step : n_mc - 1];
+  }
+  while (base < n_mc) {
+    cur = nxt;
+    const uint32_t nb1 = base + step;
+    if (nb1 < n_mc) {
+      load_fast(prm, weights, r2, v2, kf, live, live_q, nxt);
+      const uint32_t nb2 = nb1 + step;
+      if (nb2 < n_mc) {
+        const uint32_t i2 = nb2 + h;
+        v2 = i2 < n_mc;
+        r2 = refs[v2 ? i2 : n_mc - 1];
+      }
+    }
+    const uint32_t bx = cur.bins.x, by = cur.bins.y;
+    add_four(col_s, bx & 0xffu, (bx >> 8) & 0xffu, (bx >> 16) & 0xffu, bx >> 24, cur.w[0], cur.w[1],
+             cur.w[2], cur.w[3]);
+    add_four(col_s, by & 0xffu, (by >> 8) & 0xffu, (by >> 16) & 0xffu, by >> 24, cur.w[4], cur.w[5],
+             cur.w[6], cur.w[7]);
+    if (live_q) {  // non-members carry weight 0
+      eacc += cur.w[0] * static_cast<double>(cur.qa.x);
+      eacc += cur.w[1] * static_cast<double>(cur.qa.y);
+      eacc += cur.w[2] * static_cast<double>(cur.qa.z);
+      eacc += cur.w[3] * static_cast<double>(cur.qa.w);
+      eacc += cur.w[4] * static_cast<double>(cur.qb.x);
+      eacc += cur.w[5] * static_cast<double>(cur.qb.y);
+      eacc += cur.w[6] * static_cast<double>(cur.qb.z);
+      eacc += cur.w[7] * static_cast<double>(cur.qb.w);
+    }
+    base = nb1;
+  }
+  return eacc;
+}
+
+// A slow warp: one update per chunk with the chunk's weight sum, four chunks per step.
+template <int SLOTS>
+__device__ __forceinline__ double slow_accumulate(const bf_param_tables& prm,
+                                                  const double* __restrict__ weights,
+                                                  const uint2* refs, uint32_t n_mc, uint32_t first,
+                                                  uint32_t nsw, int ks, bool live, bool live_q,
+                                                  int lane, double* col) {
+  const uint32_t h = SLOTS == 2 ? static_cast<uint32_t>(lane >> 4) : 0u;
+  const uint32_t step = nsw * SLOTS;
+  const uint32_t col_s = static_cast<uint32_t>(__cvta_generic_to_shared(col));
+  double eacc = 0.0;
+  for (uint32_t base = first * SLOTS; base < n_mc; base += 4 * step) {
+    double ws[4];
+    uint32_t bin[4];
+    int q[4];
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      const uint32_t i = base + u * step + h;
+      const bool valid = i < n_mc;
+      const uint2 ref = refs[valid ? i : n_mc - 1];
+      const double2* wp = reinterpret_cast<const double2*>(weights + static_cast<size_t>(ref.y) * BF_CHUNK);
+      double2 a = make_double2(0.0, 0.0), b = a, c = a, d = a;
+      if (valid) {
+        a = __ldg(wp);
+        b = __ldg(wp + 1);
+        c = __ldg(wp + 2);
+        d = __ldg(wp + 3);
+      }
+      ws[u] = ((a.x + a.y) + (b.x + b.y)) + ((c.x + c.y) + (d.x + d.y));
+      bin[u] = 0;
+      q[u] = 0;
+      if (live) bin[u] = __ldg(prm.slow_bin + static_cast<size_t>(ref.x) * prm.slow_pad + ks);
+      if (live_q) q[u] = __ldg(prm.slow_q + static_cast<size_t>(ref.x) * prm.slow_pad + ks);
+    }
+    add_four(col_s, bin[0], bin[1], bin[2], bin[3], ws[0], ws[1], ws[2], ws[3]);
+    if (live_q) {
+      eacc += ws[0] * static_cast<double>(q[0]);
+      eacc += ws[1] * static_cast<double>(q[1]);
+      eacc += ws[2] * static_cast<double>(q[2]);
+      eacc += ws[3] * static_cast<double>(q[3]);
+    }
+  }
+  return eacc;
+}
+
+// occupied bin range of the class parameters over the star's member chunks
+template <int SLOTS, bool FAST>
+__device__ __forceinline__ void class_ranges(const bf_param_tables& prm, const uint2* refs,
+                                             uint32_t n_mc, int warp, int lane, int n, int* wmin,
+                                             int* wmax) {
+  const uint32_t h = SLOTS == 2 ? static_cast<uint32_t>(lane >> 4) : 0u;
+  const int p = SLOTS == 2 ? (lane & 15) : lane;
+  const bool live = p < n;
+  uint32_t mn2 = 0x00ff00ffu, mx2 = 0;
+  for (uint32_t base = static_cast<uint32_t>(warp) * SLOTS; base < n_mc; base += kSplitWarps * SLOTS) {
+    const uint32_t i = base + h;
+    if (i < n_mc && live) {
+      const uint32_t chunk = refs[i].x;
+      if (FAST) {
+        const uint2 bb = __ldg(reinterpret_cast<const uint2*>(
+            prm.fast_bin + (static_cast<size_t>(chunk) * prm.fast_pad + p) * BF_CHUNK));
+        const uint32_t xe = __byte_perm(bb.x, 0, 0x4240), xo = __byte_perm(bb.x, 0, 0x4341);
+        const uint32_t ye = __byte_perm(bb.y, 0, 0x4240), yo = __byte_perm(bb.y, 0, 0x4341);
+        mn2 = __vimin3_u16x2(__vimin3_u16x2(mn2, xe, xo), ye, yo);
+        mx2 = __vimax3_u16x2(__vimax3_u16x2(mx2, xe, xo), ye, yo);
+      } else {
+        const uint32_t b = __ldg(prm.slow_bin + static_cast<size_t>(chunk) * prm.slow_pad + p);
+        const uint32_t b2 = b | (b << 16);
+        mn2 = __vminu2(mn2, b2);
+        mx2 = __vmaxu2(mx2, b2);
+      }
+    }
+  }
+  if (live) {
+    atomicMin(wmin + p, static_cast<int>(min(mn2 & 0xffffu, mn2 >> 16)));
+    atomicMax(wmax + p, static_cast<int>(max(mx2 & 0xffffu, mx2 >> 16)));
+  }
+}
+
+template <int FS, int SS>  // chunk slots per instruction of the fast / slow class (1 or 2)
+__global__ void __launch_bounds__(kSplitWarps * 32, 1)
+split_hist_kernel(bf_param_tables prm, int hist_doubles, const double* __restrict__ pmax,
+                  const uint32_t* __restrict__ offsets, const uint32_t* __restrict__ list,
+                  const int32_t* __restrict__ star_order, int64_t star_begin, int64_t entry_base,
+                  bf_accum_scratch sc, double p0, double p1, double p2, bf_star_outputs out) {
+  extern __shared__ __align__(16) double smem_d[];
+  constexpr int NW = kSplitWarps;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int nq = prm.n_q, tb = prm.total_bins, nf = prm.n_fast, nsl = prm.n_slow;
+
+  double* hist = smem_d;
+  double* red = hist + hist_doubles;
+  long long* redj = reinterpret_cast<long long*>(red + 2 * NW);
+  uint32_t* sscan = reinterpret_cast<uint32_t*>(redj + NW);
+  double* epart = red + 4 * NW;  // [NW][32]
+  int* wmin = reinterpret_cast<int*>(epart + NW * 32);  // [64]: fast 0..31, slow 32..63
+  int* wmax = wmin + 64;
+  int* kcls = wmax + 64;       // [64] by parameter: class-local index, +32 for slow (n_q <= 64)
+  int* lparam = kcls + 64;     // [2][32] by class and lane: class-local parameter or -1
+  int* lcol = lparam + 64;     // [2][32]
+  int* plane = lcol + 64;      // [2][64] by class, slot*32 + parameter: lane
+  int* tmpw = plane + 128;     // [2][32]
+  int* misc = tmpw + 64;       // [0] n_mc, [1] fast copy, [2] slow copy, [3] fast warps, [4] slow warps
+
+  const int64_t s =
+      star_begin + (star_order ? star_order[blockIdx.x] : static_cast<int64_t>(blockIdx.x));
+  const uint32_t e0 = offsets[s * BF_SELECT_SPLIT];
+  const uint32_t e1 = offsets[(s + 1) * BF_SELECT_SPLIT];
+  const double M = pmax[s];
+  for (int i = threadIdx.x; i < 64; i += blockDim.x) {
+    wmin[i] = 255;
+    wmax[i] = 0;
+  }
+  for (int i = threadIdx.x; i < nf; i += blockDim.x) kcls[prm.fast_k[i]] = i;
+  for (int i = threadIdx.x; i < nsl; i += blockDim.x) kcls[prm.slow_k[i]] = 32 + i;
+
+  // ---- the star's chunks that hold a member: (chunk id, place of its weights) ------------
+  uint2* refs = reinterpret_cast<uint2*>(sc.chunk_refs) + (static_cast<size_t>(e0) - entry_base) * 8;
+  uint32_t carry = 0;
+  for (uint32_t eb = e0; eb < e1; eb += blockDim.x) {
+    const uint32_t e = eb + threadIdx.x;
+    uint32_t occ = 0, g = 0;
+    if (e < e1) {
+      const uint2 mm = *reinterpret_cast<const uint2*>(out.member_mask + static_cast<size_t>(e) * kWordsPerGroup);
+      g = list[e];
+#pragma unroll
+      for (int c = 0; c < 8; ++c)
+        if ((((c < 4 ? mm.x : mm.y) >> (8 * (c & 3))) & 0xffu) != 0) occ |= 1u << c;
+    }
+    const uint32_t v = __popc(occ);
+    uint32_t inc = v;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+      const uint32_t t = __shfl_up_sync(0xffffffffu, inc, d);
+      if (lane >= d) inc += t;
+    }
+    __syncthreads();
+    if (lane == 31) sscan[warp] = inc;
+    __syncthreads();
+    uint32_t woff = 0, tot = 0;
+    for (int w = 0; w < NW; ++w) {
+      if (w < warp) woff += sscan[w];
+      tot += sscan[w];
+    }
+    uint32_t pos = carry + woff + inc - v;
+    const uint32_t wslot = static_cast<uint32_t>((static_cast<int64_t>(e) - entry_base) * 8);
+    while (occ) {
+      const int c = __ffs(occ) - 1;
+      occ &= occ - 1;
+      refs[pos++] = make_uint2(g * 8u + c, wslot + c);
+    }
+    carry += tot;
+  }
+  const uint32_t n_mc = carry;
+  __syncthreads();  // refs (global) and the tables above are visible to the whole block
+
+  // ---- occupied bin ranges -----------------------------------------------------------------
+  if (nf > 0) class_ranges<FS, true>(prm, refs, n_mc, warp, lane, nf, wmin, wmax);
+  if (nsl > 0) class_ranges<SS, false>(prm, refs, n_mc, warp, lane, nsl, wmin + 32, wmax + 32);
+  __syncthreads();
+
+  // ---- layout: warp 0 the fast class, warp 1 the slow class ----------------------------------
+  if (warp == 0) {
+    const int c = layout_class(FS, nf, wmin, wmax, lparam, lcol, plane, tmpw, lane);
+    if (lane == 0) misc[1] = c;
+  } else if (warp == 1) {
+    const int c = layout_class(SS, nsl, wmin + 32, wmax + 32, lparam + 32, lcol + 32, plane + 64,
+                               tmpw + 32, lane);
+    if (lane == 0) misc[2] = c;
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    const int cf = misc[1], cs = misc[2];
+    int F = 0, S = 0;
+    if (nf == 0) {
+      S = hist_doubles / cs;
+      if (S > NW) S = NW;
+    } else if (nsl == 0) {
+      F = hist_doubles / cf;
+      if (F > NW) F = NW;
+    } else {
+      // a slow warp keeps up with about six fast ones
+      for (S = 1; S <= 3; ++S) {
+        F = (hist_doubles - S * cs) / cf;
+        if (F > NW - S) F = NW - S;
+        if (F <= 6 * S || S == 3) break;
+      }
+      if (F < 1) {  // cannot happen: the host checked the worst case
+        F = 1;
+        S = 1;
+      }
+    }
+    misc[3] = F;
+    misc[4] = S;
+  }
+  __syncthreads();
+  const int cf = misc[1], cs = misc[2], F = misc[3], S = misc[4];
+  const int used = F * cf + S * cs;
+  for (int i = threadIdx.x; i < used; i += blockDim.x) hist[i] = 0.0;
+  if (threadIdx.x == 0 && sc.star_flags) sc.star_flags[s - star_begin] = 1;
+  __syncthreads();
+
+  // ---- accumulate ---------------------------------------------------------------------------
+  double eacc = 0.0;
+  if (n_mc > 0) {
+    if (warp < F) {
+      const int kf = lparam[lane];
+      const bool live = kf >= 0;
+      const bool live_q = live && !(prm.q_const && prm.q_const[prm.fast_k[live ? kf : 0]]);
+      eacc = fast_accumulate<FS>(prm, sc.weights, refs, n_mc, warp, F, live ? kf : 0, live, live_q,
+                                 lane, hist + warp * cf + lcol[lane]);
+    } else if (warp < F + S) {
+      const int ks = lparam[32 + lane];
+      const bool live = ks >= 0;
+      const bool live_q = live && !(prm.q_const && prm.q_const[prm.slow_k[live ? ks : 0]]);
+      eacc = slow_accumulate<SS>(prm, sc.weights, refs, n_mc, warp - F, S, live ? ks : 0, live,
+                                 live_q, lane, hist + F * cf + (warp - F) * cs + lcol[32 + lane]);
+    }
+  }
+  epart[warp * 32 + lane] = eacc;
+
+  const double wtot = star_totals(e0, e1, entry_base, sc, M, s, red, redj, out);  // syncs
+  const bool empty = !(wtot > 0.0);
+
+  // ---- expectations of the parameters not taken from the histogram (fit.py:743) -------------
+  for (int k = threadIdx.x; k < nq; k += blockDim.x) {
+    if (prm.q_const && prm.q_const[k]) continue;
+    const int cl = kcls[k];
+    const bool slow = cl >= 32;
+    const int p = cl & 31;
+    const int slots = slow ? SS : FS;
+    const int w0 = slow ? F : 0, nw = slow ? S : F;
+    double e = 0.0;
+    for (int w = 0; w < nw; ++w)
+      for (int sl = 0; sl < slots; ++sl) e += epart[(w0 + w) * 32 + plane[(slow ? 64 : 0) + sl * 32 + p]];
+    out.exp_vals[s * nq + k] = empty ? __longlong_as_double(0x7ff8000000000000LL)
+                                     : prm.q_lin[2 * k] + prm.q_lin[2 * k + 1] * (e / wtot);
+  }
+
+  // ---- merge the private copies (fixed order), normalise; bins outside the range are 0 ------
+  const double inv = empty ? 0.0 : 1.0 / wtot;
+  for (int kq = warp; kq < nq; kq += NW) {
+    const int b0 = prm.bin_off[kq];
+    const int nbk = prm.bin_off[kq + 1] - b0;
+    const int cl = kcls[kq];
+    const bool slow = cl >= 32;
+    const int p = cl & 31;
+    const int mn = wmin[cl];
+    const int width = wmax[cl] >= mn ? wmax[cl] - mn + 1 : 0;
+    const int slots = slow ? SS : FS;
+    const int ncopy = slow ? S : F, csize = slow ? cs : cf;
+    const double* area = hist + (slow ? F * cf : 0);
+    const int* lc = lcol + (slow ? 32 : 0);
+    const int* pl = plane + (slow ? 64 : 0);
+    double* row = out.pdf1d + s * tb + b0;
+    const bool from_bins = prm.q_const && prm.q_const[kq];
+    double eq = 0.0;
+    for (int b = lane; b < nbk; b += 32) {
+      double v = 0.0;
+      if (b >= mn && b < mn + width)
+        for (int w = 0; w < ncopy; ++w)
+          for (int sl = 0; sl < slots; ++sl) v += area[w * csize + lc[pl[sl * 32 + p]] + b * 16];
+      row[b] = v * inv;
+      if (from_bins) eq += v * prm.bin_q[b0 + b];
+    }
+    if (from_bins)
+      store_bin_expectation(eq, wtot, empty, prm.q_lin[2 * kq], out.exp_vals + s * nq + kq, lane);
+  }
+  __syncthreads();  // histograms are consumed: their memory becomes the percentile scratch
+  star_percentiles_and_prefix(prm, s, e0, e1, p0, p1, p2, hist, sscan, out);
+}
+
+static int split_hist_doubles(size_t smem_budget) {
+  if (smem_budget < SplitSmem::bytes(0) + 2048) return 0;
+  return static_cast<int>((smem_budget - 1024 - SplitSmem::bytes(0)) / sizeof(double)) & ~1;
+}
+
+bool split_hist_supported(const bf_param_tables& prm, size_t smem_budget) {
+  if (prm.n_fast + prm.n_slow != prm.n_q || prm.n_q > 64) return false;
+  if (prm.n_fast < 0 || prm.n_fast > 32 || prm.n_slow < 0 || prm.n_slow > 32) return false;
+  if ((prm.n_fast > 0 && !(prm.fast_k && prm.fast_bin && prm.fast_q)) ||
+      (prm.n_slow > 0 && !(prm.slow_k && prm.slow_bin && prm.slow_q)))
+    return false;
+  if ((prm.fast_pad != 16 && prm.fast_pad != 32) || (prm.slow_pad != 16 && prm.slow_pad != 32)) return false;
+  if (prm.n_fast > prm.fast_pad || prm.n_slow > prm.slow_pad) return false;
+  // worst case of one copy of each class: 16 stacks of two full-width ranges
+  const int hd = split_hist_doubles(smem_budget);
+  const int worst = 2 * 32 * prm.max_bins;
+  return hd >= worst && hd >= kSplitWarps * kMaxBinsPerParam;
+}
+
+int launch_split_hist(const bf_param_tables& prm, const double* pmax, const uint32_t* offsets,
+                      const uint32_t* list, const int32_t* star_order, int64_t star_begin,
+                      int64_t n_stars, int64_t entry_base, const bf_accum_scratch& sc, double p0,
+                      double p1, double p2, const bf_star_outputs& out, size_t smem_budget,
+                      cudaStream_t st) {
+  const int hd = split_hist_doubles(smem_budget);
+  const size_t smem = SplitSmem::bytes(hd);
+  const int fs = prm.fast_pad == 16 ? 2 : 1, ss = prm.slow_pad == 16 ? 2 : 1;
+  static bool configured[64][4] = {};
+  int dev = 0;
+  BF_CUDA_TRY(cudaGetDevice(&dev));
+#define BF_SPLIT_CASE(A, B)                                                                    \
+  if (fs == A && ss == B) {                                                                    \
+    if (dev < 64 && !configured[dev][(A - 1) * 2 + (B - 1)]) {                                 \
+      BF_CUDA_TRY(cudaFuncSetAttribute(split_hist_kernel<A, B>,                                \
+                                       cudaFuncAttributeMaxDynamicSharedMemorySize,            \
+                                       static_cast<int>(smem_budget)));                        \
+      BF_CUDA_TRY(cudaFuncSetAttribute(split_hist_kernel<A, B>,                                \
+                                       cudaFuncAttributePreferredSharedMemoryCarveout,         \
+                                       cudaSharedmemCarveoutMaxShared));                       \
+      configured[dev][(A - 1) * 2 + (B - 1)] = true;                                           \
+    }                                                                                          \
+    split_hist_kernel<A, B><<<static_cast<unsigned>(n_stars), kSplitWarps * 32, smem, st>>>(   \
+        prm, hd, pmax, offsets, list, star_order, star_begin, entry_base, sc, p0, p1, p2, out); \
+  }
+  BF_SPLIT_CASE(1, 1)
+  BF_SPLIT_CASE(1, 2)
+  BF_SPLIT_CASE(2, 1)
+  BF_SPLIT_CASE(2, 2)
+#undef BF_SPLIT_CASE
+  BF_CHECK_LAUNCH("split_hist_kernel");
+  return BF_OK;
+}
+
+}  // namespace bf
+
+extern "C" int64_t bf_group_order_work_elems(int64_t n_groups) {
+  if (n_groups <= 0) return 1;
+  // counts [n_groups], offsets [n_groups + 1], scan tile sums
+  return 2 * n_groups + 1 + bf_scan_scratch_elems(n_groups);
+}
+
+extern "C" int bf_group_order(int64_t n_groups, const uint32_t* list, int64_t entry_base,
+                              int64_t n_entries, uint32_t* work, uint32_t* group_order,
+                              void* stream) {
+  using namespace bf;
+  BF_REQUIRE(n_groups > 0 && entry_base >= 0 && n_entries >= 0, "bf_group_order: bad sizes");
+  BF_REQUIRE(list && work && group_order, "bf_group_order: null pointer");
+  BF_REQUIRE(entry_base + n_entries < (1LL << 32), "bf_group_order: list positions exceed 32 bits");
+  if (n_entries == 0) return BF_OK;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  uint32_t* counts = work;
+  uint32_t* goff = work + n_groups;
+  uint32_t* tiles = goff + n_groups + 1;
+  BF_CUDA_TRY(cudaMemsetAsync(counts, 0, static_cast<size_t>(n_groups) * sizeof(uint32_t), st));
+  const int64_t want = (n_entries + 255) / 256;
+  const unsigned blocks = static_cast<unsigned>(want < 8192 ? want : 8192);  // grid-stride
+  group_count_kernel<<<blocks, 256, 0, st>>>(list, entry_base, n_entries, counts);
+  BF_CHECK_LAUNCH("group_count_kernel");
+  const int rc = bf_exclusive_scan_u32(n_groups, counts, goff, tiles, stream);
+  if (rc != BF_OK) return rc;
+  BF_CUDA_TRY(cudaMemsetAsync(counts, 0, static_cast<size_t>(n_groups) * sizeof(uint32_t), st));
+  group_scatter_kernel<<<blocks, 256, 0, st>>>(list, entry_base, n_entries, goff, counts, group_order);
+  BF_CHECK_LAUNCH("group_scatter_kernel");
+  return BF_OK;
+}

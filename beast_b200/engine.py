@@ -80,7 +80,8 @@ class FitEngine:
     gmin_budget_bytes : size cap of the (group x star) minimum map of one batch
     """
 
-    def __init__(self, setup, device=None, gmin_budget_bytes=8 << 30, scratch_budget_bytes=12 << 30):
+    def __init__(self, setup, device=None, gmin_budget_bytes=8 << 30, scratch_budget_bytes=12 << 30,
+                 sparse_pass="split"):
         torch = _torch()
         self.lib = _cabi.load()
         if not torch.cuda.is_available():
@@ -104,10 +105,24 @@ class FitEngine:
             self.d_msb, self.d_ivar = up(s.msb), up(s.ivar)
             self.d_lnq, self.d_lnw = up(s.lnq), up(s.lnw)
             self.d_cov_off = up(s.cov_off) if s.cov_off is not None else None
-            self.d_bin_tab, self.d_q_tab = up(s.bin_tab), up(s.q_tab)
+            split_only = sparse_pass == "split" and s.split_ok
+            # (the per-model tables are only read by the kernels that treat all parameters alike)
+            self.d_bin_tab, self.d_q_tab = (None, None) if split_only else (up(s.bin_tab), up(s.q_tab))
             self.d_bin_off, self.d_bin_val = up(s.bin_off), up(s.bin_val)
             self.d_q_lin = up(s.q_lin)
             self.d_q_const, self.d_bin_q = up(s.q_const), up(s.bin_q)
+            # sparse_pass: "split" = group-ordered weights + class-split histogram kernel (needs
+            # the class tables; falls back when the grid has more than 32 parameters per class),
+            # "legacy" = star-ordered weights + full-width / windowed histogram kernels,
+            # "both" = all tables resident, the kernels chosen per call (tests)
+            if sparse_pass not in ("split", "legacy", "both"):
+                raise ValueError("sparse_pass must be 'split', 'legacy' or 'both'")
+            self.split = sparse_pass != "legacy" and s.split_ok
+            self.sparse_pass = sparse_pass
+            if self.split:
+                self.d_fast_k, self.d_slow_k = up(s.fast_k), up(s.slow_k)
+                self.d_fast_bin, self.d_fast_q = up(s.fast_bin), up(s.fast_q)
+                self.d_slow_bin, self.d_slow_q = up(s.slow_bin), up(s.slow_q)
             self.d_inv_scale = up((1.0 / s.band_scale).astype(np.float64))
             if s.pair_bin is not None:
                 self.d_pair_bin, self.d_pair_off = up(s.pair_bin), up(s.pair_off)
@@ -116,15 +131,25 @@ class FitEngine:
         self.grid = ExactGrid(s.nb, s.n_models, s.ld_model, self.d_msb.data_ptr(),
                               self.d_ivar.data_ptr(), self.d_lnq.data_ptr(), self.d_lnw.data_ptr(),
                               self.d_cov_off.data_ptr() if self.d_cov_off is not None else None)
-        self.params = ParamTables(s.n_q, s.total_bins, s.max_bins, self.d_bin_tab.data_ptr(),
-                                  self.d_q_tab.data_ptr(), self.d_q_lin.data_ptr(),
+        dp = lambda t: t.data_ptr() if t is not None else None  # noqa: E731
+        self.params = ParamTables(s.n_q, s.total_bins, s.max_bins, dp(self.d_bin_tab),
+                                  dp(self.d_q_tab), self.d_q_lin.data_ptr(),
                                   self.d_bin_off.data_ptr(), self.d_bin_val.data_ptr(),
                                   self.d_q_const.data_ptr(), self.d_bin_q.data_ptr())
+        if self.split:
+            p = self.params
+            p.n_fast, p.n_slow = len(s.fast_k), len(s.slow_k)
+            p.fast_pad, p.slow_pad = s.fast_pad, s.slow_pad
+            p.fast_k, p.slow_k = self.d_fast_k.data_ptr(), self.d_slow_k.data_ptr()
+            p.fast_bin, p.fast_q = self.d_fast_bin.data_ptr(), self.d_fast_q.data_ptr()
+            p.slow_bin, p.slow_q = self.d_slow_bin.data_ptr(), self.d_slow_q.data_ptr()
         per_star = s.n_groups * 4
         mb = max(STAR_BLOCK, (gmin_budget_bytes // per_star) // STAR_BLOCK * STAR_BLOCK)
         mb = min(mb, ((2**31 - 1) // max(s.n_groups, 1)) // STAR_BLOCK * STAR_BLOCK, 32768 * STAR_BLOCK)
         self.max_batch = int(max(mb, STAR_BLOCK))
-        self.max_entries = int(max(1 << 16, scratch_budget_bytes // (GROUP * 8 + 24)))
+        # per listed group: 64 weights + partials (+ the group order and the chunk lists)
+        per_entry = GROUP * 8 + 24 + (4 + 64 if self.split else 0)
+        self.max_entries = int(max(1 << 16, scratch_budget_bytes // per_entry))
         self.launches = 0  # kernels launched by this engine (bench.py reports it)
         self._result_cache = {}
         self._copy_stream = torch.cuda.Stream(device=self.device)
@@ -331,6 +356,13 @@ class FitEngine:
             flags = torch.empty(max(b - a for a, b in cuts), dtype=torch.int32, device=dev)
             scr = AccumScratch(w_scr.data_ptr(), p_w.data_ptr(), p_c.data_ptr(), p_j.data_ptr(),
                                flags.data_ptr())
+            use_split = self.split and not getattr(self, "force_legacy", False)
+            if use_split:
+                g_order = torch.empty(max(nmax, 1), dtype=torch.int32, device=dev)
+                c_refs = torch.empty(max(nmax, 1) * 16, dtype=torch.int32, device=dev)
+                g_work = torch.empty(int(self.lib.bf_group_order_work_elems(s.n_groups)),
+                                     dtype=torch.int32, device=dev)
+                scr.group_order, scr.chunk_refs = g_order.data_ptr(), c_refs.data_ptr()
             outs = StarOutputs(o["total_log_norm"].data_ptr(), o["chi2min"].data_ptr(),
                                o["chi2min_j"].data_ptr(), o["n_sparse"].data_ptr(),
                                o["exp_vals"].data_ptr(), o["pdf1d"].data_ptr(),
@@ -348,13 +380,18 @@ class FitEngine:
                 # one block per star in the histogram kernel: longest lists first, so that the
                 # last blocks of the launch are short ones
                 order = torch.argsort(n_listed[a0:b0], descending=True, stable=True).to(torch.int32)
+                if use_split and cnt:
+                    with self._timed("group_order"):
+                        _cabi.call("bf_group_order", s.n_groups, _ptr(lst), base, cnt, _ptr(g_work),
+                                   _ptr(g_order), st)
+                    self.launches += 5
                 with self._timed("accumulate"):
                     _cabi.call("bf_exact_accumulate", C.byref(self.grid), C.byref(self.params),
                                a0, b0 - a0, _ptr(d_flux), _ptr(pmax), float(threshold),
                                _ptr(offsets), _ptr(lst), _ptr(entry_star), _ptr(order), base, cnt,
                                pct, C.byref(scr), C.byref(outs), st,
                                C.c_void_p(self._aux_stream.cuda_stream))
-                self.launches += 3
+                self.launches += 2 if use_split else 3
                 if pdf2d is not None and cnt and not reeval:
                     # 2D PDFs of this range from the weights still in the scratch (fit.py:758-762)
                     with self._timed("pdf2d"):

@@ -299,6 +299,7 @@ class FitSetup:
         self.bin_q = np.zeros(self.total_bins, dtype=np.float64)
         for k in range(nq):
             btab[k, :nm] = self.bins[k].bin_num[g0]
+            btab[k, nm:] = btab[k, nm - 1]  # padding rows repeat the last model (never members)
             col = self.qcols[k][g0]
             lo, hi = float(col.min()), float(col.max())
             scale = (hi - lo) / 4294967294.0
@@ -312,8 +313,10 @@ class FitSetup:
                 occupied = np.zeros(self.bins[k].nbins, dtype=bool)
                 occupied[btab[k, :nm]] = True
                 self.bin_q[self.bin_off[k]:self.bin_off[k + 1]] = np.where(occupied, rep - self.q_lin[k, 0], 0.0)
+            qtab[k, nm:] = qtab[k, nm - 1]
         self.bin_tab = np.ascontiguousarray(btab.reshape(nq, nch, CHUNK).transpose(1, 0, 2))
         self.q_tab = np.ascontiguousarray(qtab.reshape(nq, nch, CHUNK).transpose(1, 0, 2))
+        self._class_split(btab, qtab, nch)
         if self.pairs:
             pb = np.full((len(self.pairs), nmp), -1, dtype=np.int32)
             for p, pair in enumerate(self.pairs):
@@ -324,6 +327,41 @@ class FitSetup:
         else:
             self.pair_bin = None
             self.pair_off = None
+
+    def _class_split(self, btab, qtab, nch):
+        """Tables of the split histogram kernel (csrc/split.cu).
+
+        A parameter is *slow* when its value is the same for the 8 models of every chunk
+        (on a BEAST grid: everything that depends on the stellar model only, since the dust
+        axes run innermost), otherwise *fast*.  Slow parameters take one histogram update and
+        one expectation term per chunk (the chunk's weight sum), fast ones one per model.
+        The split needs at most 32 parameters per class; beyond that the kernels that treat
+        all parameters alike are used."""
+        nq = btab.shape[0]
+        b3 = btab.reshape(nq, nch, CHUNK)
+        q3 = qtab.reshape(nq, nch, CHUNK)
+        slow = np.array([bool((b3[k] == b3[k][:, :1]).all() and (q3[k] == q3[k][:, :1]).all())
+                         for k in range(nq)])
+        self.fast_k = np.flatnonzero(~slow).astype(np.int32)
+        self.slow_k = np.flatnonzero(slow).astype(np.int32)
+        nf, nsl = len(self.fast_k), len(self.slow_k)
+        self.split_ok = nf <= 32 and nsl <= 32
+        self.fast_pad = 16 if nf <= 16 else 32
+        self.slow_pad = 16 if nsl <= 16 else 32
+        if not self.split_ok:
+            self.fast_bin = self.fast_q = self.slow_bin = self.slow_q = None
+            return
+        fb = np.zeros((nch if nf else 1, self.fast_pad, CHUNK), dtype=np.uint8)
+        fq = np.zeros((nch if nf else 1, 2, self.fast_pad, CHUNK // 2), dtype=np.int32)
+        for i, k in enumerate(self.fast_k):
+            fb[:, i, :] = b3[k]
+            fq[:, :, i, :] = q3[k].reshape(nch, 2, CHUNK // 2)
+        sb = np.zeros((nch if nsl else 1, self.slow_pad), dtype=np.uint8)
+        sq = np.zeros((nch if nsl else 1, self.slow_pad), dtype=np.int32)
+        for i, k in enumerate(self.slow_k):
+            sb[:, i] = b3[k][:, 0]
+            sq[:, i] = q3[k][:, 0]
+        self.fast_bin, self.fast_q, self.slow_bin, self.slow_q = fb, fq, sb, sq
 
     @property
     def n_q(self):

@@ -195,6 +195,23 @@ typedef struct {
   const double* bin_val;
   const uint8_t* q_const;
   const double* bin_q;
+  /* Class split for the split histogram kernel (optional: n_fast = n_slow = 0 when absent).
+   * "slow" parameters have one value per chunk (everything that depends on the stellar model
+   * only, when the dust axes run innermost), so they take one histogram update and one
+   * expectation term per chunk, with the chunk's weight sum; "fast" parameters take one per
+   * model.  n_fast + n_slow = n_q, each <= 32; fast_pad / slow_pad = 16 or 32 table lanes.
+   *   fast_k   [n_fast] int32               parameter index of fast slot i (slow_k alike)
+   *   fast_bin [ld_model/8][fast_pad][8] u8 bins of the chunk's models
+   *   fast_q   [ld_model/8][2][fast_pad][4] int32   fixed-point values (q_tab encoding), models
+   *                                         0..3 of all parameters, then models 4..7
+   *   slow_bin [ld_model/8][slow_pad] u8,  slow_q [ld_model/8][slow_pad] int32 */
+  int n_fast, n_slow, fast_pad, slow_pad;
+  const int32_t* fast_k;
+  const int32_t* slow_k;
+  const uint8_t* fast_bin;
+  const int32_t* fast_q;
+  const uint8_t* slow_bin;
+  const int32_t* slow_q;
 } bf_param_tables;
 
 typedef struct {
@@ -219,7 +236,21 @@ typedef struct {
   int32_t* star_flags;  /* [n_stars] or NULL.  Set by the histogram kernel: 1 = it has also
                            written this star's expectations (warps without a private
                            histogram did the sums), so the expectation kernel skips the star */
+  uint32_t* group_order;/* [n_entries] or NULL: the list positions of this range ordered by group
+                           id (bf_group_order).  When given (diagonal noise model, <= 12 bands)
+                           the exact weights are evaluated group by group, so that a group's
+                           model rows are fetched once for all the stars that list it */
+  uint32_t* chunk_refs; /* [n_entries][8][2] or NULL: room for the per-star lists of chunks that
+                           hold a member, built and consumed by the split histogram kernel
+                           (used when given and `params` carries the class split) */
 } bf_accum_scratch;
+
+/* Order the list positions [entry_base, entry_base + n_entries) by group id (counting sort
+ * with device atomics; the order inside a group is not defined and does not matter).
+ * work : >= bf_group_order_work_elems(n_groups) uint32 of scratch.  group_order: out [n_entries]. */
+int64_t bf_group_order_work_elems(int64_t n_groups);
+int bf_group_order(int64_t n_groups, const uint32_t* list, int64_t entry_base, int64_t n_entries,
+                   uint32_t* work, uint32_t* group_order, void* stream);
 
 /* Sparse pass: exact sparse set, weights, normalisation, chi2min, expectations, 1D PDFs
  * and p16/p50/p84 (fit.py:670-755) for stars [star_begin, star_begin + n_stars) of the

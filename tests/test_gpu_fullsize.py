@@ -24,7 +24,7 @@ def c2():
     with warnings.catch_warnings():
         warnings.simplefilter("ignore")
         setup = FitSetup(g, nz, list(keys), max_nbins=200)
-    eng = FitEngine(setup)
+    eng = FitEngine(setup, sparse_pass="both")
     res = eng.fit(obs.fluxes, threshold=-10.0, sparse=500, lnp_rng="device", seed=7)
     return g, nz, obs, keys, setup, eng, res
 
@@ -113,3 +113,27 @@ def test_full_size_histogram_kernels_agree(c2, monkeypatch):
         diff = np.abs(res.per_vals[:, k, :] - alt.per_vals[:, k, :])
         assert np.all(diff <= width), k
         assert np.mean(diff > 1e-6 * width) < 2e-3, (k, float(np.mean(diff > 1e-6 * width)))
+
+
+def test_full_size_split_and_legacy_kernels_agree(c2):
+    """C2 size: group-ordered weights + class-split histograms (the default) against star-ordered
+    weights + the windowed histogram kernel"""
+    g, nz, obs, keys, setup, eng, res = c2
+    assert eng.split
+    eng.force_legacy = True
+    try:
+        alt = eng.fit(obs.fluxes, threshold=-10.0, sparse=500, lnp_rng="device", seed=7)
+    finally:
+        eng.force_legacy = False
+    for name in ("Pmax", "Pmax_j", "chi2min", "chi2min_j", "n_sparse", "sparse_j", "sparse_lnp",
+                 "total_log_norm"):
+        np.testing.assert_array_equal(getattr(res, name), getattr(alt, name), err_msg=name)
+    np.testing.assert_allclose(res.pdf1d, alt.pdf1d, rtol=1e-11, atol=1e-300)
+    for k in range(setup.n_q):
+        col = setup.qcols[k][setup.g0_indxs]
+        span = float(col.max() - col.min())
+        np.testing.assert_allclose(res.exp_vals[:, k], alt.exp_vals[:, k], rtol=1e-12,
+                                   atol=1e-9 * span + 1e-300, err_msg=f"Exp {k}")
+        a, b = setup.bin_off[k], setup.bin_off[k + 1]
+        width = util.bin_width_tolerance(setup.bin_val[a:b])
+        assert np.all(np.abs(res.per_vals[:, k, :] - alt.per_vals[:, k, :]) <= width), k

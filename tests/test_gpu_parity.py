@@ -17,7 +17,8 @@ def _engine(g, nz, args):
                      pdf2d_param_list=args["pdf2d_param_list"],
                      make_pdf2d=args["pdf2d_param_list"] is not None,
                      do_not_normalize=args["do_not_normalize"])
-    return setup, FitEngine(setup)
+    # all parameter tables resident: BF_HIST / BF_WEIGHTS / force_legacy then choose the kernels
+    return setup, FitEngine(setup, sparse_pass="both")
 
 
 @pytest.mark.parametrize("case", util.GOLDEN_CASES)
@@ -167,3 +168,63 @@ def test_pdf2d_entry_points_agree():
     b = eng.fit(obs.fluxes, threshold=args["threshold"], want_pdf2d=True, sparse="all")
     util.compare_to_reference(setup, b, ref, n_pdf2d=len(setup.pairs))
     np.testing.assert_allclose(a.pdf2d, b.pdf2d, rtol=1e-12, atol=1e-300)
+
+
+def _same_everything(a, b, names):
+    for name in names:
+        np.testing.assert_array_equal(getattr(a, name), getattr(b, name), err_msg=name)
+
+
+ALL_OUT = ("Pmax", "Pmax_j", "total_log_norm", "chi2min", "chi2min_j", "n_sparse", "pdf1d", "exp_vals",
+           "per_vals", "sparse_j", "sparse_lnp", "sparse_chi2")
+
+
+def test_group_ordered_weights_are_bit_identical(monkeypatch):
+    """the exact weights evaluated group by group (rows in registers, stars of the group in turn)
+    and star by star are the same operations on the same numbers: every output bit agrees"""
+    g, nz, obs, args, ref = util.load_golden("small_thr10")
+    setup, eng = _engine(g, nz, args)
+    assert eng.split
+    a = eng.fit(obs.fluxes, threshold=args["threshold"], sparse="all")
+    monkeypatch.setenv("BF_WEIGHTS", "star")
+    b = eng.fit(obs.fluxes, threshold=args["threshold"], sparse="all")
+    _same_everything(a, b, ALL_OUT)
+
+
+@pytest.mark.parametrize("nbins", [50, 200])
+def test_split_histogram_kernel_against_oracle_and_legacy(nbins):
+    """the class-split histogram kernel (slow parameters once per chunk, fast ones two chunks per
+    instruction) against the oracle, and against the kernels that treat all parameters alike"""
+    from beast_b200 import synth
+    from oracle import fit_oracle as fo
+
+    g, nz, obs = synth.make_config("C1", nstars=40, seed=5)
+    keys = fo.default_keys(g)
+    want = fo.fit_all(obs.fluxes, fo.OracleSetup(g, nz, keys, max_nbins=nbins), threshold=-10.0, fast=True)
+    args = dict(keys=keys, max_nbins=nbins, pdf2d_param_list=None, do_not_normalize=False)
+    setup, eng = _engine(g, nz, args)
+    assert eng.split and len(setup.fast_k) > 0 and len(setup.slow_k) > 0
+    res = eng.fit(obs.fluxes, threshold=-10.0, sparse="all")
+    util.compare_to_reference(setup, res, want)
+    eng.force_legacy = True
+    old = eng.fit(obs.fluxes, threshold=-10.0, sparse="all")
+    _same_everything(res, old, ("Pmax", "Pmax_j", "chi2min", "chi2min_j", "n_sparse", "sparse_j",
+                                "sparse_lnp", "total_log_norm"))
+    np.testing.assert_allclose(res.pdf1d, old.pdf1d, rtol=1e-11, atol=1e-300)
+    span = np.array([c[setup.g0_indxs].max() - c[setup.g0_indxs].min() for c in setup.qcols])
+    assert np.all(np.abs(res.exp_vals - old.exp_vals) <= 1e-12 * np.abs(old.exp_vals) + 1e-9 * span)
+
+
+def test_split_kernel_with_one_class_only():
+    """parameter lists that are all fast (dust axes) or all slow (stellar axes)"""
+    from oracle import fit_oracle as fo
+
+    g, nz, obs, args, ref = util.load_golden("small_thr10")
+    for keys in (["Av", "Rv", "f_A"], ["M_ini", "logA", "Z", "logT"]):
+        a = dict(args, keys=keys)
+        want = fo.fit_all(obs.fluxes, fo.OracleSetup(g, nz, keys, max_nbins=a["max_nbins"]),
+                          threshold=a["threshold"], fast=True)
+        setup, eng = _engine(g, nz, a)
+        assert eng.split
+        res = eng.fit(obs.fluxes, threshold=a["threshold"], sparse="all")
+        util.compare_to_reference(setup, res, want)
