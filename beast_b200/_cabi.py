@@ -75,6 +75,8 @@ class AccumScratch(C.Structure):
         ("star_flags", c_void_p),
         ("group_order", c_void_p),
         ("chunk_refs", c_void_p),
+        ("chunk_wsum", c_void_p),
+        ("exp_part", c_void_p),
     ]
 
 

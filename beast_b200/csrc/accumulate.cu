@@ -840,6 +840,17 @@ extern "C" int bf_exact_accumulate(const bf_exact_grid* grid, const bf_param_tab
     BF_CUDA_TRY(cudaDeviceGetAttribute(&sm_count[dev], cudaDevAttrMultiProcessorCount, dev));
     smem_limit[dev] = optin;
   }
+  // The class-split histogram kernel needs the class tables, room for the chunk lists and the
+  // by-products of the group-ordered weights kernel (chunk sums, expectation partials of the
+  // fast class); BF_HIST=full|window and BF_WEIGHTS=star select the other kernels.
+  const char* hist_env = getenv("BF_HIST");
+  const char* wenv = getenv("BF_WEIGHTS");
+  const bool grouped = scratch->group_order != nullptr && grid->cov_off == nullptr && grid->nb <= 8 &&
+                       !(wenv && wenv[0] == 's') && !getenv("BF_WEIGHTS_GENERIC");
+  const bool want_split = grouped && scratch->chunk_refs && scratch->chunk_wsum &&
+                          (scratch->exp_part || params->n_fast == 0) &&
+                          split_hist_supported(*params, static_cast<size_t>(smem_limit[dev])) &&
+                          !(hist_env && (hist_env[0] == 'f' || hist_env[0] == 'w'));
   if (n_entries > 0) {
     const int64_t blocks = (n_entries + kWeightWarps - 1) / kWeightWarps;
     BF_REQUIRE(blocks < (1LL << 31), "bf_exact_accumulate: too many list entries in one call");
@@ -850,14 +861,13 @@ extern "C" int bf_exact_accumulate(const bf_exact_grid* grid, const bf_param_tab
     int nbk = grid->cov_off == nullptr && grid->nb <= 12 ? grid->nb : 0;
     if (getenv("BF_WEIGHTS_GENERIC")) nbk = 0;  // measurements
     // with the list positions ordered by group the rows of a group are fetched once for all
-    // its stars (BF_WEIGHTS=star keeps the star-ordered kernel, for measurements and tests)
-    const char* wenv = getenv("BF_WEIGHTS");
-    // (two models' rows per lane: up to 8 bands fit the register file without spills)
-    const bool grouped = scratch->group_order != nullptr && nbk > 0 && nbk <= 8 &&
-                         !(wenv && wenv[0] == 's');
+    // its stars (two models' rows per lane: up to 8 bands fit the register file without spills)
     if (grouped) {
       const int rc = launch_weights_grouped(*grid, flux64, pmax, threshold, list, entry_star,
-                                            entry_base, n_entries, *scratch, *out, sm_count[dev], st);
+                                            entry_base, n_entries, *scratch,
+                                            want_split ? params->fast_q : nullptr,
+                                            want_split && params->n_fast > 0 ? params->fast_pad : 0,
+                                            *out, sm_count[dev], st);
       if (rc != BF_OK) return rc;
     } else {
 #define BF_WEIGHTS_CASE(N)                                                                      \
@@ -895,7 +905,6 @@ extern "C" int bf_exact_accumulate(const bf_exact_grid* grid, const bf_param_tab
   }
   // wide bin tables leave the full-width layout few warps: use the windowed kernel there
   // (BF_HIST=full|window overrides the choice, for measurements and tests)
-  const char* hist_env = getenv("BF_HIST");
   const size_t wbytes_total = budget - 1024;
   const int hist_doubles = static_cast<int>(
       (wbytes_total - WindowSmem::bytes(0, rounds)) / sizeof(double)) & ~1;
@@ -907,9 +916,7 @@ extern "C" int bf_exact_accumulate(const bf_exact_grid* grid, const bf_param_tab
   if (hist_env && hist_env[0] == 'w') use_window = window_fits;
   // the class-split kernel needs the class tables, room for the chunk lists and, like the
   // windowed kernel, one worst-case private copy per class; it does every expectation itself
-  const bool use_split = scratch->chunk_refs != nullptr && split_hist_supported(*params, budget) &&
-                         !(hist_env && (hist_env[0] == 'f' || hist_env[0] == 'w'));
-  if (use_split) {
+  if (want_split) {
     const int rc = launch_split_hist(*params, pmax, offsets, list, star_order, star_begin, n_stars,
                                      entry_base, *scratch, percentiles_host[0], percentiles_host[1],
                                      percentiles_host[2], *out, budget, st);

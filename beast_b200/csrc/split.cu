@@ -73,7 +73,56 @@ __device__ __forceinline__ bool warp_min_chi2(bool member, double chi2, int lane
   return true;
 }
 
-template <int NB>
+// Per-warp shared memory of the grouped kernel when it also forms the expectation partials of
+// the fast parameters: the weights of up to 8 list positions (A operand) and the group's
+// fixed-point parameter values (B operand) of the FP64 tensor-core products below.
+constexpr int kWtLd = BF_GROUP + 4;  // row pitch of the weight tile: conflict-free fragments
+template <int NT>
+struct GroupedSmem {
+  static constexpr int kLdq = NT * 8 + 4;
+  static constexpr size_t kWarpBytes =
+      NT == 0 ? 0 : 8 * kWtLd * sizeof(double) + BF_GROUP * kLdq * sizeof(int32_t) + 8 * sizeof(int32_t);
+};
+
+// D[8 list positions][8 parameters] += A[8][4 models] * B[4 models][8 parameters]  (FP64 tensor core)
+__device__ __forceinline__ void dmma_8x8x4(double& c0, double& c1, double a, double b) {
+  asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};"
+               : "+d"(c0), "+d"(c1)
+               : "d"(a), "d"(b));
+}
+
+// sum_m w_m * fix_m[k] (fit.py:743) for the pending list positions of a warp: rows of wt are
+// list positions, qg holds the group's 64 x (NT*8) fixed-point values
+template <int NT>
+__device__ __forceinline__ void flush_expectations(const double* wt, const int32_t* qg,
+                                                   const int32_t* slots, int pending,
+                                                   double* __restrict__ exp_part, int lane) {
+  constexpr int kLdq = GroupedSmem<NT>::kLdq;
+  __syncwarp();
+  double acc[NT][2];
+#pragma unroll
+  for (int n = 0; n < NT; ++n) acc[n][0] = acc[n][1] = 0.0;
+  const int r = lane >> 2, c = lane & 3;
+#pragma unroll 4
+  for (int t = 0; t < BF_GROUP / 4; ++t) {
+    const double a = wt[r * kWtLd + 4 * t + c];
+#pragma unroll
+    for (int n = 0; n < NT; ++n) {
+      const double b = static_cast<double>(qg[(4 * t + c) * kLdq + n * 8 + r]);
+      dmma_8x8x4(acc[n][0], acc[n][1], a, b);
+    }
+  }
+  if (r < pending) {
+    double* dst = exp_part + static_cast<size_t>(slots[r]) * (NT * 8) + c * 2;
+#pragma unroll
+    for (int n = 0; n < NT; ++n)
+      *reinterpret_cast<double2*>(dst + n * 8) = make_double2(acc[n][0], acc[n][1]);
+  }
+  __syncwarp();
+}
+
+// NT: 8-parameter tiles of the fast class whose expectation partials are formed here (0: none)
+template <int NB, int NT>
 __global__ void __launch_bounds__(kGroupedWarps * 32, 2)
 exact_weights_grouped_kernel(bf_exact_grid grid, const double* __restrict__ flux64,
                              const double* __restrict__ pmax, double threshold,
@@ -81,9 +130,16 @@ exact_weights_grouped_kernel(bf_exact_grid grid, const double* __restrict__ flux
                              const uint32_t* __restrict__ entry_star,
                              const uint32_t* __restrict__ order, int64_t entry_base,
                              int64_t n_entries, bf_accum_scratch sc,
+                             const int32_t* __restrict__ fast_q,
                              uint32_t* __restrict__ member_mask,
                              uint32_t* __restrict__ member_prefix) {
+  extern __shared__ __align__(16) unsigned char grouped_smem[];
   const int lane = threadIdx.x & 31;
+  constexpr int kLdq = GroupedSmem<NT>::kLdq;
+  unsigned char* mine = grouped_smem + (threadIdx.x >> 5) * GroupedSmem<NT>::kWarpBytes;
+  double* wt = reinterpret_cast<double*>(mine);
+  int32_t* qg = reinterpret_cast<int32_t*>(wt + 8 * kWtLd);
+  int32_t* slots = qg + BF_GROUP * kLdq;
   const int64_t n_stretch = (n_entries + kOrderStretch - 1) / kOrderStretch;
   for (int64_t st = static_cast<int64_t>(blockIdx.x) * kGroupedWarps + (threadIdx.x >> 5);
        st < n_stretch; st += static_cast<int64_t>(gridDim.x) * kGroupedWarps) {
@@ -94,6 +150,7 @@ exact_weights_grouped_kernel(bf_exact_grid grid, const double* __restrict__ flux
     double lq0 = 0.0, lw0 = 0.0, lq1 = 0.0, lw1 = 0.0;
     bool ok0 = false, ok1 = false;
     int64_t j0 = 0;
+    int pending = 0;  // list positions whose weights wait in wt for the expectation products
     for (int64_t blk = i0; blk < i1; blk += 32) {
       const int cnt = static_cast<int>(i1 - blk < 32 ? i1 - blk : 32);
       // every lane fetches the description of one list position of this block of 32
@@ -115,6 +172,23 @@ exact_weights_grouped_kernel(bf_exact_grid grid, const double* __restrict__ flux
 #pragma unroll
         for (int b = 0; b < NB; ++b) f[b] = __ldg(sflux + b);
         if (g != cur_g) {  // warp-uniform: the rows of the next group
+          if constexpr (NT > 0) {
+            if (pending) flush_expectations<NT>(wt, qg, slots, pending, sc.exp_part, lane);
+            pending = 0;
+            // fast_q rows of the group: [8 chunks][2][pad][4] int32 -> qg[model][parameter]
+            const int4* src = reinterpret_cast<const int4*>(fast_q) +
+                              static_cast<size_t>(g) * (BF_GROUP / 4) * (NT * 8);
+#pragma unroll
+            for (int it = 0; it < NT * 4; ++it) {
+              const int v = lane + 32 * it;
+              const int4 q4 = __ldg(src + v);
+              const int quad = v / (NT * 8), p = v % (NT * 8);
+              qg[(quad * 4 + 0) * kLdq + p] = q4.x;
+              qg[(quad * 4 + 1) * kLdq + p] = q4.y;
+              qg[(quad * 4 + 2) * kLdq + p] = q4.z;
+              qg[(quad * 4 + 3) * kLdq + p] = q4.w;
+            }
+          }
           cur_g = g;
           j0 = static_cast<int64_t>(g) * BF_GROUP + lane;
           ok0 = j0 < grid.n_models;
@@ -155,11 +229,26 @@ exact_weights_grouped_kernel(bf_exact_grid grid, const double* __restrict__ flux
         const int64_t slot = static_cast<int64_t>(e) - entry_base;
         sc.weights[slot * BF_GROUP + lane] = w0;
         sc.weights[slot * BF_GROUP + 32 + lane] = w1;
-        // group partials: weight sum in the order of exact_weights_kernel (word 0 then word 1
-        // per lane, then the butterfly), chi2 minimum with the lowest index on ties
-        double wsum = w0 + w1;
+        if constexpr (NT > 0) {
+          wt[pending * kWtLd + lane] = w0;
+          wt[pending * kWtLd + 32 + lane] = w1;
+          if (lane == 0) slots[pending] = static_cast<int32_t>(slot);
+        }
+        // weight sums of the 8 chunks (8 neighbouring lanes each), then of the group
+        double s0 = w0, s1 = w1;
 #pragma unroll
-        for (int d = 16; d > 0; d >>= 1) wsum += __shfl_xor_sync(0xffffffffu, wsum, d);
+        for (int d = 1; d < 8; d <<= 1) {
+          s0 += __shfl_xor_sync(0xffffffffu, s0, d);
+          s1 += __shfl_xor_sync(0xffffffffu, s1, d);
+        }
+        if (sc.chunk_wsum && (lane & 7) == 0) {
+          sc.chunk_wsum[slot * 8 + (lane >> 3)] = s0;
+          sc.chunk_wsum[slot * 8 + 4 + (lane >> 3)] = s1;
+        }
+        double wsum = s0 + s1;
+        wsum += __shfl_xor_sync(0xffffffffu, wsum, 8);
+        wsum += __shfl_xor_sync(0xffffffffu, wsum, 16);
+        // chi2 minimum of the members, lowest index on ties (fit.py:725-726)
         double c0 = 0.0, c1 = 0.0;
         int l0 = 0, l1 = 0;
         const bool h0 = warp_min_chi2(mem0, a0, lane, c0, l0);
@@ -182,48 +271,86 @@ exact_weights_grouped_kernel(bf_exact_grid grid, const double* __restrict__ flux
           sc.part_chi2_j[slot] = cj;
           member_prefix[e] = __popc(mw0) + __popc(mw1);
         }
+        if constexpr (NT > 0) {
+          if (++pending == 8) {
+            flush_expectations<NT>(wt, qg, slots, pending, sc.exp_part, lane);
+            pending = 0;
+          }
+        }
       }
+    }
+    if constexpr (NT > 0) {
+      if (pending) flush_expectations<NT>(wt, qg, slots, pending, sc.exp_part, lane);
     }
   }
 }
 
+template <int NB, int NT>
+static int launch_grouped_inst(const bf_exact_grid& grid, const double* flux64, const double* pmax,
+                               double threshold, const uint32_t* list, const uint32_t* entry_star,
+                               int64_t entry_base, int64_t n_entries, const bf_accum_scratch& sc,
+                               const int32_t* fast_q, const bf_star_outputs& out, unsigned gridx,
+                               cudaStream_t st) {
+  const size_t smem = kGroupedWarps * GroupedSmem<NT>::kWarpBytes;
+  static bool configured[64] = {};
+  int dev = 0;
+  BF_CUDA_TRY(cudaGetDevice(&dev));
+  if (smem > 48 * 1024 && dev >= 0 && dev < 64 && !configured[dev]) {
+    BF_CUDA_TRY(cudaFuncSetAttribute(exact_weights_grouped_kernel<NB, NT>,
+                                     cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                     static_cast<int>(smem)));
+    configured[dev] = true;
+  }
+  exact_weights_grouped_kernel<NB, NT><<<gridx, kGroupedWarps * 32, smem, st>>>(
+      grid, flux64, pmax, threshold, list, entry_star, sc.group_order, entry_base, n_entries, sc,
+      fast_q, out.member_mask, out.member_prefix);
+  BF_CHECK_LAUNCH("exact_weights_grouped_kernel");
+  return BF_OK;
+}
+
+// fast_pad: 0 = weights only; 16 / 32 = also the expectation partials of the fast class
+// (needs sc.exp_part and prm_fast_q)
 int launch_weights_grouped(const bf_exact_grid& grid, const double* flux64, const double* pmax,
                            double threshold, const uint32_t* list, const uint32_t* entry_star,
                            int64_t entry_base, int64_t n_entries, const bf_accum_scratch& sc,
-                           const bf_star_outputs& out, int sm_count, cudaStream_t st) {
+                           const int32_t* fast_q, int fast_pad, const bf_star_outputs& out,
+                           int sm_count, cudaStream_t st) {
   const int64_t n_stretch = (n_entries + kOrderStretch - 1) / kOrderStretch;
   const int64_t blocks = (n_stretch + kGroupedWarps - 1) / kGroupedWarps;
   const int64_t cap = static_cast<int64_t>(sm_count) * 64;
   const unsigned gridx = static_cast<unsigned>(blocks < cap ? blocks : cap);
-#define BF_GROUPED_CASE(N)                                                                    \
-  case N:                                                                                     \
-    exact_weights_grouped_kernel<N><<<gridx, kGroupedWarps * 32, 0, st>>>(                    \
-        grid, flux64, pmax, threshold, list, entry_star, sc.group_order, entry_base,          \
-        n_entries, sc, out.member_mask, out.member_prefix);                                   \
-    break;
+#define BF_GROUPED_CASE(N)                                                                        \
+  case N:                                                                                         \
+    if (fast_pad == 16)                                                                           \
+      return launch_grouped_inst<N, 2>(grid, flux64, pmax, threshold, list, entry_star,           \
+                                       entry_base, n_entries, sc, fast_q, out, gridx, st);        \
+    if (fast_pad == 32)                                                                           \
+      return launch_grouped_inst<N, 4>(grid, flux64, pmax, threshold, list, entry_star,           \
+                                       entry_base, n_entries, sc, fast_q, out, gridx, st);        \
+    return launch_grouped_inst<N, 0>(grid, flux64, pmax, threshold, list, entry_star, entry_base, \
+                                     n_entries, sc, fast_q, out, gridx, st);
   switch (grid.nb) {
     BF_GROUPED_CASE(1) BF_GROUPED_CASE(2) BF_GROUPED_CASE(3) BF_GROUPED_CASE(4)
     BF_GROUPED_CASE(5) BF_GROUPED_CASE(6) BF_GROUPED_CASE(7) BF_GROUPED_CASE(8)
     default:
-      set_error("exact_weights_grouped_kernel: %d bands not instantiated", grid.nb);
-      return BF_ERR_UNSUPPORTED;
+      break;
   }
 #undef BF_GROUPED_CASE
-  BF_CHECK_LAUNCH("exact_weights_grouped_kernel");
-  return BF_OK;
+  set_error("exact_weights_grouped_kernel: %d bands not instantiated", grid.nb);
+  return BF_ERR_UNSUPPORTED;
 }
 
 // =========================================================================================
 // (B) split histogram kernel
 // =========================================================================================
-constexpr int kSplitWarps = 20;
+constexpr int kSplitWarpsMax = 20;
 
 // shared memory: hist [hist_doubles] | red [2 NW] | redj [NW] | sscan (NW u32, as NW/2 doubles)
-//   | epart [NW][32] | int tables (see kernel)
-constexpr int kSplitInts = 64 + 64 + 64 + 4 * 32 + 4 * 64 + 32 + 16;
+//   | epart [NW][32] | int tables (see kernel); sized for the largest block
+constexpr int kSplitInts = 3 * 64 + 2 * 64 + 128 + 64 + 16;
 struct SplitSmem {
   static __host__ __device__ size_t bytes(int hist_doubles) {
-    return (static_cast<size_t>(hist_doubles) + 4 * kSplitWarps + kSplitWarps * 32) * sizeof(double) +
+    return (static_cast<size_t>(hist_doubles) + 4 * kSplitWarpsMax + kSplitWarpsMax * 32) * sizeof(double) +
            kSplitInts * sizeof(int);
   }
 };
@@ -265,14 +392,12 @@ __device__ __forceinline__ int layout_class(int slots, int n, const int* wmin, c
 
 struct FastRows {
   uint2 bins;
-  int4 qa, qb;
   double w[8];
 };
 
 // rows of one chunk for a fast lane.  ref = (chunk id, index of the chunk's 8 weights / 8)
 __device__ __forceinline__ void load_fast(const bf_param_tables& prm, const double* __restrict__ weights,
-                                          uint2 ref, bool valid, int kf, bool live, bool live_q,
-                                          FastRows& r) {
+                                          uint2 ref, bool valid, int kf, bool live, FastRows& r) {
   const double2* wp = reinterpret_cast<const double2*>(weights + static_cast<size_t>(ref.y) * BF_CHUNK);
   double2 a = make_double2(0.0, 0.0), b = a, c = a, d = a;
   if (valid) {
@@ -287,14 +412,6 @@ __device__ __forceinline__ void load_fast(const bf_param_tables& prm, const doub
   if (live)
     r.bins = __ldg(reinterpret_cast<const uint2*>(
         prm.fast_bin + (static_cast<size_t>(ref.x) * prm.fast_pad + kf) * BF_CHUNK));
-  r.qa = make_int4(0, 0, 0, 0);
-  r.qb = r.qa;
-  if (live_q) {
-    const int4* qp = reinterpret_cast<const int4*>(prm.fast_q) +
-                     static_cast<size_t>(ref.x) * 2 * prm.fast_pad + kf;
-    r.qa = __ldg(qp);
-    r.qb = __ldg(qp + prm.fast_pad);
-  }
 }
 
 // four updates of one lane's column at a time: four loads in flight, models that share a bin
@@ -325,67 +442,109 @@ __device__ __forceinline__ void add_four(uint32_t col_s, uint32_t b0, uint32_t b
   asm volatile("st.shared.f64 [%0], %1;" ::"r"(a3), "d"(h3));
 }
 
+__device__ __forceinline__ void add_chunk(uint32_t col_s, const FastRows& r) {
+  const uint32_t bx = r.bins.x, by = r.bins.y;
+  add_four(col_s, bx & 0xffu, (bx >> 8) & 0xffu, (bx >> 16) & 0xffu, bx >> 24, r.w[0], r.w[1], r.w[2],
+           r.w[3]);
+  add_four(col_s, by & 0xffu, (by >> 8) & 0xffu, (by >> 16) & 0xffu, by >> 24, r.w[4], r.w[5], r.w[6],
+           r.w[7]);
+}
+
 // A fast warp: chunks first*SLOTS + h, then every nfw*SLOTS-th, of the star's member chunks.
+// Software pipeline in registers: the chunk reference is read four steps ahead, the rows (8 bin
+// bytes + 8 weights) three steps ahead of their use, so that three steps' rows are in flight
+// per warp -- the loop waits on L2 / HBM, not on shared memory.
 template <int SLOTS>
-__device__ __forceinline__ double fast_accumulate(const bf_param_tables& prm,
-                                                  const double* __restrict__ weights,
-                                                  const uint2* refs, uint32_t n_mc, uint32_t first,
-                                                  uint32_t nfw, int kf, bool live, bool live_q,
-                                                  int lane, double* col) {
+__device__ __forceinline__ void fast_accumulate(const bf_param_tables& prm,
+                                                const double* __restrict__ weights, const uint2* refs,
+                                                uint32_t n_mc, uint32_t first, uint32_t nfw, int kf,
+                                                bool live, int lane, double* col) {
   const uint32_t h = SLOTS == 2 ? static_cast<uint32_t>(lane >> 4) : 0u;
   const uint32_t step = nfw * SLOTS;
   const uint32_t col_s = static_cast<uint32_t>(__cvta_generic_to_shared(col));
-  double eacc = 0.0;
-  uint32_t base = first * SLOTS;  // warp-uniform position of slot 0
-  if (base >= n_mc) return 0.0;
-  // software pipeline: chunk reference two steps ahead, rows one step ahead
-  FastRows cur, nxt;
-  uint32_t i = base + h;
-  bool v1 = i < n_mc;
-  uint2 r1 = refs[v1 ? i : n_mc - 1];
-  load_fast(prm, weights, r1, v1, kf, live, live_q, nxt);
-  bool v2 = false;
-  uint2 r2 = r1;
-  if (base + step < n_mc) {
-    v2 = i + step < n_mc;
-    r2 = refs[v2 ? i + step : n_mc - 1];
-  }
-  while (base < n_mc) {
-    cur = nxt;
-    const uint32_t nb1 = base + step;
-    if (nb1 < n_mc) {
-      load_fast(prm, weights, r2, v2, kf, live, live_q, nxt);
-      const uint32_t nb2 = nb1 + step;
-      if (nb2 < n_mc) {
-        const uint32_t i2 = nb2 + h;
-        v2 = i2 < n_mc;
-        r2 = refs[v2 ? i2 : n_mc - 1];
-      }
+  const uint32_t start = first * SLOTS;  // warp-uniform position of slot 0
+  if (start >= n_mc) return;
+  const uint32_t n_steps = (n_mc - start + step - 1) / step;
+  // reference of step t (clamped; the flag says whether this lane's slot exists)
+  auto ref_of = [&](uint32_t t, bool& valid) {
+    const uint32_t i = start + t * step + h;
+    valid = t < n_steps && i < n_mc;
+    return refs[valid ? i : n_mc - 1];
+  };
+  FastRows r0, r1, r2;
+  bool v;
+  uint2 ref = ref_of(0, v);
+  load_fast(prm, weights, ref, v, kf, live, r0);
+  ref = ref_of(1, v);
+  load_fast(prm, weights, ref, v, kf, live, r1);
+  ref = ref_of(2, v);
+  load_fast(prm, weights, ref, v, kf, live, r2);
+  bool vn;
+  uint2 refn = ref_of(3, vn);
+  for (uint32_t t = 0; t < n_steps; t += 3) {
+    // step t uses r0; its replacement (step t+3) is requested before the shared-memory work
+    {
+      const uint2 rr = refn;
+      const bool vv = vn;
+      refn = ref_of(t + 4, vn);
+      FastRows nx;
+      load_fast(prm, weights, rr, vv, kf, live, nx);
+      add_chunk(col_s, r0);
+      r0 = nx;
     }
-    const uint32_t bx = cur.bins.x, by = cur.bins.y;
-    add_four(col_s, bx & 0xffu, (bx >> 8) & 0xffu, (bx >> 16) & 0xffu, bx >> 24, cur.w[0], cur.w[1],
-             cur.w[2], cur.w[3]);
-    add_four(col_s, by & 0xffu, (by >> 8) & 0xffu, (by >> 16) & 0xffu, by >> 24, cur.w[4], cur.w[5],
-             cur.w[6], cur.w[7]);
-    if (live_q) {  // non-members carry weight 0
-      eacc += cur.w[0] * static_cast<double>(cur.qa.x);
-      eacc += cur.w[1] * static_cast<double>(cur.qa.y);
-      eacc += cur.w[2] * static_cast<double>(cur.qa.z);
-      eacc += cur.w[3] * static_cast<double>(cur.qa.w);
-      eacc += cur.w[4] * static_cast<double>(cur.qb.x);
-      eacc += cur.w[5] * static_cast<double>(cur.qb.y);
-      eacc += cur.w[6] * static_cast<double>(cur.qb.z);
-      eacc += cur.w[7] * static_cast<double>(cur.qb.w);
+    if (t + 1 < n_steps) {
+      const uint2 rr = refn;
+      const bool vv = vn;
+      refn = ref_of(t + 5, vn);
+      FastRows nx;
+      load_fast(prm, weights, rr, vv, kf, live, nx);
+      add_chunk(col_s, r1);
+      r1 = nx;
     }
-    base = nb1;
+    if (t + 2 < n_steps) {
+      const uint2 rr = refn;
+      const bool vv = vn;
+      refn = ref_of(t + 6, vn);
+      FastRows nx;
+      load_fast(prm, weights, rr, vv, kf, live, nx);
+      add_chunk(col_s, r2);
+      r2 = nx;
+    }
   }
-  return eacc;
 }
 
-// A slow warp: one update per chunk with the chunk's weight sum, four chunks per step.
+// A slow warp: one update per chunk with the chunk's weight sum (written by the grouped weights
+// kernel), four chunks per step; values of the next step are requested before this step's
+// shared-memory work.  Returns this lane's sum of wsum * fix (fit.py:743).
+struct SlowRows {
+  double ws[4];
+  uint32_t bin[4];
+  int q[4];
+};
+
+template <int SLOTS>
+__device__ __forceinline__ void load_slow(const bf_param_tables& prm, const double* __restrict__ chunk_wsum,
+                                          const uint2* refs, uint32_t n_mc, uint32_t base, uint32_t step,
+                                          uint32_t h, int ks, bool live, bool live_q, SlowRows& r) {
+  uint2 ref[4];
+  bool valid[4];
+#pragma unroll
+  for (int u = 0; u < 4; ++u) {
+    const uint32_t i = base + u * step + h;
+    valid[u] = base + u * step < n_mc && i < n_mc;
+    ref[u] = refs[valid[u] ? i : n_mc - 1];
+  }
+#pragma unroll
+  for (int u = 0; u < 4; ++u) {
+    r.ws[u] = valid[u] ? __ldg(chunk_wsum + ref[u].y) : 0.0;
+    r.bin[u] = live ? __ldg(prm.slow_bin + static_cast<size_t>(ref[u].x) * prm.slow_pad + ks) : 0u;
+    r.q[u] = live_q ? __ldg(prm.slow_q + static_cast<size_t>(ref[u].x) * prm.slow_pad + ks) : 0;
+  }
+}
+
 template <int SLOTS>
 __device__ __forceinline__ double slow_accumulate(const bf_param_tables& prm,
-                                                  const double* __restrict__ weights,
+                                                  const double* __restrict__ chunk_wsum,
                                                   const uint2* refs, uint32_t n_mc, uint32_t first,
                                                   uint32_t nsw, int ks, bool live, bool live_q,
                                                   int lane, double* col) {
@@ -393,98 +552,97 @@ __device__ __forceinline__ double slow_accumulate(const bf_param_tables& prm,
   const uint32_t step = nsw * SLOTS;
   const uint32_t col_s = static_cast<uint32_t>(__cvta_generic_to_shared(col));
   double eacc = 0.0;
-  for (uint32_t base = first * SLOTS; base < n_mc; base += 4 * step) {
-    double ws[4];
-    uint32_t bin[4];
-    int q[4];
-#pragma unroll
-    for (int u = 0; u < 4; ++u) {
-      const uint32_t i = base + u * step + h;
-      const bool valid = i < n_mc;
-      const uint2 ref = refs[valid ? i : n_mc - 1];
-      const double2* wp = reinterpret_cast<const double2*>(weights + static_cast<size_t>(ref.y) * BF_CHUNK);
-      double2 a = make_double2(0.0, 0.0), b = a, c = a, d = a;
-      if (valid) {
-        a = __ldg(wp);
-        b = __ldg(wp + 1);
-        c = __ldg(wp + 2);
-        d = __ldg(wp + 3);
-      }
-      ws[u] = ((a.x + a.y) + (b.x + b.y)) + ((c.x + c.y) + (d.x + d.y));
-      bin[u] = 0;
-      q[u] = 0;
-      if (live) bin[u] = __ldg(prm.slow_bin + static_cast<size_t>(ref.x) * prm.slow_pad + ks);
-      if (live_q) q[u] = __ldg(prm.slow_q + static_cast<size_t>(ref.x) * prm.slow_pad + ks);
-    }
-    add_four(col_s, bin[0], bin[1], bin[2], bin[3], ws[0], ws[1], ws[2], ws[3]);
+  uint32_t base = first * SLOTS;
+  if (base >= n_mc) return 0.0;
+  SlowRows cur, nxt;
+  load_slow<SLOTS>(prm, chunk_wsum, refs, n_mc, base, step, h, ks, live, live_q, nxt);
+  while (base < n_mc) {
+    cur = nxt;
+    const uint32_t nb1 = base + 4 * step;
+    if (nb1 < n_mc) load_slow<SLOTS>(prm, chunk_wsum, refs, n_mc, nb1, step, h, ks, live, live_q, nxt);
+    add_four(col_s, cur.bin[0], cur.bin[1], cur.bin[2], cur.bin[3], cur.ws[0], cur.ws[1], cur.ws[2],
+             cur.ws[3]);
     if (live_q) {
-      eacc += ws[0] * static_cast<double>(q[0]);
-      eacc += ws[1] * static_cast<double>(q[1]);
-      eacc += ws[2] * static_cast<double>(q[2]);
-      eacc += ws[3] * static_cast<double>(q[3]);
+      eacc += cur.ws[0] * static_cast<double>(cur.q[0]);
+      eacc += cur.ws[1] * static_cast<double>(cur.q[1]);
+      eacc += cur.ws[2] * static_cast<double>(cur.q[2]);
+      eacc += cur.ws[3] * static_cast<double>(cur.q[3]);
     }
+    base = nb1;
   }
   return eacc;
 }
 
-// occupied bin range of the class parameters over the star's member chunks
+// occupied bin range of the class parameters over the star's member chunks (four chunks per
+// lane in flight: this walk waits on L2 only)
 template <int SLOTS, bool FAST>
 __device__ __forceinline__ void class_ranges(const bf_param_tables& prm, const uint2* refs,
-                                             uint32_t n_mc, int warp, int lane, int n, int* wmin,
-                                             int* wmax) {
+                                             uint32_t n_mc, int warp, int nw, int lane, int n,
+                                             int* wmin, int* wmax) {
   const uint32_t h = SLOTS == 2 ? static_cast<uint32_t>(lane >> 4) : 0u;
   const int p = SLOTS == 2 ? (lane & 15) : lane;
   const bool live = p < n;
+  if (!live) return;
   uint32_t mn2 = 0x00ff00ffu, mx2 = 0;
-  for (uint32_t base = static_cast<uint32_t>(warp) * SLOTS; base < n_mc; base += kSplitWarps * SLOTS) {
-    const uint32_t i = base + h;
-    if (i < n_mc && live) {
-      const uint32_t chunk = refs[i].x;
-      if (FAST) {
-        const uint2 bb = __ldg(reinterpret_cast<const uint2*>(
-            prm.fast_bin + (static_cast<size_t>(chunk) * prm.fast_pad + p) * BF_CHUNK));
-        const uint32_t xe = __byte_perm(bb.x, 0, 0x4240), xo = __byte_perm(bb.x, 0, 0x4341);
-        const uint32_t ye = __byte_perm(bb.y, 0, 0x4240), yo = __byte_perm(bb.y, 0, 0x4341);
+  const uint32_t step = static_cast<uint32_t>(nw) * SLOTS;
+  for (uint32_t base = static_cast<uint32_t>(warp) * SLOTS + h; base < n_mc; base += 4 * step) {
+    uint32_t chunk[4];
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      const uint32_t i = base + u * step;
+      chunk[u] = refs[i < n_mc ? i : base].x;  // (a repeated chunk changes nothing)
+    }
+    if (FAST) {
+      uint2 bb[4];
+#pragma unroll
+      for (int u = 0; u < 4; ++u)
+        bb[u] = __ldg(reinterpret_cast<const uint2*>(
+            prm.fast_bin + (static_cast<size_t>(chunk[u]) * prm.fast_pad + p) * BF_CHUNK));
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        const uint32_t xe = __byte_perm(bb[u].x, 0, 0x4240), xo = __byte_perm(bb[u].x, 0, 0x4341);
+        const uint32_t ye = __byte_perm(bb[u].y, 0, 0x4240), yo = __byte_perm(bb[u].y, 0, 0x4341);
         mn2 = __vimin3_u16x2(__vimin3_u16x2(mn2, xe, xo), ye, yo);
         mx2 = __vimax3_u16x2(__vimax3_u16x2(mx2, xe, xo), ye, yo);
-      } else {
-        const uint32_t b = __ldg(prm.slow_bin + static_cast<size_t>(chunk) * prm.slow_pad + p);
-        const uint32_t b2 = b | (b << 16);
-        mn2 = __vminu2(mn2, b2);
-        mx2 = __vmaxu2(mx2, b2);
       }
+    } else {
+      uint32_t b[4];
+#pragma unroll
+      for (int u = 0; u < 4; ++u)
+        b[u] = __ldg(prm.slow_bin + static_cast<size_t>(chunk[u]) * prm.slow_pad + p);
+      const uint32_t p01 = b[0] | (b[1] << 16), p23 = b[2] | (b[3] << 16);
+      mn2 = __vimin3_u16x2(mn2, p01, p23);
+      mx2 = __vimax3_u16x2(mx2, p01, p23);
     }
   }
-  if (live) {
-    atomicMin(wmin + p, static_cast<int>(min(mn2 & 0xffffu, mn2 >> 16)));
-    atomicMax(wmax + p, static_cast<int>(max(mx2 & 0xffffu, mx2 >> 16)));
-  }
+  atomicMin(wmin + p, static_cast<int>(min(mn2 & 0xffffu, mn2 >> 16)));
+  atomicMax(wmax + p, static_cast<int>(max(mx2 & 0xffffu, mx2 >> 16)));
 }
 
 template <int FS, int SS>  // chunk slots per instruction of the fast / slow class (1 or 2)
-__global__ void __launch_bounds__(kSplitWarps * 32, 1)
+__global__ void __launch_bounds__(kSplitWarpsMax * 32, 1)
 split_hist_kernel(bf_param_tables prm, int hist_doubles, const double* __restrict__ pmax,
                   const uint32_t* __restrict__ offsets, const uint32_t* __restrict__ list,
                   const int32_t* __restrict__ star_order, int64_t star_begin, int64_t entry_base,
                   bf_accum_scratch sc, double p0, double p1, double p2, bf_star_outputs out) {
   extern __shared__ __align__(16) double smem_d[];
-  constexpr int NW = kSplitWarps;
+  const int NW = blockDim.x >> 5;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int nq = prm.n_q, tb = prm.total_bins, nf = prm.n_fast, nsl = prm.n_slow;
 
   double* hist = smem_d;
   double* red = hist + hist_doubles;
-  long long* redj = reinterpret_cast<long long*>(red + 2 * NW);
-  uint32_t* sscan = reinterpret_cast<uint32_t*>(redj + NW);
-  double* epart = red + 4 * NW;  // [NW][32]
-  int* wmin = reinterpret_cast<int*>(epart + NW * 32);  // [64]: fast 0..31, slow 32..63
+  long long* redj = reinterpret_cast<long long*>(red + 2 * kSplitWarpsMax);
+  uint32_t* sscan = reinterpret_cast<uint32_t*>(redj + kSplitWarpsMax);
+  double* epart = red + 4 * kSplitWarpsMax;  // [NW][32]
+  int* wmin = reinterpret_cast<int*>(epart + kSplitWarpsMax * 32);  // [64]: fast 0..31, slow 32..63
   int* wmax = wmin + 64;
   int* kcls = wmax + 64;       // [64] by parameter: class-local index, +32 for slow (n_q <= 64)
   int* lparam = kcls + 64;     // [2][32] by class and lane: class-local parameter or -1
   int* lcol = lparam + 64;     // [2][32]
   int* plane = lcol + 64;      // [2][64] by class, slot*32 + parameter: lane
   int* tmpw = plane + 128;     // [2][32]
-  int* misc = tmpw + 64;       // [0] n_mc, [1] fast copy, [2] slow copy, [3] fast warps, [4] slow warps
+  int* misc = tmpw + 64;       // [1] fast copy, [2] slow copy, [3] fast warps, [4] slow warps
 
   const int64_t s =
       star_begin + (star_order ? star_order[blockIdx.x] : static_cast<int64_t>(blockIdx.x));
@@ -539,8 +697,8 @@ split_hist_kernel(bf_param_tables prm, int hist_doubles, const double* __restric
   __syncthreads();  // refs (global) and the tables above are visible to the whole block
 
   // ---- occupied bin ranges -----------------------------------------------------------------
-  if (nf > 0) class_ranges<FS, true>(prm, refs, n_mc, warp, lane, nf, wmin, wmax);
-  if (nsl > 0) class_ranges<SS, false>(prm, refs, n_mc, warp, lane, nsl, wmin + 32, wmax + 32);
+  if (nf > 0) class_ranges<FS, true>(prm, refs, n_mc, warp, NW, lane, nf, wmin, wmax);
+  if (nsl > 0) class_ranges<SS, false>(prm, refs, n_mc, warp, NW, lane, nsl, wmin + 32, wmax + 32);
   __syncthreads();
 
   // ---- layout: warp 0 the fast class, warp 1 the slow class ----------------------------------
@@ -561,19 +719,19 @@ split_hist_kernel(bf_param_tables prm, int hist_doubles, const double* __restric
       if (S > NW) S = NW;
     } else if (nsl == 0) {
       F = hist_doubles / cf;
-      if (F > NW) F = NW;
     } else {
-      // a slow warp keeps up with about six fast ones
-      for (S = 1; S <= 3; ++S) {
-        F = (hist_doubles - S * cs) / cf;
-        if (F > NW - S) F = NW - S;
-        if (F <= 6 * S || S == 3) break;
+      // a slow warp moves a sixteenth of what a fast warp moves per chunk: one is enough up to
+      // a dozen fast warps
+      S = 1;
+      F = (hist_doubles - cs) / cf;
+      if (F > 12 && (hist_doubles - 2 * cs) / cf >= 12 && NW > 15) {
+        S = 2;
+        F = (hist_doubles - 2 * cs) / cf;
       }
-      if (F < 1) {  // cannot happen: the host checked the worst case
-        F = 1;
-        S = 1;
-      }
+      if (F < 1) F = 1;  // cannot happen: the host checked the worst case
     }
+    // two warps always stay free for the expectation partials of the fast class
+    if (nf > 0 && F > NW - S - 2) F = NW - S - 2;
     misc[3] = F;
     misc[4] = S;
   }
@@ -590,15 +748,33 @@ split_hist_kernel(bf_param_tables prm, int hist_doubles, const double* __restric
     if (warp < F) {
       const int kf = lparam[lane];
       const bool live = kf >= 0;
-      const bool live_q = live && !(prm.q_const && prm.q_const[prm.fast_k[live ? kf : 0]]);
-      eacc = fast_accumulate<FS>(prm, sc.weights, refs, n_mc, warp, F, live ? kf : 0, live, live_q,
-                                 lane, hist + warp * cf + lcol[lane]);
+      fast_accumulate<FS>(prm, sc.weights, refs, n_mc, warp, F, live ? kf : 0, live, lane,
+                          hist + warp * cf + lcol[lane]);
     } else if (warp < F + S) {
       const int ks = lparam[32 + lane];
       const bool live = ks >= 0;
       const bool live_q = live && !(prm.q_const && prm.q_const[prm.slow_k[live ? ks : 0]]);
-      eacc = slow_accumulate<SS>(prm, sc.weights, refs, n_mc, warp - F, S, live ? ks : 0, live,
+      eacc = slow_accumulate<SS>(prm, sc.chunk_wsum, refs, n_mc, warp - F, S, live ? ks : 0, live,
                                  live_q, lane, hist + F * cf + (warp - F) * cs + lcol[32 + lane]);
+    } else if (nf > 0) {
+      // warps without a private copy add up the expectation partials of the fast class that
+      // the grouped weights kernel left per list position: lane <-> (parameter, part)
+      const int pad = prm.fast_pad;
+      const int per = 32 / pad;  // list positions per warp instruction
+      const int p = lane % pad, sub = lane / pad;
+      const uint32_t stride = static_cast<uint32_t>(NW - F - S) * per;
+      const double* src = sc.exp_part + p;
+      double acc8[8];
+#pragma unroll
+      for (int u = 0; u < 8; ++u) acc8[u] = 0.0;
+      for (uint32_t e = e0 + (warp - F - S) * per + sub; e < e1; e += 8 * stride) {
+#pragma unroll
+        for (int u = 0; u < 8; ++u) {  // eight rows in flight per lane
+          const uint32_t eu = e + u * stride;
+          if (eu < e1) acc8[u] += __ldg(src + (static_cast<size_t>(eu) - entry_base) * pad);
+        }
+      }
+      eacc = ((acc8[0] + acc8[1]) + (acc8[2] + acc8[3])) + ((acc8[4] + acc8[5]) + (acc8[6] + acc8[7]));
     }
   }
   epart[warp * 32 + lane] = eacc;
@@ -607,16 +783,20 @@ split_hist_kernel(bf_param_tables prm, int hist_doubles, const double* __restric
   const bool empty = !(wtot > 0.0);
 
   // ---- expectations of the parameters not taken from the histogram (fit.py:743) -------------
+  const int nx = NW - F - S;
   for (int k = threadIdx.x; k < nq; k += blockDim.x) {
     if (prm.q_const && prm.q_const[k]) continue;
     const int cl = kcls[k];
-    const bool slow = cl >= 32;
-    const int p = cl & 31;
-    const int slots = slow ? SS : FS;
-    const int w0 = slow ? F : 0, nw = slow ? S : F;
     double e = 0.0;
-    for (int w = 0; w < nw; ++w)
-      for (int sl = 0; sl < slots; ++sl) e += epart[(w0 + w) * 32 + plane[(slow ? 64 : 0) + sl * 32 + p]];
+    if (cl >= 32) {
+      const int p = cl & 31;
+      for (int w = 0; w < S; ++w)
+        for (int sl = 0; sl < SS; ++sl) e += epart[(F + w) * 32 + plane[64 + sl * 32 + p]];
+    } else {
+      const int pad = prm.fast_pad;
+      for (int w = 0; w < nx; ++w)
+        for (int sub = 0; sub < 32 / pad; ++sub) e += epart[(F + S + w) * 32 + sub * pad + cl];
+    }
     out.exp_vals[s * nq + k] = empty ? __longlong_as_double(0x7ff8000000000000LL)
                                      : prm.q_lin[2 * k] + prm.q_lin[2 * k + 1] * (e / wtot);
   }
@@ -659,6 +839,13 @@ static int split_hist_doubles(size_t smem_budget) {
   return static_cast<int>((smem_budget - 1024 - SplitSmem::bytes(0)) / sizeof(double)) & ~1;
 }
 
+// worst case of one copy of each class: 16 stacks of two full-width ranges; the percentile
+// scratch of every warp must fit too
+static bool split_fits(const bf_param_tables& prm, size_t smem, int warps) {
+  const int hd = split_hist_doubles(smem);
+  return hd >= 2 * 32 * prm.max_bins && hd >= warps * kMaxBinsPerParam;
+}
+
 bool split_hist_supported(const bf_param_tables& prm, size_t smem_budget) {
   if (prm.n_fast + prm.n_slow != prm.n_q || prm.n_q > 64) return false;
   if (prm.n_fast < 0 || prm.n_fast > 32 || prm.n_slow < 0 || prm.n_slow > 32) return false;
@@ -667,10 +854,7 @@ bool split_hist_supported(const bf_param_tables& prm, size_t smem_budget) {
     return false;
   if ((prm.fast_pad != 16 && prm.fast_pad != 32) || (prm.slow_pad != 16 && prm.slow_pad != 32)) return false;
   if (prm.n_fast > prm.fast_pad || prm.n_slow > prm.slow_pad) return false;
-  // worst case of one copy of each class: 16 stacks of two full-width ranges
-  const int hd = split_hist_doubles(smem_budget);
-  const int worst = 2 * 32 * prm.max_bins;
-  return hd >= worst && hd >= kSplitWarps * kMaxBinsPerParam;
+  return split_fits(prm, smem_budget, kSplitWarpsMax);
 }
 
 int launch_split_hist(const bf_param_tables& prm, const double* pmax, const uint32_t* offsets,
@@ -678,7 +862,16 @@ int launch_split_hist(const bf_param_tables& prm, const double* pmax, const uint
                       int64_t n_stars, int64_t entry_base, const bf_accum_scratch& sc, double p0,
                       double p1, double p2, const bf_star_outputs& out, size_t smem_budget,
                       cudaStream_t st) {
-  const int hd = split_hist_doubles(smem_budget);
+  // two blocks of 10 warps per SM when a worst-case star fits half the shared memory: two
+  // stars' phases (chunk list, ranges, accumulation, percentiles) then overlap on an SM;
+  // otherwise one block of 20 warps.  BF_SPLIT_WARPS=10|20 overrides (measurements).
+  const size_t half = (smem_budget + 1024) / 2 - 1024;
+  int warps = split_fits(prm, half, kSplitWarpsMax / 2) ? kSplitWarpsMax / 2 : kSplitWarpsMax;
+  if (const char* env = getenv("BF_SPLIT_WARPS")) {
+    if (env[0] == '2') warps = kSplitWarpsMax;
+    if (env[0] == '1' && split_fits(prm, half, kSplitWarpsMax / 2)) warps = kSplitWarpsMax / 2;
+  }
+  const int hd = split_hist_doubles(warps == kSplitWarpsMax ? smem_budget : half);
   const size_t smem = SplitSmem::bytes(hd);
   const int fs = prm.fast_pad == 16 ? 2 : 1, ss = prm.slow_pad == 16 ? 2 : 1;
   static bool configured[64][4] = {};
@@ -695,7 +888,7 @@ int launch_split_hist(const bf_param_tables& prm, const double* pmax, const uint
                                        cudaSharedmemCarveoutMaxShared));                       \
       configured[dev][(A - 1) * 2 + (B - 1)] = true;                                           \
     }                                                                                          \
-    split_hist_kernel<A, B><<<static_cast<unsigned>(n_stars), kSplitWarps * 32, smem, st>>>(   \
+    split_hist_kernel<A, B><<<static_cast<unsigned>(n_stars), warps * 32, smem, st>>>(         \
         prm, hd, pmax, offsets, list, star_order, star_begin, entry_base, sc, p0, p1, p2, out); \
   }
   BF_SPLIT_CASE(1, 1)

@@ -148,7 +148,7 @@ class FitEngine:
         mb = min(mb, ((2**31 - 1) // max(s.n_groups, 1)) // STAR_BLOCK * STAR_BLOCK, 32768 * STAR_BLOCK)
         self.max_batch = int(max(mb, STAR_BLOCK))
         # per listed group: 64 weights + partials (+ the group order and the chunk lists)
-        per_entry = GROUP * 8 + 24 + (4 + 64 if self.split else 0)
+        per_entry = GROUP * 8 + 24 + (4 + 64 + 64 + 8 * s.fast_pad if self.split else 0)
         self.max_entries = int(max(1 << 16, scratch_budget_bytes // per_entry))
         self.launches = 0  # kernels launched by this engine (bench.py reports it)
         self._result_cache = {}
@@ -362,7 +362,10 @@ class FitEngine:
                 c_refs = torch.empty(max(nmax, 1) * 16, dtype=torch.int32, device=dev)
                 g_work = torch.empty(int(self.lib.bf_group_order_work_elems(s.n_groups)),
                                      dtype=torch.int32, device=dev)
+                c_wsum = torch.empty(max(nmax, 1) * 8, dtype=torch.float64, device=dev)
+                e_part = torch.empty(max(nmax, 1) * s.fast_pad, dtype=torch.float64, device=dev)
                 scr.group_order, scr.chunk_refs = g_order.data_ptr(), c_refs.data_ptr()
+                scr.chunk_wsum, scr.exp_part = c_wsum.data_ptr(), e_part.data_ptr()
             outs = StarOutputs(o["total_log_norm"].data_ptr(), o["chi2min"].data_ptr(),
                                o["chi2min_j"].data_ptr(), o["n_sparse"].data_ptr(),
                                o["exp_vals"].data_ptr(), o["pdf1d"].data_ptr(),

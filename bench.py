@@ -51,6 +51,8 @@ def parse_args():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--pdf2d", action="store_true", help="also build 2D PDFs for Av, M_ini, logT (config C4)")
     ap.add_argument("--cpu-stars-per-core", type=int, default=2)
+    ap.add_argument("--sparse-pass", default="split", choices=["split", "legacy", "both"],
+                    help="kernels of the sparse pass (FitEngine sparse_pass); measurements")
     return ap.parse_args()
 
 
@@ -222,7 +224,7 @@ def run_ours(args, rank, world, local_rank):
     t0 = time.perf_counter()
     p2d = ["Av", "M_ini", "logT"] if args.pdf2d else None
     setup = FitSetup(g, nz, keys, max_nbins=args.max_nbins, pdf2d_param_list=p2d, make_pdf2d=args.pdf2d)
-    eng = FitEngine(setup, device=dev, gmin_budget_bytes=24 << 30)
+    eng = FitEngine(setup, device=dev, gmin_budget_bytes=24 << 30, sparse_pass=args.sparse_pass)
     setup_s = time.perf_counter() - t0
     nm = setup.n_models
     fluxes = np.ascontiguousarray(obs.fluxes)

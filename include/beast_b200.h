@@ -241,8 +241,14 @@ typedef struct {
                            the exact weights are evaluated group by group, so that a group's
                            model rows are fetched once for all the stars that list it */
   uint32_t* chunk_refs; /* [n_entries][8][2] or NULL: room for the per-star lists of chunks that
-                           hold a member, built and consumed by the split histogram kernel
-                           (used when given and `params` carries the class split) */
+                           hold a member, built and consumed by the split histogram kernel */
+  double* chunk_wsum;   /* [n_entries][8] or NULL: weight sum of each chunk, written by the
+                           group-ordered weights kernel for the slow parameters */
+  double* exp_part;     /* [n_entries][fast_pad] or NULL: sum_m w_m * fix_m[k] of each listed
+                           group for the fast parameters (FP64 tensor-core products in the
+                           group-ordered weights kernel).  The split histogram kernel runs when
+                           group_order, chunk_refs, chunk_wsum and exp_part are all given and
+                           `params` carries the class split */
 } bf_accum_scratch;
 
 /* Order the list positions [entry_base, entry_base + n_entries) by group id (counting sort
