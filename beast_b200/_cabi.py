@@ -63,6 +63,7 @@ class ParamTables(C.Structure):
         ("fast_q", c_void_p),
         ("slow_bin", c_void_p),
         ("slow_q", c_void_p),
+        ("slow_run", c_void_p),
     ]
 
 

@@ -121,8 +121,8 @@ __device__ __forceinline__ void star_percentiles_and_prefix(const bf_param_table
 int launch_weights_grouped(const bf_exact_grid& grid, const double* flux64, const double* pmax,
                            double threshold, const uint32_t* list, const uint32_t* entry_star,
                            int64_t entry_base, int64_t n_entries, const bf_accum_scratch& sc,
-                           const int32_t* fast_q, int fast_pad, const bf_star_outputs& out,
-                           int sm_count, cudaStream_t st);
+                           const int32_t* fast_q, int fast_pad, const uint8_t* slow_run,
+                           const bf_star_outputs& out, int sm_count, cudaStream_t st);
 // class-split histogram kernel: histograms, percentiles and all expectations
 bool split_hist_supported(const bf_param_tables& prm, size_t smem_budget);
 int launch_split_hist(const bf_param_tables& prm, const double* pmax, const uint32_t* offsets,

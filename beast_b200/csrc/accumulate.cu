@@ -867,7 +867,8 @@ extern "C" int bf_exact_accumulate(const bf_exact_grid* grid, const bf_param_tab
                                             entry_base, n_entries, *scratch,
                                             want_split ? params->fast_q : nullptr,
                                             want_split && params->n_fast > 0 ? params->fast_pad : 0,
-                                            *out, sm_count[dev], st);
+                                            want_split ? params->slow_run : nullptr, *out,
+                                            sm_count[dev], st);
       if (rc != BF_OK) return rc;
     } else {
 #define BF_WEIGHTS_CASE(N)                                                                      \

@@ -131,6 +131,7 @@ exact_weights_grouped_kernel(bf_exact_grid grid, const double* __restrict__ flux
                              const uint32_t* __restrict__ order, int64_t entry_base,
                              int64_t n_entries, bf_accum_scratch sc,
                              const int32_t* __restrict__ fast_q,
+                             const uint8_t* __restrict__ slow_run,
                              uint32_t* __restrict__ member_mask,
                              uint32_t* __restrict__ member_prefix) {
   extern __shared__ __align__(16) unsigned char grouped_smem[];
@@ -151,6 +152,7 @@ exact_weights_grouped_kernel(bf_exact_grid grid, const double* __restrict__ flux
     bool ok0 = false, ok1 = false;
     int64_t j0 = 0;
     int pending = 0;  // list positions whose weights wait in wt for the expectation products
+    uint32_t run_bits = 0xffu;  // chunks of the group that start a run of equal slow values
     for (int64_t blk = i0; blk < i1; blk += 32) {
       const int cnt = static_cast<int>(i1 - blk < 32 ? i1 - blk : 32);
       // every lane fetches the description of one list position of this block of 32
@@ -190,6 +192,7 @@ exact_weights_grouped_kernel(bf_exact_grid grid, const double* __restrict__ flux
             }
           }
           cur_g = g;
+          run_bits = slow_run ? (__ldg(slow_run + g) | 1u) : 0xffu;
           j0 = static_cast<int64_t>(g) * BF_GROUP + lane;
           ok0 = j0 < grid.n_models;
           ok1 = j0 + 32 < grid.n_models;
@@ -241,9 +244,22 @@ exact_weights_grouped_kernel(bf_exact_grid grid, const double* __restrict__ flux
           s0 += __shfl_xor_sync(0xffffffffu, s0, d);
           s1 += __shfl_xor_sync(0xffffffffu, s1, d);
         }
-        if (sc.chunk_wsum && (lane & 7) == 0) {
-          sc.chunk_wsum[slot * 8 + (lane >> 3)] = s0;
-          sc.chunk_wsum[slot * 8 + 4 + (lane >> 3)] = s1;
+        if (sc.chunk_wsum) {
+          // lane c (< 8) takes chunk c's sum, then adds the later chunks of its run: the sum of
+          // a run of equal slow values sits at the run's first chunk, 0 at the others
+          const double t0 = __shfl_sync(0xffffffffu, s0, (lane & 3) * 8);
+          const double t1 = __shfl_sync(0xffffffffu, s1, (lane & 3) * 8);
+          const double cs = (lane & 4) ? t1 : t0;
+          const int c = lane & 7;
+          const uint32_t later = run_bits >> (c + 1);
+          const int end = later ? c + __ffs(later) : 8;
+          double run = cs;
+#pragma unroll
+          for (int d = 1; d < 8; ++d) {
+            const double v = __shfl_down_sync(0xffffffffu, cs, d, 8);
+            if (c + d < end) run += v;
+          }
+          if (lane < 8) sc.chunk_wsum[slot * 8 + c] = ((run_bits >> c) & 1u) ? run : 0.0;
         }
         double wsum = s0 + s1;
         wsum += __shfl_xor_sync(0xffffffffu, wsum, 8);
@@ -289,8 +305,8 @@ template <int NB, int NT>
 static int launch_grouped_inst(const bf_exact_grid& grid, const double* flux64, const double* pmax,
                                double threshold, const uint32_t* list, const uint32_t* entry_star,
                                int64_t entry_base, int64_t n_entries, const bf_accum_scratch& sc,
-                               const int32_t* fast_q, const bf_star_outputs& out, unsigned gridx,
-                               cudaStream_t st) {
+                               const int32_t* fast_q, const uint8_t* slow_run,
+                               const bf_star_outputs& out, unsigned gridx, cudaStream_t st) {
   const size_t smem = kGroupedWarps * GroupedSmem<NT>::kWarpBytes;
   static bool configured[64] = {};
   int dev = 0;
@@ -303,7 +319,7 @@ static int launch_grouped_inst(const bf_exact_grid& grid, const double* flux64, 
   }
   exact_weights_grouped_kernel<NB, NT><<<gridx, kGroupedWarps * 32, smem, st>>>(
       grid, flux64, pmax, threshold, list, entry_star, sc.group_order, entry_base, n_entries, sc,
-      fast_q, out.member_mask, out.member_prefix);
+      fast_q, slow_run, out.member_mask, out.member_prefix);
   BF_CHECK_LAUNCH("exact_weights_grouped_kernel");
   return BF_OK;
 }
@@ -313,8 +329,8 @@ static int launch_grouped_inst(const bf_exact_grid& grid, const double* flux64, 
 int launch_weights_grouped(const bf_exact_grid& grid, const double* flux64, const double* pmax,
                            double threshold, const uint32_t* list, const uint32_t* entry_star,
                            int64_t entry_base, int64_t n_entries, const bf_accum_scratch& sc,
-                           const int32_t* fast_q, int fast_pad, const bf_star_outputs& out,
-                           int sm_count, cudaStream_t st) {
+                           const int32_t* fast_q, int fast_pad, const uint8_t* slow_run,
+                           const bf_star_outputs& out, int sm_count, cudaStream_t st) {
   const int64_t n_stretch = (n_entries + kOrderStretch - 1) / kOrderStretch;
   const int64_t blocks = (n_stretch + kGroupedWarps - 1) / kGroupedWarps;
   const int64_t cap = static_cast<int64_t>(sm_count) * 64;
@@ -323,12 +339,12 @@ int launch_weights_grouped(const bf_exact_grid& grid, const double* flux64, cons
   case N:                                                                                         \
     if (fast_pad == 16)                                                                           \
       return launch_grouped_inst<N, 2>(grid, flux64, pmax, threshold, list, entry_star,           \
-                                       entry_base, n_entries, sc, fast_q, out, gridx, st);        \
+                                       entry_base, n_entries, sc, fast_q, slow_run, out, gridx, st);        \
     if (fast_pad == 32)                                                                           \
       return launch_grouped_inst<N, 4>(grid, flux64, pmax, threshold, list, entry_star,           \
-                                       entry_base, n_entries, sc, fast_q, out, gridx, st);        \
+                                       entry_base, n_entries, sc, fast_q, slow_run, out, gridx, st);        \
     return launch_grouped_inst<N, 0>(grid, flux64, pmax, threshold, list, entry_star, entry_base, \
-                                     n_entries, sc, fast_q, out, gridx, st);
+                                     n_entries, sc, fast_q, slow_run, out, gridx, st);
   switch (grid.nb) {
     BF_GROUPED_CASE(1) BF_GROUPED_CASE(2) BF_GROUPED_CASE(3) BF_GROUPED_CASE(4)
     BF_GROUPED_CASE(5) BF_GROUPED_CASE(6) BF_GROUPED_CASE(7) BF_GROUPED_CASE(8)
@@ -516,36 +532,41 @@ __device__ __forceinline__ void fast_accumulate(const bf_param_tables& prm,
 // A slow warp: one update per chunk with the chunk's weight sum (written by the grouped weights
 // kernel), four chunks per step; values of the next step are requested before this step's
 // shared-memory work.  Returns this lane's sum of wsum * fix (fit.py:743).
+constexpr int kSlowBatch = 8;  // runs per lane and step of a slow warp
 struct SlowRows {
-  double ws[4];
-  uint32_t bin[4];
-  int q[4];
+  double ws[kSlowBatch];
+  uint32_t bin[kSlowBatch];
+  int q[kSlowBatch];
 };
 
 template <int SLOTS>
 __device__ __forceinline__ void load_slow(const bf_param_tables& prm, const double* __restrict__ chunk_wsum,
-                                          const uint2* refs, uint32_t n_mc, uint32_t base, uint32_t step,
+                                          const uint2* refs, uint32_t n_sc, uint32_t base, uint32_t step,
                                           uint32_t h, int ks, bool live, bool live_q, SlowRows& r) {
-  uint2 ref[4];
-  bool valid[4];
+  uint2 ref[kSlowBatch];
+  bool valid[kSlowBatch];
 #pragma unroll
-  for (int u = 0; u < 4; ++u) {
+  for (int u = 0; u < kSlowBatch; ++u) {
     const uint32_t i = base + u * step + h;
-    valid[u] = base + u * step < n_mc && i < n_mc;
-    ref[u] = refs[valid[u] ? i : n_mc - 1];
+    valid[u] = base + u * step < n_sc && i < n_sc;
+    ref[u] = refs[valid[u] ? i : n_sc - 1];
   }
 #pragma unroll
-  for (int u = 0; u < 4; ++u) {
+  for (int u = 0; u < kSlowBatch; ++u) {
     r.ws[u] = valid[u] ? __ldg(chunk_wsum + ref[u].y) : 0.0;
     r.bin[u] = live ? __ldg(prm.slow_bin + static_cast<size_t>(ref[u].x) * prm.slow_pad + ks) : 0u;
     r.q[u] = live_q ? __ldg(prm.slow_q + static_cast<size_t>(ref[u].x) * prm.slow_pad + ks) : 0;
   }
 }
 
+// A slow warp: one update per run of equal slow values with the run's weight sum (written by the
+// grouped weights kernel), eight runs per lane and step; the values of the next step are
+// requested before this step's shared-memory work.  Returns this lane's sum of wsum * fix
+// (fit.py:743).
 template <int SLOTS>
 __device__ __forceinline__ double slow_accumulate(const bf_param_tables& prm,
                                                   const double* __restrict__ chunk_wsum,
-                                                  const uint2* refs, uint32_t n_mc, uint32_t first,
+                                                  const uint2* refs, uint32_t n_sc, uint32_t first,
                                                   uint32_t nsw, int ks, bool live, bool live_q,
                                                   int lane, double* col) {
   const uint32_t h = SLOTS == 2 ? static_cast<uint32_t>(lane >> 4) : 0u;
@@ -553,20 +574,20 @@ __device__ __forceinline__ double slow_accumulate(const bf_param_tables& prm,
   const uint32_t col_s = static_cast<uint32_t>(__cvta_generic_to_shared(col));
   double eacc = 0.0;
   uint32_t base = first * SLOTS;
-  if (base >= n_mc) return 0.0;
+  if (base >= n_sc) return 0.0;
   SlowRows cur, nxt;
-  load_slow<SLOTS>(prm, chunk_wsum, refs, n_mc, base, step, h, ks, live, live_q, nxt);
-  while (base < n_mc) {
+  load_slow<SLOTS>(prm, chunk_wsum, refs, n_sc, base, step, h, ks, live, live_q, nxt);
+  while (base < n_sc) {
     cur = nxt;
-    const uint32_t nb1 = base + 4 * step;
-    if (nb1 < n_mc) load_slow<SLOTS>(prm, chunk_wsum, refs, n_mc, nb1, step, h, ks, live, live_q, nxt);
+    const uint32_t nb1 = base + kSlowBatch * step;
+    if (nb1 < n_sc) load_slow<SLOTS>(prm, chunk_wsum, refs, n_sc, nb1, step, h, ks, live, live_q, nxt);
     add_four(col_s, cur.bin[0], cur.bin[1], cur.bin[2], cur.bin[3], cur.ws[0], cur.ws[1], cur.ws[2],
              cur.ws[3]);
+    add_four(col_s, cur.bin[4], cur.bin[5], cur.bin[6], cur.bin[7], cur.ws[4], cur.ws[5], cur.ws[6],
+             cur.ws[7]);
     if (live_q) {
-      eacc += cur.ws[0] * static_cast<double>(cur.q[0]);
-      eacc += cur.ws[1] * static_cast<double>(cur.q[1]);
-      eacc += cur.ws[2] * static_cast<double>(cur.q[2]);
-      eacc += cur.ws[3] * static_cast<double>(cur.q[3]);
+#pragma unroll
+      for (int u = 0; u < kSlowBatch; ++u) eacc += cur.ws[u] * static_cast<double>(cur.q[u]);
     }
     base = nb1;
   }
@@ -656,20 +677,31 @@ split_hist_kernel(bf_param_tables prm, int hist_doubles, const double* __restric
   for (int i = threadIdx.x; i < nf; i += blockDim.x) kcls[prm.fast_k[i]] = i;
   for (int i = threadIdx.x; i < nsl; i += blockDim.x) kcls[prm.slow_k[i]] = 32 + i;
 
-  // ---- the star's chunks that hold a member: (chunk id, place of its weights) ------------
-  uint2* refs = reinterpret_cast<uint2*>(sc.chunk_refs) + (static_cast<size_t>(e0) - entry_base) * 8;
-  uint32_t carry = 0;
+  // ---- the star's chunks that hold a member (chunk id, place of its 8 weights) and its runs of
+  // equal slow values that hold one (first chunk of the run, place of the run's weight sum) ----
+  uint2* refs = reinterpret_cast<uint2*>(sc.chunk_refs) + (static_cast<size_t>(e0) - entry_base) * 16;
+  uint2* srefs = refs + static_cast<size_t>(e1 - e0) * 8;
+  uint32_t carry_f = 0, carry_s = 0;
   for (uint32_t eb = e0; eb < e1; eb += blockDim.x) {
     const uint32_t e = eb + threadIdx.x;
-    uint32_t occ = 0, g = 0;
+    uint32_t occ = 0, socc = 0, g = 0;
     if (e < e1) {
       const uint2 mm = *reinterpret_cast<const uint2*>(out.member_mask + static_cast<size_t>(e) * kWordsPerGroup);
       g = list[e];
 #pragma unroll
       for (int c = 0; c < 8; ++c)
         if ((((c < 4 ? mm.x : mm.y) >> (8 * (c & 3))) & 0xffu) != 0) occ |= 1u << c;
+      if (occ && nsl > 0) {
+        uint32_t rb = prm.slow_run ? (prm.slow_run[g] | 1u) : 0xffu;
+        while (rb) {
+          const int c = __ffs(rb) - 1;
+          rb &= rb - 1;
+          const uint32_t end = rb ? __ffs(rb) - 1 : 8;
+          if (occ & ((1u << end) - (1u << c))) socc |= 1u << c;
+        }
+      }
     }
-    const uint32_t v = __popc(occ);
+    const uint32_t v = __popc(occ) | (__popc(socc) << 16);
     uint32_t inc = v;
 #pragma unroll
     for (int d = 1; d < 32; d <<= 1) {
@@ -684,21 +716,28 @@ split_hist_kernel(bf_param_tables prm, int hist_doubles, const double* __restric
       if (w < warp) woff += sscan[w];
       tot += sscan[w];
     }
-    uint32_t pos = carry + woff + inc - v;
+    const uint32_t ex = woff + inc - v;
+    uint32_t pos = carry_f + (ex & 0xffffu), spos = carry_s + (ex >> 16);
     const uint32_t wslot = static_cast<uint32_t>((static_cast<int64_t>(e) - entry_base) * 8);
     while (occ) {
       const int c = __ffs(occ) - 1;
       occ &= occ - 1;
       refs[pos++] = make_uint2(g * 8u + c, wslot + c);
     }
-    carry += tot;
+    while (socc) {
+      const int c = __ffs(socc) - 1;
+      socc &= socc - 1;
+      srefs[spos++] = make_uint2(g * 8u + c, wslot + c);
+    }
+    carry_f += tot & 0xffffu;
+    carry_s += tot >> 16;
   }
-  const uint32_t n_mc = carry;
+  const uint32_t n_mc = carry_f, n_sc = carry_s;
   __syncthreads();  // refs (global) and the tables above are visible to the whole block
 
   // ---- occupied bin ranges -----------------------------------------------------------------
   if (nf > 0) class_ranges<FS, true>(prm, refs, n_mc, warp, NW, lane, nf, wmin, wmax);
-  if (nsl > 0) class_ranges<SS, false>(prm, refs, n_mc, warp, NW, lane, nsl, wmin + 32, wmax + 32);
+  if (nsl > 0) class_ranges<SS, false>(prm, srefs, n_sc, warp, NW, lane, nsl, wmin + 32, wmax + 32);
   __syncthreads();
 
   // ---- layout: warp 0 the fast class, warp 1 the slow class ----------------------------------
@@ -730,8 +769,9 @@ split_hist_kernel(bf_param_tables prm, int hist_doubles, const double* __restric
       }
       if (F < 1) F = 1;  // cannot happen: the host checked the worst case
     }
-    // two warps always stay free for the expectation partials of the fast class
-    if (nf > 0 && F > NW - S - 2) F = NW - S - 2;
+    // one warp of ten always stays free for the expectation partials of the fast class
+    const int X = NW >= 16 ? 2 : 1;
+    if (nf > 0 && F > NW - S - X) F = NW - S - X;
     misc[3] = F;
     misc[4] = S;
   }
@@ -754,7 +794,7 @@ split_hist_kernel(bf_param_tables prm, int hist_doubles, const double* __restric
       const int ks = lparam[32 + lane];
       const bool live = ks >= 0;
       const bool live_q = live && !(prm.q_const && prm.q_const[prm.slow_k[live ? ks : 0]]);
-      eacc = slow_accumulate<SS>(prm, sc.chunk_wsum, refs, n_mc, warp - F, S, live ? ks : 0, live,
+      eacc = slow_accumulate<SS>(prm, sc.chunk_wsum, srefs, n_sc, warp - F, S, live ? ks : 0, live,
                                  live_q, lane, hist + F * cf + (warp - F) * cs + lcol[32 + lane]);
     } else if (nf > 0) {
       // warps without a private copy add up the expectation partials of the fast class that

@@ -105,7 +105,7 @@ class FitEngine:
             self.d_msb, self.d_ivar = up(s.msb), up(s.ivar)
             self.d_lnq, self.d_lnw = up(s.lnq), up(s.lnw)
             self.d_cov_off = up(s.cov_off) if s.cov_off is not None else None
-            split_only = sparse_pass == "split" and s.split_ok
+            split_only = sparse_pass == "split" and s.split_ok and not s.full_cov and s.nb <= 8
             # (the per-model tables are only read by the kernels that treat all parameters alike)
             self.d_bin_tab, self.d_q_tab = (None, None) if split_only else (up(s.bin_tab), up(s.q_tab))
             self.d_bin_off, self.d_bin_val = up(s.bin_off), up(s.bin_val)
@@ -117,12 +117,14 @@ class FitEngine:
             # "both" = all tables resident, the kernels chosen per call (tests)
             if sparse_pass not in ("split", "legacy", "both"):
                 raise ValueError("sparse_pass must be 'split', 'legacy' or 'both'")
-            self.split = sparse_pass != "legacy" and s.split_ok
+            # (the group-ordered weights kernel: diagonal noise model, up to 8 bands)
+            self.split = sparse_pass != "legacy" and s.split_ok and not s.full_cov and s.nb <= 8
             self.sparse_pass = sparse_pass
             if self.split:
                 self.d_fast_k, self.d_slow_k = up(s.fast_k), up(s.slow_k)
                 self.d_fast_bin, self.d_fast_q = up(s.fast_bin), up(s.fast_q)
                 self.d_slow_bin, self.d_slow_q = up(s.slow_bin), up(s.slow_q)
+                self.d_slow_run = up(s.slow_run)
             self.d_inv_scale = up((1.0 / s.band_scale).astype(np.float64))
             if s.pair_bin is not None:
                 self.d_pair_bin, self.d_pair_off = up(s.pair_bin), up(s.pair_off)
@@ -143,12 +145,13 @@ class FitEngine:
             p.fast_k, p.slow_k = self.d_fast_k.data_ptr(), self.d_slow_k.data_ptr()
             p.fast_bin, p.fast_q = self.d_fast_bin.data_ptr(), self.d_fast_q.data_ptr()
             p.slow_bin, p.slow_q = self.d_slow_bin.data_ptr(), self.d_slow_q.data_ptr()
+            p.slow_run = self.d_slow_run.data_ptr()
         per_star = s.n_groups * 4
         mb = max(STAR_BLOCK, (gmin_budget_bytes // per_star) // STAR_BLOCK * STAR_BLOCK)
         mb = min(mb, ((2**31 - 1) // max(s.n_groups, 1)) // STAR_BLOCK * STAR_BLOCK, 32768 * STAR_BLOCK)
         self.max_batch = int(max(mb, STAR_BLOCK))
         # per listed group: 64 weights + partials (+ the group order and the chunk lists)
-        per_entry = GROUP * 8 + 24 + (4 + 64 + 64 + 8 * s.fast_pad if self.split else 0)
+        per_entry = GROUP * 8 + 24 + (4 + 128 + 64 + 8 * s.fast_pad if self.split else 0)
         self.max_entries = int(max(1 << 16, scratch_budget_bytes // per_entry))
         self.launches = 0  # kernels launched by this engine (bench.py reports it)
         self._result_cache = {}
@@ -359,7 +362,7 @@ class FitEngine:
             use_split = self.split and not getattr(self, "force_legacy", False)
             if use_split:
                 g_order = torch.empty(max(nmax, 1), dtype=torch.int32, device=dev)
-                c_refs = torch.empty(max(nmax, 1) * 16, dtype=torch.int32, device=dev)
+                c_refs = torch.empty(max(nmax, 1) * 32, dtype=torch.int32, device=dev)
                 g_work = torch.empty(int(self.lib.bf_group_order_work_elems(s.n_groups)),
                                      dtype=torch.int32, device=dev)
                 c_wsum = torch.empty(max(nmax, 1) * 8, dtype=torch.float64, device=dev)

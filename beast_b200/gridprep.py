@@ -349,7 +349,7 @@ class FitSetup:
         self.fast_pad = 16 if nf <= 16 else 32
         self.slow_pad = 16 if nsl <= 16 else 32
         if not self.split_ok:
-            self.fast_bin = self.fast_q = self.slow_bin = self.slow_q = None
+            self.fast_bin = self.fast_q = self.slow_bin = self.slow_q = self.slow_run = None
             return
         fb = np.zeros((nch if nf else 1, self.fast_pad, CHUNK), dtype=np.uint8)
         fq = np.zeros((nch if nf else 1, 2, self.fast_pad, CHUNK // 2), dtype=np.int32)
@@ -362,6 +362,15 @@ class FitSetup:
             sb[:, i] = b3[k][:, 0]
             sq[:, i] = q3[k][:, 0]
         self.fast_bin, self.fast_q, self.slow_bin, self.slow_q = fb, fq, sb, sq
+        # runs of chunks with the same slow values inside a group of 8 chunks: bit c of
+        # slow_run[g] = chunk c starts a run (bit 0 always).  The weights kernel sums the weights
+        # per run, so the slow parameters take one update per run, not per chunk.
+        start = np.ones(nch, dtype=bool)
+        if nsl and nch > 1:
+            start[1:] = (sb[1:] != sb[:-1]).any(axis=1) | (sq[1:] != sq[:-1]).any(axis=1)
+        start[::GROUP // CHUNK] = True
+        bits = (start.reshape(-1, GROUP // CHUNK) << np.arange(GROUP // CHUNK)[None, :]).sum(axis=1)
+        self.slow_run = bits.astype(np.uint8)
 
     @property
     def n_q(self):

@@ -204,7 +204,9 @@ typedef struct {
    *   fast_bin [ld_model/8][fast_pad][8] u8 bins of the chunk's models
    *   fast_q   [ld_model/8][2][fast_pad][4] int32   fixed-point values (q_tab encoding), models
    *                                         0..3 of all parameters, then models 4..7
-   *   slow_bin [ld_model/8][slow_pad] u8,  slow_q [ld_model/8][slow_pad] int32 */
+   *   slow_bin [ld_model/8][slow_pad] u8,  slow_q [ld_model/8][slow_pad] int32
+   *   slow_run [ld_model/64] u8             bit c: chunk c of the group starts a run of chunks
+   *                                         with equal slow values (bit 0 always set) */
   int n_fast, n_slow, fast_pad, slow_pad;
   const int32_t* fast_k;
   const int32_t* slow_k;
@@ -212,6 +214,7 @@ typedef struct {
   const int32_t* fast_q;
   const uint8_t* slow_bin;
   const int32_t* slow_q;
+  const uint8_t* slow_run;
 } bf_param_tables;
 
 typedef struct {
@@ -240,10 +243,12 @@ typedef struct {
                            id (bf_group_order).  When given (diagonal noise model, <= 12 bands)
                            the exact weights are evaluated group by group, so that a group's
                            model rows are fetched once for all the stars that list it */
-  uint32_t* chunk_refs; /* [n_entries][8][2] or NULL: room for the per-star lists of chunks that
-                           hold a member, built and consumed by the split histogram kernel */
-  double* chunk_wsum;   /* [n_entries][8] or NULL: weight sum of each chunk, written by the
-                           group-ordered weights kernel for the slow parameters */
+  uint32_t* chunk_refs; /* [n_entries][16][2] or NULL: room for the per-star lists of chunks
+                           that hold a member and of slow-value runs that hold one, built and
+                           consumed by the split histogram kernel */
+  double* chunk_wsum;   /* [n_entries][8] or NULL: at the first chunk of every run of equal slow
+                           values (params->slow_run) the weight sum of the run, 0 elsewhere;
+                           written by the group-ordered weights kernel */
   double* exp_part;     /* [n_entries][fast_pad] or NULL: sum_m w_m * fix_m[k] of each listed
                            group for the fast parameters (FP64 tensor-core products in the
                            group-ordered weights kernel).  The split histogram kernel runs when

@@ -150,6 +150,7 @@ def test_weights_kernel_instantiations_are_bit_identical(monkeypatch):
     same operations in the same order as the runtime-band-count one: every output bit agrees"""
     g, nz, obs, args, ref = util.load_golden("small_thr10")
     setup, eng = _engine(g, nz, args)
+    monkeypatch.setenv("BF_WEIGHTS", "star")
     a = eng.fit(obs.fluxes, threshold=args["threshold"], sparse="all")
     monkeypatch.setenv("BF_WEIGHTS_GENERIC", "1")
     b = eng.fit(obs.fluxes, threshold=args["threshold"], sparse="all")
