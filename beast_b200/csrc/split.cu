@@ -237,14 +237,21 @@ exact_weights_grouped_kernel(bf_exact_grid grid, const double* __restrict__ flux
           wt[pending * kWtLd + 32 + lane] = w1;
           if (lane == 0) slots[pending] = static_cast<int32_t>(slot);
         }
-        // weight sums of the 8 chunks (8 neighbouring lanes each), then of the group
-        double s0 = w0, s1 = w1;
+        double wsum;
+        if (run_bits == 1u || !sc.chunk_wsum) {
+          // one run of equal slow values (or no run sums wanted): the group's weight sum only
+          wsum = w0 + w1;
 #pragma unroll
-        for (int d = 1; d < 8; d <<= 1) {
-          s0 += __shfl_xor_sync(0xffffffffu, s0, d);
-          s1 += __shfl_xor_sync(0xffffffffu, s1, d);
-        }
-        if (sc.chunk_wsum) {
+          for (int d = 16; d > 0; d >>= 1) wsum += __shfl_xor_sync(0xffffffffu, wsum, d);
+          if (sc.chunk_wsum && lane < 8) sc.chunk_wsum[slot * 8 + lane] = lane == 0 ? wsum : 0.0;
+        } else {
+          // weight sums of the 8 chunks (8 neighbouring lanes each), then of the group
+          double s0 = w0, s1 = w1;
+#pragma unroll
+          for (int d = 1; d < 8; d <<= 1) {
+            s0 += __shfl_xor_sync(0xffffffffu, s0, d);
+            s1 += __shfl_xor_sync(0xffffffffu, s1, d);
+          }
           // lane c (< 8) takes chunk c's sum, then adds the later chunks of its run: the sum of
           // a run of equal slow values sits at the run's first chunk, 0 at the others
           const double t0 = __shfl_sync(0xffffffffu, s0, (lane & 3) * 8);
@@ -260,10 +267,10 @@ exact_weights_grouped_kernel(bf_exact_grid grid, const double* __restrict__ flux
             if (c + d < end) run += v;
           }
           if (lane < 8) sc.chunk_wsum[slot * 8 + c] = ((run_bits >> c) & 1u) ? run : 0.0;
+          wsum = s0 + s1;
+          wsum += __shfl_xor_sync(0xffffffffu, wsum, 8);
+          wsum += __shfl_xor_sync(0xffffffffu, wsum, 16);
         }
-        double wsum = s0 + s1;
-        wsum += __shfl_xor_sync(0xffffffffu, wsum, 8);
-        wsum += __shfl_xor_sync(0xffffffffu, wsum, 16);
         // chi2 minimum of the members, lowest index on ties (fit.py:725-726)
         double c0 = 0.0, c1 = 0.0;
         int l0 = 0, l1 = 0;
@@ -902,15 +909,13 @@ int launch_split_hist(const bf_param_tables& prm, const double* pmax, const uint
                       int64_t n_stars, int64_t entry_base, const bf_accum_scratch& sc, double p0,
                       double p1, double p2, const bf_star_outputs& out, size_t smem_budget,
                       cudaStream_t st) {
-  // two blocks of 10 warps per SM when a worst-case star fits half the shared memory: two
-  // stars' phases (chunk list, ranges, accumulation, percentiles) then overlap on an SM;
-  // otherwise one block of 20 warps.  BF_SPLIT_WARPS=10|20 overrides (measurements).
+  // One block of 20 warps per SM.  BF_SPLIT_WARPS=10: two blocks of 10 warps when a worst-case
+  // star fits half the shared memory (measured slower at C2: 90 vs 67 ms per 33,792 stars -- a
+  // broad star then has half the private copies).
   const size_t half = (smem_budget + 1024) / 2 - 1024;
-  int warps = split_fits(prm, half, kSplitWarpsMax / 2) ? kSplitWarpsMax / 2 : kSplitWarpsMax;
-  if (const char* env = getenv("BF_SPLIT_WARPS")) {
-    if (env[0] == '2') warps = kSplitWarpsMax;
+  int warps = kSplitWarpsMax;
+  if (const char* env = getenv("BF_SPLIT_WARPS"))
     if (env[0] == '1' && split_fits(prm, half, kSplitWarpsMax / 2)) warps = kSplitWarpsMax / 2;
-  }
   const int hd = split_hist_doubles(warps == kSplitWarpsMax ? smem_budget : half);
   const size_t smem = SplitSmem::bytes(hd);
   const int fs = prm.fast_pad == 16 ? 2 : 1, ss = prm.slow_pad == 16 ? 2 : 1;

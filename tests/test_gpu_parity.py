@@ -195,7 +195,9 @@ def test_group_ordered_weights_match_star_ordered(monkeypatch):
                             "sparse_lnp", "sparse_chi2"))
     np.testing.assert_allclose(a.total_log_norm, b.total_log_norm, rtol=1e-14, atol=0)
     np.testing.assert_allclose(a.pdf1d, b.pdf1d, rtol=1e-13, atol=1e-300)
-    np.testing.assert_allclose(a.exp_vals, b.exp_vals, rtol=1e-13, atol=1e-300)
+    # (the fast class's expectation sums: FP64 tensor-core products per group vs a serial loop)
+    span = np.array([c[setup.g0_indxs].max() - c[setup.g0_indxs].min() for c in setup.qcols])
+    assert np.all(np.abs(a.exp_vals - b.exp_vals) <= 1e-12 * np.abs(b.exp_vals) + 1e-12 * span)
 
 
 @pytest.mark.parametrize("nbins", [50, 200])
