@@ -418,127 +418,111 @@ struct FastRows {
   double w[8];
 };
 
-// rows of one chunk for a fast lane.  ref = (chunk id, index of the chunk's 8 weights / 8)
-__device__ __forceinline__ void load_fast(const bf_param_tables& prm, const double* __restrict__ weights,
-                                          uint2 ref, bool valid, int kf, bool live, FastRows& r) {
-  const double2* wp = reinterpret_cast<const double2*>(weights + static_cast<size_t>(ref.y) * BF_CHUNK);
-  double2 a = make_double2(0.0, 0.0), b = a, c = a, d = a;
-  if (valid) {
-    a = __ldg(wp);
-    b = __ldg(wp + 1);
-    c = __ldg(wp + 2);
-    d = __ldg(wp + 3);
-  }
-  r.w[0] = a.x; r.w[1] = a.y; r.w[2] = b.x; r.w[3] = b.y;
-  r.w[4] = c.x; r.w[5] = c.y; r.w[6] = d.x; r.w[7] = d.y;
-  r.bins = make_uint2(0u, 0u);
-  if (live)
-    r.bins = __ldg(reinterpret_cast<const uint2*>(
-        prm.fast_bin + (static_cast<size_t>(ref.x) * prm.fast_pad + kf) * BF_CHUNK));
-}
+// eight zero weights: what a lane without a chunk of its own reads (tail of a star's chunk list)
+__device__ __align__(16) const double g_zero_weights[8] = {0, 0, 0, 0, 0, 0, 0, 0};
 
-// four updates of one lane's column at a time: four loads in flight, models that share a bin
-// take the earlier weights along, stores in order (see hist_window_kernel)
-__device__ __forceinline__ void add_four(uint32_t col_s, uint32_t b0, uint32_t b1, uint32_t b2,
-                                         uint32_t b3, double w0, double w1, double w2, double w3) {
-  const uint32_t a0 = col_s + b0 * 128u, a1 = col_s + b1 * 128u, a2 = col_s + b2 * 128u,
-                 a3 = col_s + b3 * 128u;
-  double h0, h1, h2, h3;
+// two updates of one lane's column: both loads in flight; when the two models share a bin the
+// second takes the first one's weight along and its store, issued second, leaves the full sum.
+// (Four at a time, as in hist_window_kernel, costs 44 instructions per four models -- most of
+// them for the six pairwise bin comparisons -- against 24 here; this kernel has few warps per
+// SM when the private copies are large and is bound by instruction issue, not by the chain.)
+__device__ __forceinline__ void add_two(uint32_t col_s, uint32_t b0, uint32_t b1, double w0, double w1) {
+  const uint32_t a0 = col_s + b0 * 128u, a1 = col_s + b1 * 128u;
+  double h0, h1;
   asm volatile("ld.shared.f64 %0, [%1];" : "=d"(h0) : "r"(a0));
   asm volatile("ld.shared.f64 %0, [%1];" : "=d"(h1) : "r"(a1));
-  asm volatile("ld.shared.f64 %0, [%1];" : "=d"(h2) : "r"(a2));
-  asm volatile("ld.shared.f64 %0, [%1];" : "=d"(h3) : "r"(a3));
-  double s1 = w1, s2 = w2, s3 = w3;
-  if (a0 == a1) s1 += w0;
-  if (a0 == a2) s2 += w0;
-  if (a1 == a2) s2 += w1;
-  if (a0 == a3) s3 += w0;
-  if (a1 == a3) s3 += w1;
-  if (a2 == a3) s3 += w2;
+  asm("{\n .reg .pred p;\n setp.eq.u32 p, %1, %2;\n @p add.f64 %0, %0, %3;\n}\n"
+      : "+d"(w1)
+      : "r"(a0), "r"(a1), "d"(w0));
   h0 += w0;
-  h1 += s1;
-  h2 += s2;
-  h3 += s3;
+  h1 += w1;
   asm volatile("st.shared.f64 [%0], %1;" ::"r"(a0), "d"(h0));
   asm volatile("st.shared.f64 [%0], %1;" ::"r"(a1), "d"(h1));
-  asm volatile("st.shared.f64 [%0], %1;" ::"r"(a2), "d"(h2));
-  asm volatile("st.shared.f64 [%0], %1;" ::"r"(a3), "d"(h3));
 }
 
 __device__ __forceinline__ void add_chunk(uint32_t col_s, const FastRows& r) {
   const uint32_t bx = r.bins.x, by = r.bins.y;
-  add_four(col_s, bx & 0xffu, (bx >> 8) & 0xffu, (bx >> 16) & 0xffu, bx >> 24, r.w[0], r.w[1], r.w[2],
-           r.w[3]);
-  add_four(col_s, by & 0xffu, (by >> 8) & 0xffu, (by >> 16) & 0xffu, by >> 24, r.w[4], r.w[5], r.w[6],
-           r.w[7]);
+  add_two(col_s, bx & 0xffu, (bx >> 8) & 0xffu, r.w[0], r.w[1]);
+  add_two(col_s, (bx >> 16) & 0xffu, bx >> 24, r.w[2], r.w[3]);
+  add_two(col_s, by & 0xffu, (by >> 8) & 0xffu, r.w[4], r.w[5]);
+  add_two(col_s, (by >> 16) & 0xffu, by >> 24, r.w[6], r.w[7]);
 }
 
 // A fast warp: chunks first*SLOTS + h, then every nfw*SLOTS-th, of the star's member chunks.
 // Software pipeline in registers: the chunk reference is read four steps ahead, the rows (8 bin
 // bytes + 8 weights) three steps ahead of their use, so that three steps' rows are in flight
-// per warp -- the loop waits on L2 / HBM, not on shared memory.
+// per warp.  bins_lane = fast_bin + this lane's parameter, bin_mask = 0 for a lane without a
+// parameter (it then adds into the one-bin column it owns); a lane whose slot has run past the
+// end of the list re-reads the last chunk's bins with zero weights.
 template <int SLOTS>
-__device__ __forceinline__ void fast_accumulate(const bf_param_tables& prm,
-                                                const double* __restrict__ weights, const uint2* refs,
-                                                uint32_t n_mc, uint32_t first, uint32_t nfw, int kf,
-                                                bool live, int lane, double* col) {
+__device__ __forceinline__ void fast_accumulate(const uint8_t* __restrict__ bins_lane, uint32_t row_bytes,
+                                                uint32_t bin_mask, const double* __restrict__ weights,
+                                                const uint2* refs, uint32_t n_mc, uint32_t first,
+                                                uint32_t nfw, int lane, double* col) {
   const uint32_t h = SLOTS == 2 ? static_cast<uint32_t>(lane >> 4) : 0u;
   const uint32_t step = nfw * SLOTS;
   const uint32_t col_s = static_cast<uint32_t>(__cvta_generic_to_shared(col));
   const uint32_t start = first * SLOTS;  // warp-uniform position of slot 0
   if (start >= n_mc) return;
   const uint32_t n_steps = (n_mc - start + step - 1) / step;
-  // reference of step t (clamped; the flag says whether this lane's slot exists)
-  auto ref_of = [&](uint32_t t, bool& valid) {
-    const uint32_t i = start + t * step + h;
-    valid = t < n_steps && i < n_mc;
-    return refs[valid ? i : n_mc - 1];
+  const uint32_t last = n_mc - 1;
+  uint32_t i = start + h;  // this lane's position of the step whose reference is read next
+  auto next_ref = [&](bool& valid) {
+    valid = i <= last;
+    const uint2 r = refs[valid ? i : last];
+    i += step;
+    return r;
+  };
+  auto load = [&](uint2 ref, bool valid, FastRows& r) {
+    const double2* wp = valid ? reinterpret_cast<const double2*>(weights + static_cast<size_t>(ref.y) * BF_CHUNK)
+                              : reinterpret_cast<const double2*>(g_zero_weights);
+    const double2 a = __ldg(wp), b = __ldg(wp + 1), c = __ldg(wp + 2), d = __ldg(wp + 3);
+    const uint2 bb = __ldg(reinterpret_cast<const uint2*>(bins_lane + static_cast<size_t>(ref.x) * row_bytes));
+    r.bins = make_uint2(bb.x & bin_mask, bb.y & bin_mask);
+    r.w[0] = a.x; r.w[1] = a.y; r.w[2] = b.x; r.w[3] = b.y;
+    r.w[4] = c.x; r.w[5] = c.y; r.w[6] = d.x; r.w[7] = d.y;
   };
   FastRows r0, r1, r2;
-  bool v;
-  uint2 ref = ref_of(0, v);
-  load_fast(prm, weights, ref, v, kf, live, r0);
-  ref = ref_of(1, v);
-  load_fast(prm, weights, ref, v, kf, live, r1);
-  ref = ref_of(2, v);
-  load_fast(prm, weights, ref, v, kf, live, r2);
-  bool vn;
-  uint2 refn = ref_of(3, vn);
+  bool v, vn;
+  uint2 ref = next_ref(v);
+  load(ref, v, r0);
+  ref = next_ref(v);
+  load(ref, v, r1);
+  ref = next_ref(v);
+  load(ref, v, r2);
+  uint2 refn = next_ref(vn);
   for (uint32_t t = 0; t < n_steps; t += 3) {
     // step t uses r0; its replacement (step t+3) is requested before the shared-memory work
     {
       const uint2 rr = refn;
       const bool vv = vn;
-      refn = ref_of(t + 4, vn);
+      refn = next_ref(vn);
       FastRows nx;
-      load_fast(prm, weights, rr, vv, kf, live, nx);
+      load(rr, vv, nx);
       add_chunk(col_s, r0);
       r0 = nx;
     }
     if (t + 1 < n_steps) {
       const uint2 rr = refn;
       const bool vv = vn;
-      refn = ref_of(t + 5, vn);
+      refn = next_ref(vn);
       FastRows nx;
-      load_fast(prm, weights, rr, vv, kf, live, nx);
+      load(rr, vv, nx);
       add_chunk(col_s, r1);
       r1 = nx;
     }
     if (t + 2 < n_steps) {
       const uint2 rr = refn;
       const bool vv = vn;
-      refn = ref_of(t + 6, vn);
+      refn = next_ref(vn);
       FastRows nx;
-      load_fast(prm, weights, rr, vv, kf, live, nx);
+      load(rr, vv, nx);
       add_chunk(col_s, r2);
       r2 = nx;
     }
   }
 }
 
-// A slow warp: one update per chunk with the chunk's weight sum (written by the grouped weights
-// kernel), four chunks per step; values of the next step are requested before this step's
-// shared-memory work.  Returns this lane's sum of wsum * fix (fit.py:743).
 constexpr int kSlowBatch = 8;  // runs per lane and step of a slow warp
 struct SlowRows {
   double ws[kSlowBatch];
@@ -588,10 +572,8 @@ __device__ __forceinline__ double slow_accumulate(const bf_param_tables& prm,
     cur = nxt;
     const uint32_t nb1 = base + kSlowBatch * step;
     if (nb1 < n_sc) load_slow<SLOTS>(prm, chunk_wsum, refs, n_sc, nb1, step, h, ks, live, live_q, nxt);
-    add_four(col_s, cur.bin[0], cur.bin[1], cur.bin[2], cur.bin[3], cur.ws[0], cur.ws[1], cur.ws[2],
-             cur.ws[3]);
-    add_four(col_s, cur.bin[4], cur.bin[5], cur.bin[6], cur.bin[7], cur.ws[4], cur.ws[5], cur.ws[6],
-             cur.ws[7]);
+#pragma unroll
+    for (int u = 0; u < kSlowBatch; u += 2) add_two(col_s, cur.bin[u], cur.bin[u + 1], cur.ws[u], cur.ws[u + 1]);
     if (live_q) {
 #pragma unroll
       for (int u = 0; u < kSlowBatch; ++u) eacc += cur.ws[u] * static_cast<double>(cur.q[u]);
@@ -794,9 +776,9 @@ split_hist_kernel(bf_param_tables prm, int hist_doubles, const double* __restric
   if (n_mc > 0) {
     if (warp < F) {
       const int kf = lparam[lane];
-      const bool live = kf >= 0;
-      fast_accumulate<FS>(prm, sc.weights, refs, n_mc, warp, F, live ? kf : 0, live, lane,
-                          hist + warp * cf + lcol[lane]);
+      fast_accumulate<FS>(prm.fast_bin + (kf >= 0 ? kf : 0) * BF_CHUNK,
+                          static_cast<uint32_t>(prm.fast_pad) * BF_CHUNK, kf >= 0 ? 0xffffffffu : 0u,
+                          sc.weights, refs, n_mc, warp, F, lane, hist + warp * cf + lcol[lane]);
     } else if (warp < F + S) {
       const int ks = lparam[32 + lane];
       const bool live = ks >= 0;
