@@ -482,6 +482,8 @@ __device__ __forceinline__ void fast_accumulate(const uint8_t* __restrict__ bins
     r.w[0] = a.x; r.w[1] = a.y; r.w[2] = b.x; r.w[3] = b.y;
     r.w[4] = c.x; r.w[5] = c.y; r.w[6] = d.x; r.w[7] = d.y;
   };
+  // three register sets in rotation; a set is refilled (for three steps later) right after it
+  // has been consumed, so no register copy ever waits for a load
   FastRows r0, r1, r2;
   bool v, vn;
   uint2 ref = next_ref(v);
@@ -492,33 +494,18 @@ __device__ __forceinline__ void fast_accumulate(const uint8_t* __restrict__ bins
   load(ref, v, r2);
   uint2 refn = next_ref(vn);
   for (uint32_t t = 0; t < n_steps; t += 3) {
-    // step t uses r0; its replacement (step t+3) is requested before the shared-memory work
-    {
-      const uint2 rr = refn;
-      const bool vv = vn;
-      refn = next_ref(vn);
-      FastRows nx;
-      load(rr, vv, nx);
-      add_chunk(col_s, r0);
-      r0 = nx;
-    }
+    add_chunk(col_s, r0);
+    load(refn, vn, r0);
+    refn = next_ref(vn);
     if (t + 1 < n_steps) {
-      const uint2 rr = refn;
-      const bool vv = vn;
-      refn = next_ref(vn);
-      FastRows nx;
-      load(rr, vv, nx);
       add_chunk(col_s, r1);
-      r1 = nx;
+      load(refn, vn, r1);
+      refn = next_ref(vn);
     }
     if (t + 2 < n_steps) {
-      const uint2 rr = refn;
-      const bool vv = vn;
-      refn = next_ref(vn);
-      FastRows nx;
-      load(rr, vv, nx);
       add_chunk(col_s, r2);
-      r2 = nx;
+      load(refn, vn, r2);
+      refn = next_ref(vn);
     }
   }
 }
@@ -566,19 +553,30 @@ __device__ __forceinline__ double slow_accumulate(const bf_param_tables& prm,
   double eacc = 0.0;
   uint32_t base = first * SLOTS;
   if (base >= n_sc) return 0.0;
-  SlowRows cur, nxt;
-  load_slow<SLOTS>(prm, chunk_wsum, refs, n_sc, base, step, h, ks, live, live_q, nxt);
-  while (base < n_sc) {
-    cur = nxt;
-    const uint32_t nb1 = base + kSlowBatch * step;
-    if (nb1 < n_sc) load_slow<SLOTS>(prm, chunk_wsum, refs, n_sc, nb1, step, h, ks, live, live_q, nxt);
+  // two register sets in turn, each refilled right after it has been consumed
+  SlowRows ra, rb;
+  const uint32_t stride = kSlowBatch * step;
+  load_slow<SLOTS>(prm, chunk_wsum, refs, n_sc, base, step, h, ks, live, live_q, ra);
+  if (base + stride < n_sc)
+    load_slow<SLOTS>(prm, chunk_wsum, refs, n_sc, base + stride, step, h, ks, live, live_q, rb);
+  auto consume = [&](const SlowRows& r) {
 #pragma unroll
-    for (int u = 0; u < kSlowBatch; u += 2) add_two(col_s, cur.bin[u], cur.bin[u + 1], cur.ws[u], cur.ws[u + 1]);
+    for (int u = 0; u < kSlowBatch; u += 2) add_two(col_s, r.bin[u], r.bin[u + 1], r.ws[u], r.ws[u + 1]);
     if (live_q) {
 #pragma unroll
-      for (int u = 0; u < kSlowBatch; ++u) eacc += cur.ws[u] * static_cast<double>(cur.q[u]);
+      for (int u = 0; u < kSlowBatch; ++u) eacc += r.ws[u] * static_cast<double>(r.q[u]);
     }
-    base = nb1;
+  };
+  while (base < n_sc) {
+    consume(ra);
+    if (base + 2 * stride < n_sc)
+      load_slow<SLOTS>(prm, chunk_wsum, refs, n_sc, base + 2 * stride, step, h, ks, live, live_q, ra);
+    if (base + stride < n_sc) {
+      consume(rb);
+      if (base + 3 * stride < n_sc)
+        load_slow<SLOTS>(prm, chunk_wsum, refs, n_sc, base + 3 * stride, step, h, ks, live, live_q, rb);
+    }
+    base += 2 * stride;
   }
   return eacc;
 }
