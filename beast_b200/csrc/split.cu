@@ -482,65 +482,95 @@ __device__ __forceinline__ void fast_accumulate(const uint8_t* __restrict__ bins
     r.w[0] = a.x; r.w[1] = a.y; r.w[2] = b.x; r.w[3] = b.y;
     r.w[4] = c.x; r.w[5] = c.y; r.w[6] = d.x; r.w[7] = d.y;
   };
-  // three register sets in rotation; a set is refilled (for three steps later) right after it
-  // has been consumed, so no register copy ever waits for a load
+  // Three row sets in rotation, each refilled (for three steps later) right after it has been
+  // consumed, and two sets of three chunk references in turn, requested a whole round before
+  // they are needed as addresses: no register copy and no address ever waits for a load that
+  // was issued less than three steps earlier.
   FastRows r0, r1, r2;
-  bool v, vn;
-  uint2 ref = next_ref(v);
-  load(ref, v, r0);
-  ref = next_ref(v);
-  load(ref, v, r1);
-  ref = next_ref(v);
-  load(ref, v, r2);
-  uint2 refn = next_ref(vn);
-  for (uint32_t t = 0; t < n_steps; t += 3) {
+  uint2 qa0, qa1, qa2, qb0, qb1, qb2;
+  bool va0, va1, va2, vb0, vb1, vb2;
+  {
+    bool v;
+    uint2 ref = next_ref(v);
+    load(ref, v, r0);
+    ref = next_ref(v);
+    load(ref, v, r1);
+    ref = next_ref(v);
+    load(ref, v, r2);
+  }
+  qa0 = next_ref(va0);
+  qa1 = next_ref(va1);
+  qa2 = next_ref(va2);
+  for (uint32_t t = 0; t < n_steps; t += 6) {
+    qb0 = next_ref(vb0);
+    qb1 = next_ref(vb1);
+    qb2 = next_ref(vb2);
     add_chunk(col_s, r0);
-    load(refn, vn, r0);
-    refn = next_ref(vn);
+    load(qa0, va0, r0);
     if (t + 1 < n_steps) {
       add_chunk(col_s, r1);
-      load(refn, vn, r1);
-      refn = next_ref(vn);
+      load(qa1, va1, r1);
     }
     if (t + 2 < n_steps) {
       add_chunk(col_s, r2);
-      load(refn, vn, r2);
-      refn = next_ref(vn);
+      load(qa2, va2, r2);
+    }
+    if (t + 3 >= n_steps) break;
+    qa0 = next_ref(va0);
+    qa1 = next_ref(va1);
+    qa2 = next_ref(va2);
+    add_chunk(col_s, r0);
+    load(qb0, vb0, r0);
+    if (t + 4 < n_steps) {
+      add_chunk(col_s, r1);
+      load(qb1, vb1, r1);
+    }
+    if (t + 5 < n_steps) {
+      add_chunk(col_s, r2);
+      load(qb2, vb2, r2);
     }
   }
 }
 
-constexpr int kSlowBatch = 8;  // runs per lane and step of a slow warp
+constexpr int kSlowBatch = 4;  // runs per lane and step of a slow warp
+struct SlowRefs {
+  uint2 ref[kSlowBatch];
+  uint32_t valid;  // bit u: reference u exists
+};
 struct SlowRows {
   double ws[kSlowBatch];
   uint32_t bin[kSlowBatch];
   int q[kSlowBatch];
 };
 
-template <int SLOTS>
-__device__ __forceinline__ void load_slow(const bf_param_tables& prm, const double* __restrict__ chunk_wsum,
-                                          const uint2* refs, uint32_t n_sc, uint32_t base, uint32_t step,
-                                          uint32_t h, int ks, bool live, bool live_q, SlowRows& r) {
-  uint2 ref[kSlowBatch];
-  bool valid[kSlowBatch];
+__device__ __forceinline__ void load_slow_refs(const uint2* refs, uint32_t n_sc, uint32_t base,
+                                               uint32_t step, uint32_t h, SlowRefs& r) {
+  r.valid = 0;
 #pragma unroll
   for (int u = 0; u < kSlowBatch; ++u) {
     const uint32_t i = base + u * step + h;
-    valid[u] = base + u * step < n_sc && i < n_sc;
-    ref[u] = refs[valid[u] ? i : n_sc - 1];
+    const bool ok = base + u * step < n_sc && i < n_sc;
+    r.valid |= ok ? 1u << u : 0u;
+    r.ref[u] = refs[ok ? i : n_sc - 1];
   }
+}
+
+__device__ __forceinline__ void load_slow_rows(const bf_param_tables& prm,
+                                               const double* __restrict__ chunk_wsum,
+                                               const SlowRefs& f, int ks, bool live, bool live_q,
+                                               SlowRows& r) {
 #pragma unroll
   for (int u = 0; u < kSlowBatch; ++u) {
-    r.ws[u] = valid[u] ? __ldg(chunk_wsum + ref[u].y) : 0.0;
-    r.bin[u] = live ? __ldg(prm.slow_bin + static_cast<size_t>(ref[u].x) * prm.slow_pad + ks) : 0u;
-    r.q[u] = live_q ? __ldg(prm.slow_q + static_cast<size_t>(ref[u].x) * prm.slow_pad + ks) : 0;
+    r.ws[u] = ((f.valid >> u) & 1u) ? __ldg(chunk_wsum + f.ref[u].y) : 0.0;
+    r.bin[u] = live ? __ldg(prm.slow_bin + static_cast<size_t>(f.ref[u].x) * prm.slow_pad + ks) : 0u;
+    r.q[u] = live_q ? __ldg(prm.slow_q + static_cast<size_t>(f.ref[u].x) * prm.slow_pad + ks) : 0;
   }
 }
 
 // A slow warp: one update per run of equal slow values with the run's weight sum (written by the
-// grouped weights kernel), eight runs per lane and step; the values of the next step are
-// requested before this step's shared-memory work.  Returns this lane's sum of wsum * fix
-// (fit.py:743).
+// grouped weights kernel), four runs per lane and step.  The references of a step are
+// requested two steps, its values one step before the shared-memory work that uses them.
+// Returns this lane's sum of wsum * fix (fit.py:743).
 template <int SLOTS>
 __device__ __forceinline__ double slow_accumulate(const bf_param_tables& prm,
                                                   const double* __restrict__ chunk_wsum,
@@ -553,12 +583,7 @@ __device__ __forceinline__ double slow_accumulate(const bf_param_tables& prm,
   double eacc = 0.0;
   uint32_t base = first * SLOTS;
   if (base >= n_sc) return 0.0;
-  // two register sets in turn, each refilled right after it has been consumed
-  SlowRows ra, rb;
   const uint32_t stride = kSlowBatch * step;
-  load_slow<SLOTS>(prm, chunk_wsum, refs, n_sc, base, step, h, ks, live, live_q, ra);
-  if (base + stride < n_sc)
-    load_slow<SLOTS>(prm, chunk_wsum, refs, n_sc, base + stride, step, h, ks, live, live_q, rb);
   auto consume = [&](const SlowRows& r) {
 #pragma unroll
     for (int u = 0; u < kSlowBatch; u += 2) add_two(col_s, r.bin[u], r.bin[u + 1], r.ws[u], r.ws[u + 1]);
@@ -567,15 +592,22 @@ __device__ __forceinline__ double slow_accumulate(const bf_param_tables& prm,
       for (int u = 0; u < kSlowBatch; ++u) eacc += r.ws[u] * static_cast<double>(r.q[u]);
     }
   };
+  // steps k (rows in ra), k+1 (rows in rb, requested), k+2 (references in fa, requested)
+  SlowRefs fa, fb;
+  SlowRows ra, rb;
+  load_slow_refs(refs, n_sc, base, step, h, fa);
+  load_slow_rows(prm, chunk_wsum, fa, ks, live, live_q, ra);
+  load_slow_refs(refs, n_sc, base + stride, step, h, fb);
+  load_slow_rows(prm, chunk_wsum, fb, ks, live, live_q, rb);
+  load_slow_refs(refs, n_sc, base + 2 * stride, step, h, fa);
   while (base < n_sc) {
+    load_slow_refs(refs, n_sc, base + 3 * stride, step, h, fb);
     consume(ra);
-    if (base + 2 * stride < n_sc)
-      load_slow<SLOTS>(prm, chunk_wsum, refs, n_sc, base + 2 * stride, step, h, ks, live, live_q, ra);
-    if (base + stride < n_sc) {
-      consume(rb);
-      if (base + 3 * stride < n_sc)
-        load_slow<SLOTS>(prm, chunk_wsum, refs, n_sc, base + 3 * stride, step, h, ks, live, live_q, rb);
-    }
+    load_slow_rows(prm, chunk_wsum, fa, ks, live, live_q, ra);
+    if (base + stride >= n_sc) break;
+    load_slow_refs(refs, n_sc, base + 4 * stride, step, h, fa);
+    consume(rb);
+    load_slow_rows(prm, chunk_wsum, fb, ks, live, live_q, rb);
     base += 2 * stride;
   }
   return eacc;
