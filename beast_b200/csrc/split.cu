@@ -458,7 +458,8 @@ template <int SLOTS>
 __device__ __forceinline__ void fast_accumulate(const uint8_t* __restrict__ bins_lane, uint32_t row_bytes,
                                                 uint32_t bin_mask, const double* __restrict__ weights,
                                                 const uint2* refs, uint32_t n_mc, uint32_t first,
-                                                uint32_t nfw, int lane, double* col) {
+                                                uint32_t nfw, int lane, double* col,
+                                                volatile uint32_t* progress) {
   const uint32_t h = SLOTS == 2 ? static_cast<uint32_t>(lane >> 4) : 0u;
   const uint32_t step = nfw * SLOTS;
   const uint32_t col_s = static_cast<uint32_t>(__cvta_generic_to_shared(col));
@@ -502,6 +503,7 @@ __device__ __forceinline__ void fast_accumulate(const uint8_t* __restrict__ bins
   qa1 = next_ref(va1);
   qa2 = next_ref(va2);
   for (uint32_t t = 0; t < n_steps; t += 6) {
+    if (progress && lane == 0) *progress = start + t * step;  // (the prefetching warps follow it)
     qb0 = next_ref(vb0);
     qb1 = next_ref(vb1);
     qb2 = next_ref(vb2);
@@ -611,6 +613,42 @@ __device__ __forceinline__ double slow_accumulate(const bf_param_tables& prm,
     base += 2 * stride;
   }
   return eacc;
+}
+
+// Warps without a private copy run ahead of the fast warps and pull the rows those will need
+// (a chunk's 8 weights and its bin bytes) into L2: the weights are read once per star, so
+// without this every row request of a fast warp goes to HBM.  kPrefetchAhead bounds the distance
+// in chunks (the chunks in flight over all SMs must stay well inside L2).
+constexpr uint32_t kPrefetchAhead = 1024;
+
+__device__ __forceinline__ void prefetch_l2(const void* p) {
+  asm volatile("prefetch.global.L2 [%0];" ::"l"(p));
+}
+
+__device__ __forceinline__ void prefetch_rows(const bf_param_tables& prm, const double* weights,
+                                              const double* chunk_wsum, const uint2* refs,
+                                              uint32_t n_mc, const uint2* srefs, uint32_t n_sc,
+                                              uint32_t first, uint32_t n_warps, int lane,
+                                              const volatile uint32_t* progress) {
+  const uint32_t row_bytes = static_cast<uint32_t>(prm.fast_pad) * BF_CHUNK;
+  for (uint32_t base = first * 32; base < n_mc; base += n_warps * 32) {
+    while (base >= *progress + kPrefetchAhead) __nanosleep(200);  // warp-uniform
+    const uint32_t i = base + lane;
+    if (i < n_mc) {
+      const uint2 ref = refs[i];
+      prefetch_l2(weights + static_cast<size_t>(ref.y) * BF_CHUNK);
+      const uint8_t* row = prm.fast_bin + static_cast<size_t>(ref.x) * row_bytes;
+      prefetch_l2(row);
+      if (row_bytes > 128) prefetch_l2(row + 128);
+    }
+  }
+  // the slow warp's rows (run sums, bin bytes, values): a fraction of the above, no throttle
+  for (uint32_t i = first * 32 + lane; i < n_sc; i += n_warps * 32) {
+    const uint2 ref = srefs[i];
+    prefetch_l2(chunk_wsum + ref.y);
+    prefetch_l2(prm.slow_bin + static_cast<size_t>(ref.x) * prm.slow_pad);
+    prefetch_l2(prm.slow_q + static_cast<size_t>(ref.x) * prm.slow_pad);
+  }
 }
 
 // occupied bin range of the class parameters over the star's member chunks (four chunks per
@@ -793,9 +831,11 @@ split_hist_kernel(bf_param_tables prm, int hist_doubles, const double* __restric
     if (nf > 0 && F > NW - S - X) F = NW - S - X;
     misc[3] = F;
     misc[4] = S;
+    misc[8] = 0;  // chunks the first fast warp has passed
   }
   __syncthreads();
   const int cf = misc[1], cs = misc[2], F = misc[3], S = misc[4];
+  volatile uint32_t* progress = reinterpret_cast<volatile uint32_t*>(misc + 8);
   const int used = F * cf + S * cs;
   for (int i = threadIdx.x; i < used; i += blockDim.x) hist[i] = 0.0;
   if (threadIdx.x == 0 && sc.star_flags) sc.star_flags[s - star_begin] = 1;
@@ -808,7 +848,9 @@ split_hist_kernel(bf_param_tables prm, int hist_doubles, const double* __restric
       const int kf = lparam[lane];
       fast_accumulate<FS>(prm.fast_bin + (kf >= 0 ? kf : 0) * BF_CHUNK,
                           static_cast<uint32_t>(prm.fast_pad) * BF_CHUNK, kf >= 0 ? 0xffffffffu : 0u,
-                          sc.weights, refs, n_mc, warp, F, lane, hist + warp * cf + lcol[lane]);
+                          sc.weights, refs, n_mc, warp, F, lane, hist + warp * cf + lcol[lane],
+                          warp == 0 ? progress : nullptr);
+      if (warp == 0 && lane == 0) *progress = 0xffffffffu - kPrefetchAhead;  // release the followers
     } else if (warp < F + S) {
       const int ks = lparam[32 + lane];
       const bool live = ks >= 0;
@@ -834,6 +876,9 @@ split_hist_kernel(bf_param_tables prm, int hist_doubles, const double* __restric
         }
       }
       eacc = ((acc8[0] + acc8[1]) + (acc8[2] + acc8[3])) + ((acc8[4] + acc8[5]) + (acc8[6] + acc8[7]));
+      if (F > 0)
+        prefetch_rows(prm, sc.weights, sc.chunk_wsum, refs, n_mc, srefs, n_sc, warp - F - S,
+                      NW - F - S, lane, progress);
     }
   }
   epart[warp * 32 + lane] = eacc;
