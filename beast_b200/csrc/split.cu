@@ -56,23 +56,6 @@ group_scatter_kernel(const uint32_t* __restrict__ list, int64_t entry_base, int6
 constexpr int kGroupedWarps = 8;
 constexpr int kOrderStretch = 128;  // positions of the group order one warp walks in one go
 
-// first index of the smallest chi2 among the member lanes (chi2 >= 0: its bit pattern orders
-// like the value, so two 32-bit warp reductions find the minimum); returns false if no member
-__device__ __forceinline__ bool warp_min_chi2(bool member, double chi2, int lane, double& cmin,
-                                              int& cl) {
-  const unsigned long long u = static_cast<unsigned long long>(__double_as_longlong(chi2));
-  const uint32_t hi = member ? static_cast<uint32_t>(u >> 32) : 0xffffffffu;
-  const uint32_t mh = __reduce_min_sync(0xffffffffu, hi);
-  const bool c1 = member && hi == mh;
-  const uint32_t lo = c1 ? static_cast<uint32_t>(u) : 0xffffffffu;
-  const uint32_t ml = __reduce_min_sync(0xffffffffu, lo);
-  const uint32_t who = __ballot_sync(0xffffffffu, c1 && lo == ml);
-  if (who == 0) return false;
-  cl = __ffs(who) - 1;
-  cmin = __longlong_as_double(static_cast<long long>((static_cast<unsigned long long>(mh) << 32) | ml));
-  return true;
-}
-
 // Per-warp shared memory of the grouped kernel when it also forms the expectation partials of
 // the fast parameters: the weights of up to 8 list positions (A operand) and the group's
 // fixed-point parameter values (B operand) of the FP64 tensor-core products below.
@@ -224,10 +207,17 @@ exact_weights_grouped_kernel(bf_exact_grid grid, const double* __restrict__ flux
         const bool mem1 = ok1 && (lnp1 - M) > threshold;
         const uint32_t mw0 = __ballot_sync(0xffffffffu, mem0);
         const uint32_t mw1 = __ballot_sync(0xffffffffu, mem1);
+        // one exp per lane that has a member; a second one only where a lane has two
         double w0 = 0.0, w1 = 0.0;
         if (mw0 | mw1) {
-          if (mem0) w0 = exp(lnp0 - M);
-          if (mem1) w1 = exp(lnp1 - M);
+          if (mem0 || mem1) {
+            const double r = exp((mem0 ? lnp0 : lnp1) - M);
+            if (mem0) w0 = r;
+            else w1 = r;
+          }
+          if (mw0 & mw1) {
+            if (mem0 && mem1) w1 = exp(lnp1 - M);
+          }
         }
         const int64_t slot = static_cast<int64_t>(e) - entry_base;
         sc.weights[slot * BF_GROUP + lane] = w0;
@@ -271,21 +261,25 @@ exact_weights_grouped_kernel(bf_exact_grid grid, const double* __restrict__ flux
           wsum += __shfl_xor_sync(0xffffffffu, wsum, 8);
           wsum += __shfl_xor_sync(0xffffffffu, wsum, 16);
         }
-        // chi2 minimum of the members, lowest index on ties (fit.py:725-726)
-        double c0 = 0.0, c1 = 0.0;
-        int l0 = 0, l1 = 0;
-        const bool h0 = warp_min_chi2(mem0, a0, lane, c0, l0);
-        const bool h1 = warp_min_chi2(mem1, a1, lane, c1, l1);
+        // chi2 minimum of the members, lowest index on ties (fit.py:725-726): each lane's better
+        // model first, then three 32-bit warp reductions (chi2 >= 0 orders like its bit pattern)
+        const bool has = mem0 || mem1;
+        const bool take1 = mem1 && (!mem0 || a1 < a0);
+        const unsigned long long cu =
+            static_cast<unsigned long long>(__double_as_longlong(take1 ? a1 : a0));
+        const uint32_t chi_hi = has ? static_cast<uint32_t>(cu >> 32) : 0xffffffffu;
+        const uint32_t min_hi = __reduce_min_sync(0xffffffffu, chi_hi);
+        const bool tie_hi = has && chi_hi == min_hi;
+        const uint32_t chi_lo = tie_hi ? static_cast<uint32_t>(cu) : 0xffffffffu;
+        const uint32_t min_lo = __reduce_min_sync(0xffffffffu, chi_lo);
+        const uint32_t cand = (tie_hi && chi_lo == min_lo) ? static_cast<uint32_t>(take1 ? lane + 32 : lane) : 64u;
+        const uint32_t min_idx = __reduce_min_sync(0xffffffffu, cand);
         if (lane == 0) {
           double cm = 1.7976931348623157e308;
           long long cj = -1;
-          if (h0) {
-            cm = c0;
-            cj = static_cast<long long>(g) * BF_GROUP + l0;
-          }
-          if (h1 && (!h0 || c1 < cm)) {
-            cm = c1;
-            cj = static_cast<long long>(g) * BF_GROUP + 32 + l1;
+          if (min_idx < 64u) {
+            cm = __longlong_as_double(static_cast<long long>((static_cast<unsigned long long>(min_hi) << 32) | min_lo));
+            cj = static_cast<long long>(g) * BF_GROUP + min_idx;
           }
           *reinterpret_cast<uint2*>(member_mask + static_cast<size_t>(e) * kWordsPerGroup) =
               make_uint2(mw0, mw1);
@@ -876,7 +870,7 @@ split_hist_kernel(bf_param_tables prm, int hist_doubles, const double* __restric
         }
       }
       eacc = ((acc8[0] + acc8[1]) + (acc8[2] + acc8[3])) + ((acc8[4] + acc8[5]) + (acc8[6] + acc8[7]));
-      if (F > 0)
+      if (F > 0 && NW - F - S >= 4)  // (with fewer idle warps the fast warps cover the latency)
         prefetch_rows(prm, sc.weights, sc.chunk_wsum, refs, n_mc, srefs, n_sc, warp - F - S,
                       NW - F - S, lane, progress);
     }
