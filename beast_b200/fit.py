@@ -32,6 +32,8 @@ __all__ = [
     "save_pdf1d",
     "save_pdf2d",
     "save_lnp",
+    "read_lnp_groups",
+    "write_lnp_groups",
     "FitOutputs",
 ]
 
@@ -167,6 +169,61 @@ def save_lnp(lnp_outname, save_lnp_vals):
             have["star_%d/lnp" % e] = lnp
             have["star_%d/chi2" % e] = chi2
         np.savez(path, **have)
+
+
+def read_lnp_groups(lnp_fname):
+    """{group name: {array name: array}} of an lnp file written by ``save_lnp`` or ``merge_lnp``
+    (groups ``star_<e>``; the root arrays ``grid_waves`` / ``obs_filters`` are left out) --
+    what ``tools/read_beast_data.py:35-57`` walks through"""
+    if os.path.isfile(lnp_fname) and _lnp_backend() != "npz":
+        out = {}
+        if _lnp_backend() == "tables":
+            import tables
+
+            with tables.open_file(lnp_fname, "r") as f:
+                for grp in f.root._f_iter_nodes("Group"):
+                    out[grp._v_name] = {a._v_name: a.read() for a in grp._f_iter_nodes("Array")}
+        else:
+            import h5py
+
+            with h5py.File(lnp_fname, "r") as f:
+                for name in f.keys():
+                    if isinstance(f[name], h5py.Group):
+                        out[name] = {k: f[name][k][()] for k in f[name].keys()}
+        return out
+    have = np.load(_npz_name(lnp_fname))
+    out = {}
+    for key in have.files:
+        if "/" in key:
+            grp, name = key.split("/", 1)
+            out.setdefault(grp, {})[name] = have[key]
+    return out
+
+
+def write_lnp_groups(lnp_fname, groups):
+    """new lnp file holding ``groups`` ({group: {array name: array}}), same container as
+    ``save_lnp`` (PyTables, else h5py, else .npz with "group/array" keys)"""
+    be = _lnp_backend()
+    if be == "tables":
+        import tables
+
+        with tables.open_file(lnp_fname, "w") as f:
+            for label, arrays in groups.items():
+                grp = f.create_group("/", label, title=label)
+                for name, arr in arrays.items():
+                    f.create_array(grp, name, np.asarray(arr))
+    elif be == "h5py":
+        import h5py
+
+        with h5py.File(lnp_fname, "w") as f:
+            for label, arrays in groups.items():
+                grp = f.create_group(label)
+                for name, arr in arrays.items():
+                    grp.create_dataset(name, data=np.asarray(arr))
+    else:
+        np.savez(_npz_name(lnp_fname), **{"%s/%s" % (label, name): np.asarray(arr)
+                                          for label, arrays in groups.items()
+                                          for name, arr in arrays.items()})
 
 
 # ---------------------------------------------------------------------------------------

@@ -80,8 +80,12 @@ class CudaMergeMath:
 
         self.torch = torch
         self.setup = setup
-        self.pct = (C.c_double * 3)(*[float(x) for x in percentiles])
+        self.set_percentiles(percentiles)
         self._tables = None
+
+    def set_percentiles(self, percentiles):
+        """the three percentiles ``finalize`` computes (in percent)"""
+        self.pct = (C.c_double * 3)(*[float(x) for x in percentiles])
 
     def _stream(self, t):
         return C.c_void_p(self.torch.cuda.current_stream(t.device).cuda_stream)
@@ -208,6 +212,208 @@ def local_result_tensors(setup, res, device):
             "chi2min": res.chi2min, "best_vals": best_vals, "exp_vals": res.exp_vals,
             "pdf1d": res.pdf1d}
     return {k: torch.from_numpy(np.ascontiguousarray(v)).to(device) for k, v in host.items()}
+
+
+class _BinLayout:
+    """what CudaMergeMath needs of a FitSetup, rebuilt from a pdf1d file: the bin centres are
+    the last row of every extension (fit.py:507-508)"""
+
+    def __init__(self, bin_rows):
+        self.n_q = len(bin_rows)
+        self.bin_off = np.zeros(self.n_q + 1, dtype=np.int32)
+        self.bin_off[1:] = np.cumsum([len(r) for r in bin_rows])
+        self.total_bins = int(self.bin_off[-1])
+        self.max_bins = int(max(len(r) for r in bin_rows))
+        self.bin_val = np.concatenate(bin_rows).astype(np.float64)
+
+
+def merge_pdf1d_stats(subgrid_pdf1d_fnames, subgrid_stats_fnames, re_run=False,
+                      output_fname_base=None, partial=False, device=None, math=None):
+    """Drop-in for ``beast.tools.subgridding_tools.merge_pdf1d_stats``
+    (subgridding_tools.py:274-539): merge the 1D PDF and stats files of the subgrid fits of one
+    catalog.  Same arguments, checks (``AssertionError`` on mismatching files), output files
+    (``<base>_pdf1d.fits`` / ``<base>_stats.fits`` or ``combined_*``) and return value; the
+    arithmetic runs on the GPU through ``merge_subgrids`` (``csrc/merge.cu``).
+
+    ``device`` / ``math`` are additions: the CUDA device to use, or an object with the
+    ``weights`` / ``scale_rows`` / ``finalize`` methods of ``CudaMergeMath``."""
+    import os
+    import re
+
+    import torch
+
+    from . import fitsio
+    from .fit import save_pdf1d
+
+    pdf1d_fname = (output_fname_base + "_pdf1d.fits") if output_fname_base is not None else "combined_pdf1d.fits"
+    stats_fname = (output_fname_base + "_stats.fits") if output_fname_base is not None else "combined_stats.fits"
+    if os.path.isfile(pdf1d_fname) and os.path.isfile(stats_fname) and re_run is False:
+        print(str(len(subgrid_pdf1d_fnames)) + " files already merged, skipping")
+        return pdf1d_fname, stats_fname
+    nsub = len(subgrid_pdf1d_fnames)
+    if not len(subgrid_stats_fnames) == nsub:
+        raise AssertionError()
+
+    def live_rows(ext_by_name):
+        tot = np.sum(ext_by_name["M_ini"], axis=1)
+        return len(np.where(tot > 0.0)[0]) - 1
+
+    pdf_files = []
+    for fname in subgrid_pdf1d_fnames:
+        hdus = fitsio.read_fits(fname)[1:]
+        pdf_files.append([(h["EXTNAME"], np.asarray(d)) for h, d in hdus])
+    qnames = [q for q, _ in pdf_files[0]]
+    first = dict(pdf_files[0])
+    nobs = live_rows(first) if partial else first[qnames[0]].shape[0] - 1
+    for other in pdf_files[1:]:
+        cur = dict(other)
+        for q in qnames:
+            a0, a = first[q], cur[q]
+            if not a0.shape[1] == a.shape[1]:
+                raise AssertionError()
+            if not partial:
+                if not a0.shape[0] == a.shape[0]:
+                    raise AssertionError()
+            else:
+                nobs = min(nobs, live_rows(cur))
+            if not (np.isnan(a0[-1, 0]) and np.isnan(a[-1, 0]) or (a0[-1, :] == a[-1, :]).all()):
+                raise AssertionError()
+
+    stats, filters_tab = [], None
+    for i, fname in enumerate(subgrid_stats_fnames):
+        hdus = fitsio.read_fits(fname)
+        stats.append(hdus[1][1])
+        if i == 0 and len(hdus) > 2 and isinstance(hdus[2][1], dict):
+            filters_tab = hdus[2][1]
+
+    layout = _BinLayout([first[q][-1, :] for q in qnames])
+    pcols = {}  # parameter -> percentiles present in the stats table, in column order
+    for col in stats[0].keys():
+        suffix = col.split("_")[-1]
+        if re.compile(r"p\d{1,2}$").match(suffix):
+            pcols.setdefault(col[: -len(suffix) - 1], []).append(int(suffix[1:]))
+    pvals = sorted({p for v in pcols.values() for p in v}) or [16, 50, 84]
+    trios = [(pvals[i:i + 3] + [50, 50])[:3] for i in range(0, len(pvals), 3)]
+    if math is None:
+        math = CudaMergeMath(layout, trios[0])
+        dev = torch.device("cuda" if device is None else device)
+    else:
+        math.set_percentiles(trios[0])
+        dev = torch.device("cpu" if device is None else device)
+
+    def t(a, dtype=torch.float64):
+        return torch.from_numpy(np.ascontiguousarray(a)).to(dev, dtype=dtype)
+
+    parts = []
+    for g in range(nsub):
+        cur = dict(pdf_files[g])
+        st = stats[g]
+        parts.append({
+            "total_log_norm": t(np.asarray(st["total_log_norm"])[:nobs]),
+            "Pmax": t(np.asarray(st["Pmax"])[:nobs]),
+            "Pmax_indx": t(np.asarray(st["Pmax_indx"])[:nobs], torch.int64),
+            "chi2min": t(np.asarray(st["chi2min"])[:nobs]),
+            "best_vals": t(np.stack([np.asarray(st[q + "_Best"])[:nobs] for q in qnames], axis=1)),
+            "exp_vals": t(np.stack([np.asarray(st[q + "_Exp"])[:nobs] for q in qnames], axis=1)),
+            "pdf1d": t(np.concatenate([cur[q][:nobs, :] for q in qnames], axis=1)),
+        })
+    merged = merge_subgrids(parts, math)
+    host = {k: v.cpu().numpy() for k, v in merged.items()}
+    per = {p: host["per_vals"][:, :, j] for j, p in enumerate(pvals[:3])}
+    for i, trio in enumerate(trios[1:], start=1):  # the device routine takes three per pass
+        math.set_percentiles(trio)
+        block = math.finalize(merged["pdf1d"].clone()).cpu().numpy()
+        for j, p in enumerate(pvals[3 * i:3 * i + 3]):
+            per[p] = block[:, :, j]
+
+    save_pdf1d_vals = []
+    for k, q in enumerate(qnames):
+        arr = np.zeros((nobs + 1, first[q].shape[1]))
+        arr[:-1, :] = host["pdf1d"][:, layout.bin_off[k]:layout.bin_off[k + 1]]
+        arr[-1, :] = first[q][-1, :]
+        save_pdf1d_vals.append(arr)
+    save_pdf1d(pdf1d_fname, save_pdf1d_vals, qnames)
+
+    stats_dict = {}
+    for col in stats[0].keys():
+        suffix = col.split("_")[-1]
+        if suffix == "Best" and col[:-5] in qnames:
+            stats_dict[col] = host["best_vals"][:, qnames.index(col[:-5])]
+        elif suffix == "Exp" and col[:-4] in qnames:
+            stats_dict[col] = host["exp_vals"][:, qnames.index(col[:-4])]
+        elif re.compile(r"p\d{1,2}$").match(suffix):
+            stats_dict[col] = per[int(suffix[1:])][:, qnames.index(col[: -len(suffix) - 1])]
+        elif col == "chi2min":
+            stats_dict[col] = host["chi2min"]
+        elif col == "Pmax":
+            stats_dict[col] = host["Pmax"]
+        elif col == "Pmax_indx":
+            stats_dict[col] = host["Pmax_indx"]
+        elif col == "total_log_norm":
+            stats_dict[col] = host["total_log_norm"]
+        elif not col == "chi2min_indx" and not col == "specgrid_indx":
+            stats_dict[col] = np.asarray(stats[0][col])[:nobs]
+    stats_dict["best_gridsub_tag"] = host["best_gridsub_tag"]
+    fitsio.write_table_file(stats_fname, [stats_dict] + ([filters_tab] if filters_tab is not None else []))
+    print("Saved combined 1dpdfs in " + pdf1d_fname)
+    print("Saved combined stats in " + stats_fname)
+    return pdf1d_fname, stats_fname
+
+
+def merge_lnp(subgrid_lnp_fnames, re_run=False, output_fname_base=None, threshold=None):
+    """Drop-in for ``beast.tools.subgridding_tools.merge_lnp`` (subgridding_tools.py:542-658):
+    per star, concatenate the sparse (idx, lnp) of every subgrid file in the order given, tag
+    each entry with the subgrid number taken from the ``gridsub<N>`` part of the file name,
+    drop entries that are not within ``threshold`` of the star's merged maximum, and pad all
+    stars to the same length with NaN (idx, subgrid) / -inf (lnp) (:629-656).  Like the
+    reference's reader (tools/read_beast_data.py:47-57) the stars of one file are first padded
+    to that file's longest list; with ``threshold=None`` those padding entries (lnp = -inf,
+    idx = -1 here) stay in the output."""
+    import os
+
+    from .fit import read_lnp_groups, write_lnp_groups
+
+    merged_lnp_fname = "combined_lnp.hd5" if output_fname_base is None else output_fname_base + "_lnp.hd5"
+    if (os.path.isfile(merged_lnp_fname) or os.path.isfile(merged_lnp_fname + ".npz")) and re_run is False:
+        print(str(len(subgrid_lnp_fnames)) + " files already merged, skipping")
+        return merged_lnp_fname
+    per_star, n_star = None, 0
+    for fname in subgrid_lnp_fnames:
+        subgrid_num = int([i for i in os.path.basename(fname).split("_") if "gridsub" in i][0][7:])
+        groups = read_lnp_groups(fname)
+        labels = [k for k in groups.keys() if "star" in k]
+        n_star = len(labels)
+        n_lnp = max(len(groups[k]["lnp"]) for k in labels)
+        if per_star is None:
+            per_star = [([], [], []) for _ in range(n_star)]
+        for i in range(n_star):
+            grp = groups["star_%d" % i]
+            pad = n_lnp - len(grp["lnp"])
+            per_star[i][0].append(np.concatenate([np.asarray(grp["idx"], dtype=float), np.full(pad, -1.0)]))
+            per_star[i][1].append(np.concatenate([np.asarray(grp["lnp"], dtype=float), np.full(pad, -np.inf)]))
+            per_star[i][2].append(np.full(n_lnp, float(subgrid_num)))
+    merged = [merge_star_lnp(np.concatenate(s[0]), np.concatenate(s[1]), np.concatenate(s[2]), threshold)
+              for s in per_star]
+    longest = max(len(m[1]) for m in merged) if threshold is not None else 0
+    groups = {}
+    for i, (idx, lnp, sub) in enumerate(merged):
+        pad = max(longest - len(lnp), 0)
+        groups["star_%d" % i] = {
+            "idx": np.concatenate([idx, np.full(pad, np.nan)]),
+            "lnp": np.concatenate([lnp, np.full(pad, -np.inf)]),
+            "subgrid": np.concatenate([sub, np.full(pad, np.nan)]),
+        }
+    write_lnp_groups(merged_lnp_fname, groups)
+    return merged_lnp_fname
+
+
+def merge_star_lnp(idx, lnp, sub, threshold):
+    """one star of merge_lnp: keep the entries within ``threshold`` of the merged maximum
+    (subgridding_tools.py:606-627); ``threshold=None`` keeps everything"""
+    if threshold is not None and len(lnp):
+        keep = np.where((lnp - lnp.max()) > threshold)[0]
+        idx, lnp, sub = idx[keep], lnp[keep], sub[keep]
+    return idx, lnp, sub
 
 
 def merge_sparse_lnp(per_subgrid, threshold=-10.0):

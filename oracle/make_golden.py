@@ -122,10 +122,86 @@ def make_trim_case(name="trim_tiny"):
     print("wrote", path, "%.0f kB" % (os.path.getsize(path) / 1e3), len(cap["cols"]["fullgrid_idx"]), "of", len(g))
 
 
+def stats_table(s, qnames, p=(16, 50, 84)):
+    """the stats columns as the reference's save_stats names them (fit.py:94-108)"""
+    t = {}
+    for k, q in enumerate(qnames):
+        t[q + "_Best"] = s["best_vals"][:, k]
+        t[q + "_Exp"] = s["exp_vals"][:, k]
+        for i, pv in enumerate(p):
+            t["%s_p%d" % (q, int(pv))] = s["per_vals"][:, k, i]
+    t["chi2min"] = s["chi2min"]
+    t["chi2min_indx"] = s["chi2min_indx"].astype(int)
+    t["Pmax"] = s["Pmax"]
+    t["Pmax_indx"] = s["Pmax_indx"].astype(int)
+    t["specgrid_indx"] = s["specgrid_indx"].astype(int)
+    t["total_log_norm"] = s["total_log_norm"]
+    return t
+
+
+def make_merge_case(name="merge_tiny", n_sub=3, nstars=10, max_nbins=40, threshold=-10.0):
+    """Subgrid mode end to end with the reference's own code (docs/subgrid_parallelism.rst:77-143):
+    row slices of a grid, ``reduce_grid_info`` over them, one ``Q_all_memory`` per slice with
+    ``do_not_normalize=True`` and the shared ``grid_info_dict``, then ``merge_pdf1d_stats`` and
+    ``merge_lnp`` (subgridding_tools.py:189-271, 274-539, 542-658), all unmodified under the
+    in-memory stand-ins of ``oracle/ref_shim.py``."""
+    from beast_b200.subgrid import uniform_slices
+
+    g = synth.make_sedgrid("tiny", seed=31)
+    g["weight"][::9] = 0.0
+    nz = synth.make_noisemodel(g)
+    obs = synth.make_observations(g, nz, nstars, seed=32)
+    keys = fit_oracle.default_keys(g)
+    slices = uniform_slices(len(g), n_sub)
+    subs = [g.subgrid(s) for s in slices]
+    nzs = [{k: v[s] for k, v in nz.items()} for s in slices]
+    info = ref_shim.run_reference_grid_info(subs, nzs)
+    out = pack_inputs(g, nz, obs)
+    out["keys"] = np.array(keys)
+    out["n_sub"], out["max_nbins"], out["threshold"] = n_sub, max_nbins, threshold
+    out["info_keys"] = np.array(list(info.keys()))
+    out["info_min"] = np.array([info[q]["min"] for q in info], dtype=float)
+    out["info_max"] = np.array([info[q]["max"] for q in info], dtype=float)
+    out["info_num_unique"] = np.array([info[q]["num_unique"] for q in info])
+    for q in info:
+        out["info_unique__" + q] = np.asarray(info[q]["unique_vals"])
+    pdfs, tabs, lnps = [], [], []
+    for gi, (sg, snz) in enumerate(zip(subs, nzs)):
+        ref = ref_shim.run_reference_fit(obs, sg, snz, keys, threshold=threshold, max_nbins=max_nbins,
+                                         grid_info_dict=info, do_not_normalize=True)
+        qnames = ref["stats"]["qnames"]
+        pdfs.append(ref["pdf1d"])
+        tabs.append(stats_table(ref["stats"], qnames))
+        stars = []
+        for e in range(nstars):
+            idx, lnp, _ = ref_shim.reference_sparse_set(obs.fluxes[e], sg, snz, threshold, True)
+            stars.append((idx, lnp.astype(np.float32).astype(float)))  # stored float32 (fit.py:705)
+        lnps.append(stars)
+        for k, a in enumerate(ref["pdf1d"]):
+            out["sub%d_pdf1d_%03d" % (gi, k)] = a
+        for c, v in tabs[-1].items():
+            out["sub%d_stats__%s" % (gi, c)] = np.asarray(v)
+    out["ref_qnames"] = np.array(qnames)
+    m_pdf, m_stats = ref_shim.run_reference_merge_pdf1d_stats(pdfs, qnames, tabs)
+    for k, a in enumerate(m_pdf):
+        out["merged_pdf1d_%03d" % k] = a
+    for c, v in m_stats.items():
+        out["merged_stats__" + c] = np.asarray(v)
+    m_lnp = ref_shim.run_reference_merge_lnp(lnps, threshold=threshold)
+    for e, d in enumerate(m_lnp):
+        for c in ("idx", "lnp", "subgrid"):
+            out["merged_lnp_%03d_%s" % (e, c)] = np.asarray(d[c], dtype=float)
+    path = os.path.join(GOLDEN_DIR, name + ".npz")
+    np.savez_compressed(path, **out)
+    print("wrote", path, "%.0f kB" % (os.path.getsize(path) / 1e3))
+
+
 if __name__ == "__main__":
-    names = sys.argv[1:] or list(CASES) + ["trim_tiny"]
+    names = sys.argv[1:] or list(CASES) + ["trim_tiny", "merge_tiny"]
     for n in names:
         if n.startswith("trim"):
             make_trim_case(n)
+        elif n.startswith("merge"):
+            make_merge_case(n)
         else:
             make_case(n)

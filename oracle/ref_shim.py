@@ -223,3 +223,260 @@ def run_reference_trim(sedgrid, noisemodel, obsdata, sigma_fac=3.0, trunchen=Fal
         trim_grid.trim_models(_G, noisemodel, obsdata, "sed_out", "noise_out", sigma_fac=sigma_fac,
                               trunchen=trunchen)
     return captured
+
+
+# ---------------------------------------------------------------------------------------
+# Subgrid tools (tools/subgridding_tools.py) under in-memory stand-ins for their file I/O
+# ---------------------------------------------------------------------------------------
+class _Col(np.ndarray):
+    pass
+
+
+class MemTable:
+    """the slice of astropy.table.Table the reference's merge touches: ``colnames``,
+    ``t[col]`` -> array, construction from a dict (subgridding_tools.py:385-390, 530-532)"""
+
+    def __init__(self, cols=None):
+        self.cols = dict(cols or {})
+
+    @property
+    def colnames(self):
+        return list(self.cols.keys())
+
+    def __getitem__(self, name):
+        return np.asarray(self.cols[name])
+
+
+class _MemHDU:
+    def __init__(self, name, data):
+        self.name, self.data = name, data
+
+
+class _MemHDUList(list):
+    """fits.open(...) result: hdul[1:] -> HDUs with .name, hdul[name].data; a context manager"""
+
+    def __getitem__(self, key):
+        if isinstance(key, str):
+            for h in self:
+                if h.name == key:
+                    return h
+            raise KeyError(key)
+        r = list.__getitem__(self, key)
+        return _MemHDUList(r) if isinstance(key, slice) else r
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        return False
+
+    def writeto(self, name, overwrite=False):
+        self.written_to = name
+
+
+_subgrid_module = None
+
+
+def load_reference_subgridding():
+    """import beast.tools.subgridding_tools from the reference tree.  Its h5py / PyTables /
+    astropy readers are replaced per call by the run_reference_* functions below."""
+    global _subgrid_module
+    if _subgrid_module is not None:
+        return _subgrid_module
+    load_reference_fit()
+    import beast.observationmodel.noisemodel  # noqa: F401  (empty package __init__)
+    import beast.tools  # noqa: F401
+
+    if "beast.observationmodel.noisemodel.generic_noisemodel" not in sys.modules:
+        _stub("beast.observationmodel.noisemodel.generic_noisemodel", get_noisemodelcat=None)
+    if "beast.tools.read_beast_data" not in sys.modules:
+        _stub("beast.tools.read_beast_data", read_lnp_data=None)
+        sys.modules["beast.tools"].read_beast_data = sys.modules["beast.tools.read_beast_data"]
+    from beast.tools import subgridding_tools
+
+    _subgrid_module = subgridding_tools
+    return subgridding_tools
+
+
+def run_reference_grid_info(subgrids, noisemodels, cap_unique=1000):
+    """the reference's ``reduce_grid_info`` (subgridding_tools.py:189-271, which calls its
+    ``subgrid_info`` :117-179) on in-memory subgrids: ``SEDGrid(name)`` / ``get_noisemodelcat(name)``
+    hand back ``subgrids[i]`` / ``noisemodels[i]`` for the name "sub<i>"."""
+    st = load_reference_subgridding()
+
+    class _Disk:
+        def __init__(self, g):
+            self._g = g
+            self.seds = g.seds
+            self.filters = g.filters
+
+        def keys(self):
+            return self._g.keys()
+
+        def __getitem__(self, k):
+            return self._g[k]
+
+    saved = (st.SEDGrid, st.get_noisemodelcat)
+    st.SEDGrid = lambda name, backend=None: _Disk(subgrids[int(name[3:])])
+    st.get_noisemodelcat = lambda name: noisemodels[int(name[3:])]
+    try:
+        with contextlib.redirect_stdout(io.StringIO()):
+            names = ["sub%d" % i for i in range(len(subgrids))]
+            return st.reduce_grid_info(names, names if noisemodels is not None else None,
+                                       nprocs=1, cap_unique=cap_unique)
+    finally:
+        st.SEDGrid, st.get_noisemodelcat = saved
+
+
+def run_reference_merge_pdf1d_stats(pdf1d_per_subgrid, qnames, stats_per_subgrid, filters_tab=None):
+    """the reference's ``merge_pdf1d_stats`` (subgridding_tools.py:274-539) verbatim, with
+    ``fits.open`` / ``Table.read`` serving the given arrays and ``save_pdf1d`` /
+    ``HDUList.writeto`` captured.
+
+    pdf1d_per_subgrid[g] : list of (nobs+1, nbins) arrays in ``qnames`` order
+    stats_per_subgrid[g] : dict column -> array (the stats table of subgrid g)
+    Returns (merged pdf1d arrays, merged stats dict)."""
+    st = load_reference_subgridding()
+    captured = {}
+    ng = len(pdf1d_per_subgrid)
+
+    def fits_open(name):
+        g = int(name.split("sub")[1].split("_")[0])
+        return _MemHDUList([_MemHDU("PRIMARY", None)] +
+                           [_MemHDU(q, np.array(a)) for q, a in zip(qnames, pdf1d_per_subgrid[g])])
+
+    class _Table(MemTable):
+        @staticmethod
+        def read(name, hdu=1):
+            g = int(name.split("sub")[1].split("_")[0])
+            if hdu == 1:
+                return MemTable(stats_per_subgrid[g])
+            if filters_tab is None:
+                raise ValueError("no such HDU")
+            return MemTable(filters_tab)
+
+    def table_to_hdu(tab):
+        return tab
+
+    def cap_pdf1d(outname, vals, qn):
+        captured["pdf1d"] = [np.array(v) for v in vals]
+        captured["pdf1d_qnames"] = list(qn)
+
+    fits_ns = types.SimpleNamespace(open=fits_open, HDUList=_MemHDUList, table_to_hdu=table_to_hdu)
+    saved = (st.fits, st.Table, st.save_pdf1d)
+    st.fits, st.Table, st.save_pdf1d = fits_ns, _Table, cap_pdf1d
+    # the merged stats table is appended to an HDUList: catch it there
+    orig_append = _MemHDUList.append
+
+    def append(self, item):
+        if isinstance(item, MemTable) and "stats" not in captured:
+            captured["stats"] = {k: np.asarray(v) for k, v in item.cols.items()}
+        orig_append(self, item)
+
+    _MemHDUList.append = append
+    try:
+        with contextlib.redirect_stdout(io.StringIO()):
+            st.merge_pdf1d_stats(["sub%d_pdf1d.fits" % g for g in range(ng)],
+                                 ["sub%d_stats.fits" % g for g in range(ng)], re_run=True,
+                                 output_fname_base="/nonexistent/merged")
+    finally:
+        st.fits, st.Table, st.save_pdf1d = saved
+        _MemHDUList.append = orig_append
+    return captured["pdf1d"], captured["stats"]
+
+
+def run_reference_merge_lnp(lnp_per_subgrid, threshold=-10.0):
+    """the reference's ``merge_lnp`` (subgridding_tools.py:542-658) verbatim.
+    ``lnp_per_subgrid[g]`` = list over stars of (idx, lnp) arrays.  ``read_lnp_data`` (an h5py
+    reader, tools/read_beast_data.py:13-65, whose ``np.full(..., np.nan, dtype=int)`` no longer
+    runs on NumPy 2) is replaced by a stand-in that pads the same way (-inf lnp; index -1), and
+    ``tables.open_file`` by a capture.  Returns a list over stars of dicts idx / lnp / subgrid."""
+    st = load_reference_subgridding()
+    out = {}
+
+    def read_lnp_data(fname, nstars=None, shift_lnp=True):
+        g = int([i for i in fname.split("_") if "gridsub" in i][0][7:])
+        stars = lnp_per_subgrid[g]
+        n = max(len(s[0]) for s in stars)
+        vals = np.full((n, len(stars)), -np.inf)
+        indxs = np.full((n, len(stars)), -1, dtype=int)
+        for k, (idx, lnp) in enumerate(stars):
+            vals[:len(lnp), k] = lnp
+            indxs[:len(idx), k] = idx
+        return {"vals": vals, "indxs": indxs}
+
+    class _Out:
+        def __enter__(self):
+            return self
+
+        def __exit__(self, *a):
+            return False
+
+        def create_group(self, root, label, title=None):
+            out[label] = {}
+            return label
+
+        def create_array(self, group, name, arr):
+            out[group][name] = np.array(arr)
+
+    saved = (st.read_beast_data.read_lnp_data, st.tables.open_file)
+    st.read_beast_data.read_lnp_data = read_lnp_data
+    st.tables.open_file = lambda *a, **k: _Out()
+    try:
+        with contextlib.redirect_stdout(io.StringIO()):
+            st.merge_lnp(["x_gridsub%d_lnp.hd5" % g for g in range(len(lnp_per_subgrid))],
+                         re_run=True, output_fname_base="/nonexistent/merged", threshold=threshold)
+    finally:
+        st.read_beast_data.read_lnp_data, st.tables.open_file = saved
+    return [out["star_%d" % i] for i in range(len(lnp_per_subgrid[0]))]
+
+
+def run_reference_merge_stats(tables_by_name, filters_tab=None, reorder_tag_list=None):
+    """the reference's ``merge_stats_files`` (tools/merge_beast_stats.py:12-71) on in-memory
+    tables: ``Table.read`` serves ``tables_by_name[file name]``; ``Column`` / ``add_column`` /
+    ``vstack`` are plain stand-ins (row-wise concatenation of equal-column tables), so what is
+    pinned is the function's own logic -- tag extraction from the file names, the added
+    ``reorder_tag`` column, the filter table and the return value."""
+    load_reference_fit()
+    captured = {}
+
+    class _T(MemTable):
+        @staticmethod
+        def read(name, hdu=1):
+            if hdu == 1:
+                return _T(tables_by_name[name])
+            if filters_tab is None:
+                raise ValueError("no such HDU")
+            return _T(filters_tab)
+
+        def __len__(self):
+            return len(next(iter(self.cols.values()))) if self.cols else 0
+
+        def add_column(self, col):
+            self.cols[col[1]] = np.array(col[0])
+
+    def column(values, name=None):
+        return (values, name)
+
+    def vstack(tabs):
+        names = tabs[0].colnames
+        return _T({k: np.concatenate([np.asarray(t.cols[k]) for t in tabs]) for k in names})
+
+    class _HL(_MemHDUList):
+        def append(self, item):
+            captured.setdefault("hdus", []).append(dict(item.cols))
+            list.append(self, item)
+
+    sys.modules["astropy.table"].Table = _T
+    sys.modules["astropy.table"].Column = column
+    sys.modules["astropy.table"].vstack = vstack
+    sys.modules["astropy.io.fits"].HDUList = _HL
+    sys.modules["astropy.io.fits"].table_to_hdu = lambda t: t
+    sys.modules["astropy.io"].fits = sys.modules["astropy.io.fits"]
+    sys.modules.pop("beast.tools.merge_beast_stats", None)
+    import beast.tools  # noqa: F401
+    from beast.tools import merge_beast_stats
+
+    n = merge_beast_stats.merge_stats_files(list(tables_by_name.keys()), "/nonexistent/out",
+                                            reorder_tag_list=reorder_tag_list)
+    return n, captured["hdus"]

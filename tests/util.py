@@ -83,3 +83,44 @@ def compare_sparse(setup, res, off, idx, lnp, chi2):
     np.testing.assert_array_equal(g0[res.sparse_j], idx)
     np.testing.assert_allclose(res.sparse_lnp, lnp.astype(np.float32), rtol=0, atol=LNP_ATOL)
     np.testing.assert_allclose(res.sparse_chi2, chi2.astype(np.float32), rtol=1e-6, atol=1e-6)
+
+
+class NumpyMergeMath:
+    """test double for beast_b200.subgrid.CudaMergeMath (the product's own hooks are CUDA
+    kernels): the same four hooks in NumPy, percentiles with the oracle's restated function"""
+
+    def __init__(self, bin_rows, percentiles=(16.0, 50.0, 84.0)):
+        self.bin_rows = [np.asarray(b, dtype=float) for b in bin_rows]
+        self.set_percentiles(percentiles)
+
+    def set_percentiles(self, percentiles):
+        self.pct = tuple(float(x) for x in percentiles)
+
+    def weights(self, tln_all):
+        import torch
+
+        t = tln_all.numpy()
+        mx = t.max(axis=0)
+        w = np.exp(t - mx[None, :])
+        return torch.from_numpy(w), torch.from_numpy(np.log(w.sum(axis=0)) + mx)
+
+    def scale_rows(self, rows, w):
+        return rows * w.reshape(-1, *([1] * (rows.dim() - 1)))
+
+    def finalize(self, pdf):
+        import torch
+
+        from oracle import fit_oracle as fo
+
+        p = pdf.numpy()
+        per = np.zeros((p.shape[0], len(self.bin_rows), 3))
+        off = 0
+        for k, b in enumerate(self.bin_rows):
+            blk = p[:, off:off + len(b)]
+            norm = blk.sum(axis=1, keepdims=True)
+            np.divide(blk, norm, out=blk, where=norm > 0)
+            for e in range(p.shape[0]):
+                if blk[e].max() > 0:
+                    per[e, k] = fo.percentile(b, list(self.pct), blk[e])
+            off += len(b)
+        return torch.from_numpy(per)
