@@ -467,16 +467,22 @@ def run_reference_merge_stats(tables_by_name, filters_tab=None, reorder_tag_list
             captured.setdefault("hdus", []).append(dict(item.cols))
             list.append(self, item)
 
-    sys.modules["astropy.table"].Table = _T
-    sys.modules["astropy.table"].Column = column
-    sys.modules["astropy.table"].vstack = vstack
-    sys.modules["astropy.io.fits"].HDUList = _HL
-    sys.modules["astropy.io.fits"].table_to_hdu = lambda t: t
-    sys.modules["astropy.io"].fits = sys.modules["astropy.io.fits"]
+    tmod, fmod = sys.modules["astropy.table"], sys.modules["astropy.io.fits"]
+    saved_t, saved_f = dict(tmod.__dict__), dict(fmod.__dict__)
+    tmod.Table, tmod.Column, tmod.vstack = _T, column, vstack
+    fmod.HDUList, fmod.table_to_hdu = _HL, (lambda t: t)
+    sys.modules["astropy.io"].fits = fmod
     sys.modules.pop("beast.tools.merge_beast_stats", None)
-    import beast.tools  # noqa: F401
-    from beast.tools import merge_beast_stats
+    try:
+        import beast.tools  # noqa: F401
+        from beast.tools import merge_beast_stats
 
-    n = merge_beast_stats.merge_stats_files(list(tables_by_name.keys()), "/nonexistent/out",
-                                            reorder_tag_list=reorder_tag_list)
+        n = merge_beast_stats.merge_stats_files(list(tables_by_name.keys()), "/nonexistent/out",
+                                                reorder_tag_list=reorder_tag_list)
+    finally:  # the stubs are shared with the other run_reference_* functions
+        tmod.__dict__.clear()
+        tmod.__dict__.update(saved_t)
+        fmod.__dict__.clear()
+        fmod.__dict__.update(saved_f)
+        sys.modules.pop("beast.tools.merge_beast_stats", None)
     return n, captured["hdus"]
