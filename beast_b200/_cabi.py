@@ -95,6 +95,57 @@ class StarOutputs(C.Structure):
     ]
 
 
+class FitPlan(C.Structure):
+    _fields_ = [
+        ("nb", C.c_int),
+        ("full_cov", C.c_int),
+        ("n_groups", i64),
+        ("n_tiles", i64),
+        ("tiles", c_void_p),
+        ("n_tiles_coarse", i64),
+        ("tiles_coarse", c_void_p),
+        ("inv_band_scale", c_void_p),
+        ("err_a", C.c_float),
+        ("err_b", C.c_float),
+        ("grid", ExactGrid),
+        ("params", ParamTables),
+        ("n_pairs", C.c_int),
+        ("pair_bin", c_void_p),
+        ("pair_off", c_void_p),
+        ("pair_len", i64),
+        ("sm_count", C.c_int),
+        ("force_legacy", C.c_int),
+    ]
+
+
+class FitOutputsC(C.Structure):
+    _fields_ = [(n, c_void_p) for n in (
+        "pmax", "pmax_j", "total_log_norm", "chi2min", "chi2min_j", "n_sparse", "n_groups_selected",
+        "exp_vals", "pdf1d", "per_vals", "pdf2d", "sparse_off", "sparse_j", "sparse_lnp",
+        "sparse_chi2")] + [("sparse_capacity", i64)]
+
+
+class FitState(C.Structure):
+    _fields_ = [
+        ("flux64", c_void_p),
+        ("offsets", c_void_p),
+        ("list", c_void_p),
+        ("member_mask", c_void_p),
+        ("member_prefix", c_void_p),
+        ("perm", c_void_p),
+        ("n_sparse_sorted", c_void_p),
+        ("n_list", i64),
+        ("n_records", i64),
+        ("launches", i64),
+        ("split", C.c_int),
+        ("want_timing", C.c_int),
+        ("stage_ms", C.c_float * 12),
+    ]
+
+
+STAGES = ("presort", "dense", "select", "exact_max", "group_order", "exact_weights", "histograms",
+          "expectations", "pdf2d", "reorder", "sparse_records")
+
 # name -> (restype, argtypes); every symbol declared in include/beast_b200.h
 PROTOTYPES = {
     "bf_last_error": (C.c_char_p, []),
@@ -114,6 +165,13 @@ PROTOTYPES = {
     "bf_exclusive_scan_u32_noalloc": (C.c_int, [i64, c_void_p, c_void_p, c_void_p]),
     "bf_group_order_work_elems": (i64, [i64]),
     "bf_group_order": (C.c_int, [i64, c_void_p, i64, i64, c_void_p, c_void_p, c_void_p]),
+    "bf_fit_workspace_bytes": (i64, [C.POINTER(FitPlan), i64, i64]),
+    "bf_fit_batch": (C.c_int, [C.POINTER(FitPlan), i64, c_void_p, C.c_int, C.c_double,
+                               C.POINTER(C.c_double), C.c_int, i64, C.c_uint64, i64, c_void_p,
+                               C.c_size_t, C.POINTER(FitOutputsC), C.POINTER(FitState), c_void_p,
+                               c_void_p]),
+    "bf_fit_sparse_records": (C.c_int, [C.POINTER(FitPlan), C.POINTER(FitState), i64, c_void_p,
+                                        c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]),
     "bf_exact_max": (C.c_int, [C.POINTER(ExactGrid), i64, i64, c_void_p, c_void_p, c_void_p,
                                C.c_float, C.c_float, c_void_p, c_void_p, c_void_p, c_void_p,
                                c_void_p]),

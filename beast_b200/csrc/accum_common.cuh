@@ -116,6 +116,15 @@ __device__ __forceinline__ void star_percentiles_and_prefix(const bf_param_table
 }
 
 
+// Per-kernel device times of bf_exact_accumulate for a caller that asked for them
+// (bf_fit_batch with state->want_timing): the calling thread switches it on, every call then
+// synchronises and adds its kernels' times.
+struct AccumTimer {
+  bool on = false;
+  float weights_ms = 0.f, hist_ms = 0.f, exp_ms = 0.f;
+};
+extern thread_local AccumTimer g_accum_timer;
+
 // ---- the split sparse pass (split.cu), launched from bf_exact_accumulate --------------------
 // group-ordered exact weights kernel: same outputs as exact_weights_kernel
 int launch_weights_grouped(const bf_exact_grid& grid, const double* flux64, const double* pmax,

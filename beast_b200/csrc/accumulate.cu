@@ -26,6 +26,8 @@
 
 namespace bf {
 
+thread_local AccumTimer g_accum_timer;
+
 constexpr int kWeightWarps = 8;
 constexpr int kStageDoubles = BF_GROUP;  // per-warp staging: the current group's weights
 constexpr int kSideBlocksPerSm = 64;  // grid cap of the grid-stride kernels, in blocks per SM
@@ -807,7 +809,8 @@ extern "C" int bf_exact_accumulate(const bf_exact_grid* grid, const bf_param_tab
              "bf_exact_accumulate: null output pointer");
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   // BF_TIMING=1: synchronous per-kernel timing of this call on stderr (diagnostics only)
-  static const bool timing = getenv("BF_TIMING") != nullptr;
+  static const bool env_timing = getenv("BF_TIMING") != nullptr;
+  const bool timing = env_timing || g_accum_timer.on;
   cudaEvent_t tev[5] = {};
   if (timing) {
     for (auto& e : tev) cudaEventCreate(&e);
@@ -928,9 +931,12 @@ extern "C" int bf_exact_accumulate(const bf_exact_grid* grid, const bf_param_tab
       float w = 0, h = 0;
       cudaEventElapsedTime(&w, tev[0], tev[1]);
       cudaEventElapsedTime(&h, tev[1], tev[2]);
-      fprintf(stderr, "[bf timing] stars=%lld entries=%lld weights=%.2f ms (%s) split hist=%.2f ms\n",
-              static_cast<long long>(n_stars), static_cast<long long>(n_entries), w,
-              scratch->group_order ? "grouped" : "by star", h);
+      g_accum_timer.weights_ms += w;
+      g_accum_timer.hist_ms += h;
+      if (env_timing)
+        fprintf(stderr, "[bf timing] stars=%lld entries=%lld weights=%.2f ms (%s) split hist=%.2f ms\n",
+                static_cast<long long>(n_stars), static_cast<long long>(n_entries), w,
+                scratch->group_order ? "grouped" : "by star", h);
       for (auto& e : tev) cudaEventDestroy(e);
     }
     return BF_OK;
@@ -938,7 +944,7 @@ extern "C" int bf_exact_accumulate(const bf_exact_grid* grid, const bf_param_tab
   BF_REQUIRE(params->bin_tab && params->q_tab,
              "bf_exact_accumulate: the per-model tables bin_tab / q_tab are needed (no class split "
              "usable for this call)");
-  if (timing && getenv("BF_TIMING")[0] == '2') aux_stream = nullptr;  // serial: each kernel alone
+  if (timing && (g_accum_timer.on || getenv("BF_TIMING")[0] == '2')) aux_stream = nullptr;  // each kernel alone
   // the windowed kernel tells the expectation kernel which stars it has done: same stream
   if (use_window) aux_stream = nullptr;
   cudaStream_t sx = aux_stream ? static_cast<cudaStream_t>(aux_stream) : st;
@@ -989,10 +995,14 @@ extern "C" int bf_exact_accumulate(const bf_exact_grid* grid, const bf_param_tab
     cudaEventElapsedTime(&h, tev[1], tev[2]);
     cudaEventElapsedTime(&x, tev[3], tev[4]);
     cudaEventElapsedTime(&tot, tev[0], tev[4]);
-    fprintf(stderr, "[bf timing] stars=%lld entries=%lld weights=%.2f ms hist=%.2f ms exp=%.2f ms "
-            "(exp end - start of call = %.2f ms, hist warps=%d%s)\n",
-            static_cast<long long>(n_stars), static_cast<long long>(n_entries), w, h, x, tot,
-            use_window ? kWindowWarps : nw, use_window ? " windowed" : "");
+    g_accum_timer.weights_ms += w;
+    g_accum_timer.hist_ms += h;
+    g_accum_timer.exp_ms += x;
+    if (env_timing)
+      fprintf(stderr, "[bf timing] stars=%lld entries=%lld weights=%.2f ms hist=%.2f ms exp=%.2f ms "
+              "(exp end - start of call = %.2f ms, hist warps=%d%s)\n",
+              static_cast<long long>(n_stars), static_cast<long long>(n_entries), w, h, x, tot,
+              use_window ? kWindowWarps : nw, use_window ? " windowed" : "");
     for (auto& e : tev) cudaEventDestroy(e);
   }
   return BF_OK;

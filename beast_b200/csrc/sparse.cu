@@ -102,6 +102,79 @@ __global__ void sample_ranks_kernel(int64_t n_stars, const uint32_t* __restrict_
     ranks[r0 + i] = (k >= n) ? i : feistel_perm(i, n, key);
 }
 
+// Sparse records of a whole batch whose stars were fitted in another order than the caller's:
+// block i works on the i-th star of the fit order, input star perm[i] (perm == nullptr: the same
+// order); its records go to out_off[input star] of the output arrays.  The ranks are the ones
+// given (positions out_off[.] + r of `ranks`), or all of 0..n-1, or -- lnp_npts > 0 -- the first
+// min(n, lnp_npts) values of the keyed permutation of sample_ranks_kernel.
+__global__ void __launch_bounds__(kGatherThreads)
+sparse_records_kernel(bf_exact_grid grid, const double* __restrict__ flux64,
+                      const uint32_t* __restrict__ offsets, const uint32_t* __restrict__ list,
+                      const uint32_t* __restrict__ member_mask,
+                      const uint32_t* __restrict__ member_prefix,
+                      const uint32_t* __restrict__ n_sparse_sorted, const int32_t* __restrict__ perm,
+                      const int64_t* __restrict__ out_off, const uint32_t* __restrict__ ranks,
+                      int64_t lnp_npts, uint64_t seed, int64_t star_base,
+                      int64_t* __restrict__ out_j, float* __restrict__ out_lnp,
+                      float* __restrict__ out_chi2) {
+  __shared__ double sflux[BF_MAX_BANDS];
+  const int64_t s = blockIdx.x;
+  const int64_t s_in = perm ? perm[s] : s;
+  if (threadIdx.x < grid.nb) sflux[threadIdx.x] = flux64[s * grid.nb + threadIdx.x];
+  __syncthreads();
+  const uint32_t e0 = offsets[s * BF_SELECT_SPLIT];
+  const uint32_t e1 = offsets[(s + 1) * BF_SELECT_SPLIT];
+  const uint32_t n = n_sparse_sorted[s];
+  const int64_t r0 = out_off[s_in];
+  const uint32_t k = static_cast<uint32_t>(out_off[s_in + 1] - r0);
+  const uint64_t sid = static_cast<uint64_t>(star_base + s_in);
+  const uint32_t key = mix32(static_cast<uint32_t>(seed) ^ mix32(static_cast<uint32_t>(sid) * 0x9e3779b9u +
+                                                               static_cast<uint32_t>(seed >> 32)));
+  for (uint32_t r = threadIdx.x; r < k; r += kGatherThreads) {
+    uint32_t rank = r;
+    if (ranks) rank = ranks[r0 + r];
+    else if (lnp_npts > 0 && k < n) rank = feistel_perm(r, n, key);
+    uint32_t lo = e0, hi = e1;  // invariant: prefix[lo] <= rank, answer in [lo, hi)
+    while (hi - lo > 1) {
+      const uint32_t mid = lo + (hi - lo) / 2;
+      if (member_prefix[mid] <= rank) lo = mid; else hi = mid;
+    }
+    uint32_t local = rank - member_prefix[lo];
+    int64_t j = -1;
+#pragma unroll
+    for (int h = 0; h < kWordsPerGroup; ++h) {
+      const uint32_t word = member_mask[static_cast<size_t>(lo) * kWordsPerGroup + h];
+      const uint32_t c = __popc(word);
+      if (j < 0) {
+        if (local < c) {
+          const int bit = __fns(word, 0, static_cast<int>(local) + 1);
+          j = static_cast<int64_t>(list[lo]) * BF_GROUP + h * 32 + bit;
+        } else {
+          local -= c;
+        }
+      }
+    }
+    double lnp = 0.0, chi2 = 0.0;
+    if (j >= 0) exact_lnp(grid, sflux, j, lnp, chi2);
+    out_j[r0 + r] = j;
+    out_lnp[r0 + r] = static_cast<float>(lnp);
+    out_chi2[r0 + r] = static_cast<float>(chi2);
+  }
+}
+
+int launch_sparse_records(const bf_exact_grid& grid, int64_t n_stars, const double* flux64,
+                          const uint32_t* offsets, const uint32_t* list, const uint32_t* member_mask,
+                          const uint32_t* member_prefix, const uint32_t* n_sparse_sorted,
+                          const int32_t* perm, const int64_t* out_off, const uint32_t* ranks,
+                          int64_t lnp_npts, uint64_t seed, int64_t star_base, int64_t* out_j,
+                          float* out_lnp, float* out_chi2, cudaStream_t st) {
+  sparse_records_kernel<<<static_cast<unsigned>(n_stars), kGatherThreads, 0, st>>>(
+      grid, flux64, offsets, list, member_mask, member_prefix, n_sparse_sorted, perm, out_off, ranks,
+      lnp_npts, seed, star_base, out_j, out_lnp, out_chi2);
+  BF_CHECK_LAUNCH("sparse_records_kernel");
+  return BF_OK;
+}
+
 // one warp per listed group; weights are already normalised: exp(lnp - total_log_norm)
 constexpr int kPdf2dWarps = 8;
 

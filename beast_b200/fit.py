@@ -302,18 +302,24 @@ def Q_all_memory(prev_result, obs, sedgrid, obsmodel, qnames_in, p=[16.0, 50.0, 
                  gridbackend="cache", max_nbins=200, stats_outname=None, pdf1d_outname=None,
                  pdf2d_outname=None, pdf2d_param_list=None, grid_info_dict=None, lnp_outname=None,
                  lnp_npts=None, save_every_npts=None, threshold=-40, resume=False,
-                 use_full_cov_matrix=True, do_not_normalize=False, lnp_rng="numpy", device=None,
-                 engine=None):
+                 use_full_cov_matrix=True, do_not_normalize=False, lnp_rng="device", device=None,
+                 engine=None, keep_lnp=False):
     """Fit each star, compute the fit statistics and write them to files (fit.py:313-833).
 
-    Arguments as in the reference; ``lnp_rng`` / ``device`` / ``engine`` are additions
-    (``engine`` lets a caller reuse a resident grid across calls).  ``qnames_in`` is extended
-    in place with the symlog flux parameter names, as the reference does (fit.py:456-459).
-    """
-    from .engine import FitEngine
+    Arguments as in the reference.  Additions: ``lnp_rng`` ("device": the lnp_npts subsample of
+    the sparse lnP is drawn on the GPU; "numpy": with ``np.random.choice`` in catalog order, the
+    reference's own random stream, at O(|S|) host work per star), ``device``, ``engine`` (a
+    ``FitEngine`` whose resident grid is reused across calls; with ``engine.reuse_buffers`` set
+    the returned arrays are the engine's page-locked buffers and are overwritten by its next
+    call) and ``keep_lnp`` (return the sparse lnP records in ``FitOutputs.save_lnp_vals`` even
+    when no lnp file is written).  ``qnames_in`` is extended in place with the symlog flux
+    parameter names, as the reference does (fit.py:456-459).
 
-    if len(p) != 3:
-        raise NotImplementedError("the CUDA path computes exactly three percentiles (got %d)" % len(p))
+    The arrays of the returned ``FitOutputs`` are views of the page-locked buffers the GPU
+    results were copied into: one (nobs+1, total_bins) block for all 1D PDFs, whose column
+    ranges are the per-parameter arrays (last row = bin centres) the reference builds."""
+    from .engine import FitEngine, FitResult
+
     g0 = _load_grid(sedgrid, gridbackend)
     make_pdf2d = pdf2d_outname is not None
     if engine is None:
@@ -329,29 +335,47 @@ def Q_all_memory(prev_result, obs, sedgrid, obsmodel, qnames_in, p=[16.0, 50.0, 
         qnames_in.append("symlog" + f + "_wd_bias")
     qnames = setup.qnames
     nobs, nq = len(obs), setup.n_q
+    pvals = [float(x) for x in p]
+    trios = [(pvals[i:i + 3] + [50.0, 50.0])[:3] for i in range(0, len(pvals), 3)] or [[16.0, 50.0, 84.0]]
+
+    sparse = None
+    if lnp_outname is not None or keep_lnp:
+        sparse = "all" if lnp_npts is None else int(lnp_npts)
+    pair_len = int(setup.pair_off[-1]) if (make_pdf2d and setup.pair_off is not None) else 0
+    cap = nobs * int(sparse) if (sparse is not None and sparse != "all") else 0
+    key = ("Q", nobs, pair_len, cap)
+    res = engine._result_cache.get(key) if getattr(engine, "reuse_buffers", False) else None
+    if res is None:
+        res = FitResult(nobs, nq, setup.total_bins, pair_len, cap, extra_rows=1, extra_rows_2d=2)
+        if getattr(engine, "reuse_buffers", False):
+            engine._result_cache = {key: res}
+    res.sparse_filled, res.sparse_off = 0, None
+    res.pdf1d[nobs, :] = setup.bin_val
+    if pair_len:
+        for k, pr in enumerate(setup.pairs):
+            a0, b0 = setup.pair_off[k], setup.pair_off[k + 1]
+            res.pdf2d[nobs, a0:b0] = np.tile(pr.bin_vals_p1, (pr.nb2, 1)).T.ravel()
+            res.pdf2d[nobs + 1, a0:b0] = np.tile(pr.bin_vals_p2, (pr.nb1, 1)).ravel()
 
     out = FitOutputs()
     out.qnames = list(qnames)
     out.best_vals = np.zeros((nobs, nq))
-    out.exp_vals = np.zeros((nobs, nq))
-    out.per_vals = np.zeros((nobs, nq, 3))
-    out.chi2_vals = np.zeros(nobs)
+    out.per_vals = np.zeros((nobs, nq, len(pvals))) if len(pvals) != 3 else res.per_vals
+    out.exp_vals = res.exp_vals
+    out.chi2_vals, out.lnp_vals, out.total_log_norm = res.chi2min, res.Pmax, res.total_log_norm
     out.chi2_indx = np.zeros(nobs)
-    out.lnp_vals = np.zeros(nobs)
     out.lnp_indx = np.zeros(nobs)
     out.best_specgrid_indx = np.zeros(nobs)
-    out.total_log_norm = np.zeros(nobs)
-    for k in range(nq):
-        a = np.zeros((nobs + 1, setup.bins[k].nbins))
-        a[-1, :] = setup.bins[k].bin_vals
-        out.save_pdf1d_vals.append(a)
+    out.save_pdf1d_vals = [res.pdf1d[:, setup.bin_off[k]:setup.bin_off[k + 1]] for k in range(nq)]
     if make_pdf2d:
         out.pdf2d_qname_pairs = [pr.name for pr in setup.pairs]
-        for pr in setup.pairs:
-            a = np.zeros((nobs + 2, pr.nb1, pr.nb2))
-            a[-2, :, :] = np.tile(pr.bin_vals_p1, (pr.nb2, 1)).T
-            a[-1, :, :] = np.tile(pr.bin_vals_p2, (pr.nb1, 1))
-            out.save_pdf2d_vals.append(a)
+        out.save_pdf2d_vals = [res.pdf2d[:, setup.pair_off[k]:setup.pair_off[k + 1]].reshape(nobs + 2, pr.nb1, pr.nb2)
+                               for k, pr in enumerate(setup.pairs)]
+    for name in ("Pmax", "Pmax_j", "total_log_norm", "chi2min", "chi2min_j", "exp_vals", "per_vals"):
+        getattr(res, name)[...] = 0  # rows not fitted yet read as zeros, as in the reference
+    res.pdf1d[:nobs] = 0
+    if pair_len:
+        res.pdf2d[:nobs] = 0
 
     start_pos = 0
     if resume:
@@ -362,13 +386,13 @@ def Q_all_memory(prev_result, obs, sedgrid, obsmodel, qnames_in, p=[16.0, 50.0, 
             out.exp_vals[:, k] = tab["{0:s}_Exp".format(qname)]
             for i, pval in enumerate(p):
                 out.per_vals[:, k, i] = tab["{0:s}_p{1:d}".format(qname, int(pval))]
-        out.chi2_vals = np.array(tab["chi2min"], dtype=float)
+        out.chi2_vals[:] = np.array(tab["chi2min"], dtype=float)
         out.chi2_indx = np.array(tab["chi2min_indx"], dtype=float)
-        out.lnp_vals = np.array(tab["Pmax"], dtype=float)
+        out.lnp_vals[:] = np.array(tab["Pmax"], dtype=float)
         out.lnp_indx = np.array(tab["Pmax_indx"], dtype=float)
         out.best_specgrid_indx = np.array(tab["specgrid_indx"], dtype=float)
         if "total_log_norm" in tab:
-            out.total_log_norm = np.array(tab["total_log_norm"], dtype=float)
+            out.total_log_norm[:] = np.array(tab["total_log_norm"], dtype=float)
         (done,) = np.where(out.lnp_vals != 0.0)
         start_pos = int(max(done)) + 1
         print("resuming run with start indx = " + str(start_pos) + " out of " + str(nobs))
@@ -376,16 +400,39 @@ def Q_all_memory(prev_result, obs, sedgrid, obsmodel, qnames_in, p=[16.0, 50.0, 
             print("restoring the already computed 1D PDFs from " + pdf1d_outname)
             ph = fitsio.read_fits(pdf1d_outname)
             for k in range(nq):
-                out.save_pdf1d_vals[k] = np.array(ph[k + 1][1])
+                out.save_pdf1d_vals[k][...] = np.array(ph[k + 1][1])
         if pdf2d_outname is not None:
             print("restoring the already computed 2D PDFs from " + pdf2d_outname)
             ph = fitsio.read_fits(pdf2d_outname)
             for k in range(len(out.pdf2d_qname_pairs)):
-                out.save_pdf2d_vals[k] = np.array(ph[k + 1][1])
+                out.save_pdf2d_vals[k][...] = np.array(ph[k + 1][1])
     elif lnp_outname is not None:
         _lnp_create(lnp_outname, g0.lamb, obs.getFilters())
 
-    def write_files():
+    g0i = setup.g0_indxs
+    fluxes = _collect_fluxes(obs, start_pos)
+    lnp_written = [start_pos]
+
+    def finish_rows(lo, hi):
+        """host-side columns of stars [lo, hi): full-grid indices, Best values"""
+        pj, cj = res.Pmax_j[lo:hi], res.chi2min_j[lo:hi]
+        best_full = np.where(pj >= 0, g0i[np.maximum(pj, 0)], 0)
+        out.lnp_indx[lo:hi] = best_full
+        out.chi2_indx[lo:hi] = np.where(cj >= 0, g0i[np.maximum(cj, 0)], 0)
+        out.best_specgrid_indx[lo:hi] = setup.specgrid_indx[best_full]
+        for k in range(nq):
+            out.best_vals[lo:hi, k] = setup.qcols[k][best_full]
+
+    def lnp_records(lo, hi):
+        """save_lnp_vals entries of stars [lo, hi) (fit.py:701-709), views of the flat arrays"""
+        off = res.sparse_off
+        full_idx = g0i[res.sparse_j[off[lo]:off[hi]]]
+        base = off[lo]
+        return [[e, full_idx[off[e] - base:off[e + 1] - base],
+                 res.sparse_lnp[off[e]:off[e + 1]], res.sparse_chi2[off[e]:off[e + 1]],
+                 fluxes[e - start_pos].reshape(-1, 1)] for e in range(lo, hi)]
+
+    def write_files(upto):
         if pdf1d_outname is not None:
             save_pdf1d(pdf1d_outname, out.save_pdf1d_vals, qnames)
         if pdf2d_outname is not None:
@@ -394,53 +441,41 @@ def Q_all_memory(prev_result, obs, sedgrid, obsmodel, qnames_in, p=[16.0, 50.0, 
                                     out.per_vals, out.chi2_vals, out.chi2_indx, out.lnp_vals,
                                     out.lnp_indx, out.best_specgrid_indx, out.total_log_norm,
                                     qnames, p, g0.filters, g0.lamb)
-        if lnp_outname is not None and out.save_lnp_vals:
-            save_lnp(lnp_outname, out.save_lnp_vals)
-            out.save_lnp_vals = []
+        if lnp_outname is not None and sparse is not None and upto > lnp_written[0]:
+            save_lnp(lnp_outname, lnp_records(lnp_written[0], upto))
+            lnp_written[0] = upto
 
-    fluxes = _collect_fluxes(obs, start_pos)
     bs = engine.max_batch
     if save_every_npts is not None:
-        bs = max(int(save_every_npts), (min(bs, 16384) // int(save_every_npts)) * int(save_every_npts))
-        bs = min(bs, engine.max_batch)
-    sparse = None
-    if lnp_outname is not None:
-        sparse = "all" if lnp_npts is None else int(lnp_npts)
-    g0i = setup.g0_indxs
-    for a in range(0, len(fluxes), bs):
-        b = min(len(fluxes), a + bs)
-        res = engine.fit(fluxes[a:b], threshold=float(threshold), percentiles=tuple(p),
-                         want_pdf2d=make_pdf2d, sparse=sparse, lnp_rng=lnp_rng, seed=a + start_pos)
-        lo, hi = start_pos + a, start_pos + b
-        best_full = np.where(res.Pmax_j >= 0, g0i[np.maximum(res.Pmax_j, 0)], 0)
-        out.lnp_vals[lo:hi] = res.Pmax
-        out.lnp_indx[lo:hi] = best_full
-        out.chi2_vals[lo:hi] = res.chi2min
-        out.chi2_indx[lo:hi] = np.where(res.chi2min_j >= 0, g0i[np.maximum(res.chi2min_j, 0)], 0)
-        out.total_log_norm[lo:hi] = res.total_log_norm
-        out.best_specgrid_indx[lo:hi] = setup.specgrid_indx[best_full]
-        out.exp_vals[lo:hi] = res.exp_vals
-        out.per_vals[lo:hi] = res.per_vals
-        for k in range(nq):
-            out.best_vals[lo:hi, k] = setup.qcols[k][best_full]
-            out.save_pdf1d_vals[k][lo:hi, :] = res.pdf1d[:, setup.bin_off[k]:setup.bin_off[k + 1]]
-        if make_pdf2d:
-            for k, pr in enumerate(setup.pairs):
-                blk = res.pdf2d[:, setup.pair_off[k]:setup.pair_off[k + 1]]
-                out.save_pdf2d_vals[k][lo:hi] = blk.reshape(-1, pr.nb1, pr.nb2)
-        if sparse is not None:
-            for i in range(b - a):
-                r0, r1 = res.sparse_off[i], res.sparse_off[i + 1]
-                out.save_lnp_vals.append([
-                    lo + i,
-                    np.array(g0i[res.sparse_j[r0:r1]], dtype=np.int64),
-                    np.array(res.sparse_lnp[r0:r1], dtype=np.float32),
-                    np.array(res.sparse_chi2[r0:r1], dtype=np.float32),
-                    np.array([fluxes[a + i]]).T,
-                ])
-        if save_every_npts is not None and b < len(fluxes):
-            write_files()
-    write_files()
+        every = int(save_every_npts)
+        bs = min(engine.max_batch, max(every, engine.max_batch // every * every))
+
+    def checkpoint(lo, hi):
+        finish_rows(lo, hi)
+        # (with the whole sparse set per star -- lnp_npts=None -- the records are assembled at
+        # the end of the run only: those checkpoints leave the lnp file for the final write)
+        if save_every_npts is not None and hi < nobs:
+            write_files(hi if cap else lnp_written[0])
+
+    if len(fluxes):
+        engine.fit(fluxes, threshold=float(threshold), percentiles=tuple(trios[0]),
+                   want_pdf2d=make_pdf2d, sparse=sparse, lnp_rng=lnp_rng, seed=start_pos, batch=bs,
+                   result=res, row_offset=start_pos, on_batch=checkpoint)
+    if len(pvals) != 3:  # any list of percentiles (fit.py:749-753): three per pass on the device
+        from .subgrid import CudaMergeMath
+
+        math = CudaMergeMath(setup, trios[0])
+        import torch
+
+        d_pdf = torch.from_numpy(np.ascontiguousarray(res.pdf1d[:nobs])).to(engine.device)
+        for i, trio in enumerate(trios):
+            math.set_percentiles(trio)
+            blk = math.finalize(d_pdf.clone()).cpu().numpy()
+            for j in range(len(pvals[3 * i:3 * i + 3])):
+                out.per_vals[:, :, 3 * i + j] = blk[:, :, j]
+    if sparse is not None and (keep_lnp or lnp_outname is not None) and res.sparse_off is not None:
+        out.save_lnp_vals = lnp_records(start_pos, nobs) if keep_lnp else []
+    write_files(nobs)
     return out
 
 

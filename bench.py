@@ -16,11 +16,13 @@ against a replicated grid (stars shard, no data-path collective): weak scaling.
 disjoint star slices -- the reference's own parallel model (tools/run/helper_functions.py:55-58).
 """
 import argparse
+import contextlib
 import json
 import os
 import sys
 import threading
 import time
+import warnings
 
 import numpy as np
 
@@ -32,6 +34,7 @@ CONFIGS = {
     # name: (axes name, stars per GPU, description)
     "C1": ("C1", 1000, "synthetic PHAT 6-band SEDGrid 1e5 models, 1,000 stars"),
     "C2": ("C2", 100000, "PHAT 6-band 4e6-model grid, 1e5 stars, stats+pdf1d+sparse lnP"),
+    "C3": ("C2", 1000000, "PHAT 6-band 4e6-model grid, 1e6 stars sharded over the GPUs (grid replicated)"),
     "C4": ("C4", 200000, "8-band UV-NIR grid 1e7 models, 2e5 stars"),
 }
 THRESHOLD = -10.0  # summary_table_memory / run_fitting default (fit.py:924, run_fitting.py:303)
@@ -51,6 +54,8 @@ def parse_args():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--pdf2d", action="store_true", help="also build 2D PDFs for Av, M_ini, logT (config C4)")
     ap.add_argument("--cpu-stars-per-core", type=int, default=2)
+    ap.add_argument("--files", action="store_true",
+                    help="also time one plugin call that writes stats/pdf1d/lnp files to tmpfs")
     ap.add_argument("--sparse-pass", default="split", choices=["split", "legacy", "both"],
                     help="kernels of the sparse pass (FitEngine sparse_pass); measurements")
     return ap.parse_args()
@@ -165,7 +170,7 @@ def cpu_reference_run(g, nz, obs, max_nbins, stars_per_core, steps, warmup):
                 rates.append((cores * stars_per_core * nm / dt, dt))
     sample = "%d stars (%d per core x %d cores) of the same catalog against the full %d-model grid per step" % (
         cores * stars_per_core, stars_per_core, cores, nm)
-    return rates, cores, sample
+    return rates, cores, sample, "port"
 
 
 # ---------------------------------------------------------------------------------------
@@ -174,8 +179,8 @@ def run_reference(args, rank, world):
         return
     stars = max(64, len(os.sched_getaffinity(0)) * args.cpu_stars_per_core * (args.steps + args.warmup))
     g, nz, obs = build_inputs(args.config, stars, seed=4321)
-    rates, cores, sample = cpu_reference_run(g, nz, obs, args.max_nbins, args.cpu_stars_per_core,
-                                             args.steps, args.warmup)
+    rates, cores, sample, kind = cpu_reference_run(g, nz, obs, args.max_nbins, args.cpu_stars_per_core,
+                                                   args.steps, args.warmup)
     nm = int(np.count_nonzero(g["weight"] > 0))
     val = float(np.mean([r for r, _ in rates]))
     ms = float(np.mean([dt for _, dt in rates]) * 1e3)
@@ -185,7 +190,7 @@ def run_reference(args, rank, world):
         "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "f64", "data": "synthetic",
         "config": workload_config(args, nm, stars),
-        "cpu_baseline": {"value": val, "unit": "star*model/s", "cores": cores, "kind": "port",
+        "cpu_baseline": {"value": val, "unit": "star*model/s", "cores": cores, "kind": kind,
                          "sample": sample},
         "e2e": {"value": val, "unit": "star*model/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
@@ -205,6 +210,7 @@ def workload_config(args, nm, stars):
 def run_ours(args, rank, world, local_rank):
     import torch
 
+    from beast_b200 import fit as bfit
     from beast_b200.engine import FitEngine
     from beast_b200.gridprep import FitSetup
 
@@ -217,7 +223,11 @@ def run_ours(args, rank, world, local_rank):
         dist = dist_mod
         dist.init_process_group("nccl", device_id=dev)
 
-    stars = args.stars or CONFIGS[args.config][1]
+    # C3 is C2's grid with 1e6 stars split over the ranks (strong scaling); the others give
+    # every rank its own catalog (weak scaling)
+    strong = args.config == "C3"
+    total_stars = args.stars or CONFIGS[args.config][1]
+    stars = -(-total_stars // world) if strong else total_stars
     g, nz, obs = build_inputs(args.config, stars, seed=4321 + rank)
     keys = [k for k in g.keys() if k not in
             "osl keep weight grid_weight prior_weight fullgrid_idx stage specgrid_indx phase eep".split()]
@@ -233,7 +243,6 @@ def run_ours(args, rank, world, local_rank):
         bs = int(max(1, min(bs, (16 << 30) // (int(setup.pair_off[-1]) * 8))))
     batches = [(a, min(stars, a + bs)) for a in range(0, stars, bs)]
     d_flux = [torch.from_numpy(fluxes[a:b]).to(dev) for a, b in batches]
-    pinned = torch.from_numpy(fluxes).pin_memory()
 
     def barrier():
         if dist is not None:
@@ -245,11 +254,7 @@ def run_ours(args, rank, world, local_rank):
             eng.fit_batch(df, THRESHOLD, sparse=LNP_NPTS, lnp_rng="device", seed=1, star_base=a,
                           want_pdf2d=args.pdf2d)
 
-    def step_e2e():
-        return eng.fit(pinned.numpy(), THRESHOLD, sparse=LNP_NPTS, lnp_rng="device", seed=1,
-                       reuse_buffers=True, want_pdf2d=args.pdf2d)
-
-    # ---- device-resident throughput ------------------------------------------------
+    # ---- device-resident throughput: one bf_fit_batch call per batch of stars ------------
     sampler = ClockSampler(local_rank)  # started before the warm-up: the first NVML queries stall
     sampler.recording = False           # CUDA API calls for a while on some drivers
     sampler.start()
@@ -257,8 +262,6 @@ def run_ours(args, rank, world, local_rank):
         step_resident()
     barrier()
     eng.launches = 0
-    eng.profile = True
-    eng.stage_ms()
     sampler.recording = True
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     barrier()
@@ -270,62 +273,142 @@ def run_ours(args, rank, world, local_rank):
     sampler.stop_flag = True
     ms_total = ev0.elapsed_time(ev1)
     launches = eng.launches
-    stage_tot, stage_cnt = eng.stage_ms()
-    eng.profile = False
     t = torch.tensor([ms_total], dtype=torch.float64, device=dev)
     if dist is not None:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
     ms_step = float(t.item()) / args.steps
     value = world * stars * nm / (ms_step * 1e-3)
 
-    # ---- end to end through the engine API (host in, host out) -----------------------
+    # ---- one more step with bf_fit_batch timing its stages (CUDA events on the launching stream,
+    # a synchronisation after every stage: outside the timed region) -------------------------
+    eng.profile = True
+    eng.stage_ms()
+    step_resident()
+    torch.cuda.synchronize(dev)
+    stage_tot, stage_cnt = eng.stage_ms()
+    eng.profile = False
+    n_list = 0
+    for (a, b), df in zip(batches, d_flux):  # listed groups of the catalog (for the rooflines)
+        eng.fit_batch(df, THRESHOLD)
+        n_list += int(eng.last_state[1].n_list)
+
+    # ---- end to end through the reference-facing call: Q_all_memory with host objects in and
+    # the reference's result arrays back on the host, every step ------------------------------
+    e2e_stars = stars
+    if args.pdf2d:  # 2D PDFs of a whole catalog do not fit host memory (1 MB per star)
+        e2e_stars = min(stars, 16384)
+    e2e_obs = obs if e2e_stars == stars else obs.subset(slice(0, e2e_stars))
+    eng.reuse_buffers = True  # page-locked result arrays are kept across calls (not re-pinned)
+    qkw = dict(p=[16.0, 50.0, 84.0], max_nbins=args.max_nbins, lnp_npts=LNP_NPTS, threshold=THRESHOLD,
+               engine=eng, keep_lnp=True, pdf2d_param_list=p2d)
+
+    def step_e2e(files=None):
+        kw = dict(qkw)
+        if files:
+            kw.update(stats_outname=files + "_stats.fits", pdf1d_outname=files + "_pdf1d.fits",
+                      lnp_outname=files + "_lnp.hd5", keep_lnp=False)
+        if args.pdf2d:
+            kw["pdf2d_outname"] = (files + "_pdf2d.fits") if files else os.devnull
+        with open(os.devnull, "w") as devnull, contextlib.redirect_stdout(devnull):
+            return bfit.Q_all_memory({}, e2e_obs, g, nz, list(keys), **kw)
+
     step_e2e()
     barrier()
     t0 = time.perf_counter()
     for _ in range(args.steps):
-        res = step_e2e()
+        out = step_e2e()
     barrier()
     e2e_s = (time.perf_counter() - t0) / args.steps
     t = torch.tensor([e2e_s], dtype=torch.float64, device=dev)
     if dist is not None:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
     e2e_s = float(t.item())
-    h2d = fluxes.nbytes
-    d2h = sum(getattr(res, n).nbytes for n in ("Pmax", "Pmax_j", "total_log_norm", "chi2min", "chi2min_j",
-                                                "exp_vals", "per_vals", "pdf1d", "sparse_j",
-                                                "sparse_lnp", "sparse_chi2")) + 4 * stars
+    h2d = e2e_obs.fluxes.nbytes
+    res = eng._result_cache[next(iter(eng._result_cache))]
+    d2h = sum(getattr(res, n)[:e2e_stars].nbytes for n in ("Pmax", "Pmax_j", "total_log_norm", "chi2min",
+                                                          "chi2min_j", "n_sparse", "n_groups_selected",
+                                                          "exp_vals", "per_vals", "pdf1d"))
+    d2h += sum(getattr(res, n).nbytes for n in ("sparse_j", "sparse_lnp", "sparse_chi2")) + 8 * e2e_stars
+    if args.pdf2d:
+        d2h += res.pdf2d[:e2e_stars].nbytes
+    mean_sparse = float(np.mean(res.n_sparse[:e2e_stars]))
+    mean_groups = float(np.mean(res.n_groups_selected[:e2e_stars]))
+    members = float(np.sum(res.n_sparse[:e2e_stars].astype(np.float64))) * (stars / e2e_stars)
+    files_s = None
+    if rank == 0 and args.files and not args.pdf2d:
+        import tempfile
+
+        with warnings.catch_warnings():
+            warnings.simplefilter("ignore")
+            with tempfile.TemporaryDirectory(dir="/dev/shm" if os.path.isdir("/dev/shm") else None) as td:
+                t0 = time.perf_counter()
+                step_e2e(os.path.join(td, "bench"))
+                files_s = time.perf_counter() - t0
     if rank != 0:
+        if dist is not None:
+            dist.destroy_process_group()
         return
 
-    # ---- roofline of the dominant kernel (dense FP32 sweep) ---------------------------
+    # ---- rooflines ------------------------------------------------------------------------------
     peaks, peak_src = measured_peaks()
     nb = setup.nb
-    flop_per_eval = 4 * nb + 2  # 2*nb+1 FMA per star x model (SURVEY.md section 8d)
-    dense_ms = stage_tot.get("dense", 0.0) / max(stage_cnt.get("dense", 1), 1)
-    evals_per_launch = stars * setup.ld_model / len(batches)
-    achieved = flop_per_eval * evals_per_launch / (dense_ms * 1e-3) / 1e12 if dense_ms else None
-    # DRAM traffic of one dense launch: every block of 1024 stars streams the tiles once, plus the
-    # group-minimum map (validated against ncu dram__bytes: profiles/r01_dense_chi2_ncu.md)
-    stars_per_launch = stars / len(batches)
-    ld = -(-int(stars_per_launch) // 1024) * 1024
-    traffic = (ld // 1024) * setup.tiles.nbytes + setup.n_groups * ld * 4
+    hbm = float(peaks.get("hbm_gbs", 6650.0))
     sm_max = float(peaks.get("sm_max_mhz", 1965.0))
     peak_tf = eng.sm_count * 128 * 2 * sm_max * 1e6 / 1e12
-    roofline = {
-        "bound": "fp32", "kernel": "dense_chi2_kernel", "achieved": achieved, "peak": peak_tf,
-        "unit": "TFLOP/s", "frac": (achieved / peak_tf) if achieved else None, "traffic": int(traffic),
-        "traffic_note": "bytes per launch = star blocks x tile bytes + group-minimum map; equals ncu "
-                        "dram__bytes_read+write of the same kernel (profiles/r01_dense_chi2_ncu.md)",
-        "peak_source": "%d SMs x 128 FP32 lanes x 2 x sm_max_mhz (%s); MEASURED_PEAKS.json has no "
-                       "FP32 entry" % (eng.sm_count, peak_src),
-        "dense_ms_per_launch": dense_ms, "flop_per_star_model": flop_per_eval,
-        "hbm_gbs_peak": peaks.get("hbm_gbs"),
-        "stage_ms_per_step": {k: v / args.steps for k, v in stage_tot.items()},
-        # where the step goes: the sparse pass (exact weights, histograms, expectations) is the
-        # longest stage; its kernels are bound by HBM latency and the L1/shared data pipe
-        # (profiles/r01_exact_weights_ncu.md, profiles/r01_hist_window_ncu.md)
-        "stage_share_of_step": {k: (v / args.steps) / ms_step for k, v in stage_tot.items()},
-    }
+    flop_per_eval = 4 * nb + 2  # 2*nb+1 FMA per star x model (SURVEY.md section 8d)
+    nbat = len(batches)
+
+    def per_launch(name):
+        return stage_tot.get(name, 0.0) / max(nbat, 1)
+
+    dense_ms = per_launch("dense")
+    evals_per_launch = stars * setup.ld_model / nbat
+    dense_tf = flop_per_eval * evals_per_launch / (dense_ms * 1e-3) / 1e12 if dense_ms else None
+    ld = -(-int(stars / nbat) // 1024) * 1024
+    dense_traffic = (ld // 1024) * setup.tiles.nbytes + setup.n_groups * ld * 4
+    peak_note = "%d SMs x 128 FP32 lanes x 2 x sm_max_mhz (%s); MEASURED_PEAKS.json has no FP32 entry" % (
+        eng.sm_count, peak_src)
+    r_dense = {"bound": "fp32", "kernel": "dense_chi2_kernel", "achieved": dense_tf, "peak": peak_tf,
+               "unit": "TFLOP/s", "frac": (dense_tf / peak_tf) if dense_tf else None,
+               "traffic": int(dense_traffic), "ms_per_step": stage_tot.get("dense", 0.0),
+               "work": "%d flop per star x model (2 nb + 1 FMA)" % flop_per_eval, "peak_source": peak_note,
+               "traffic_note": "bytes per launch = star blocks x tile bytes + group-minimum map; equals ncu "
+                               "dram__bytes of the kernel (profiles/r01_dense_chi2_ncu.md)"}
+    # exact weights: every listed model's FP64 rows (2 nb + 2 doubles) are needed once, every
+    # member's weight is produced once (SURVEY.md 8d / VERDICT r01: 112 B x evaluated + 8 B x members)
+    w_ms = stage_tot.get("exact_weights", 0.0)
+    w_bytes = (2 * nb + 2) * 8.0 * 64 * n_list + 8.0 * members
+    r_weights = {"bound": "hbm", "kernel": "exact_weights_grouped_kernel" if eng.split else "exact_weights_kernel",
+                 "achieved": w_bytes / (w_ms * 1e-3) / 1e9 if w_ms else None, "peak": hbm, "unit": "GB/s",
+                 "frac": (w_bytes / (w_ms * 1e-3) / 1e9 / hbm) if w_ms else None, "traffic": None,
+                 "ms_per_step": w_ms,
+                 "work": "%d B of model rows per listed model + 8 B per member weight; the kernel writes 64 weights "
+                         "(+ run sums, expectation partials) per listed group, 0.7 KB, which is what its DRAM "
+                         "traffic consists of (profiles/r02_exact_weights_grouped_ncu.md)" % ((2 * nb + 2) * 8)}
+    # histograms: every member's weight is read once and added to one bin of each parameter
+    h_ms = stage_tot.get("histograms", 0.0)
+    h_bytes = 8.0 * members + stars * setup.total_bins * 8.0
+    upd = members * setup.n_q
+    r_hist = {"bound": "hbm", "kernel": "split_hist_kernel" if eng.split else "hist_window_kernel / hist_kernel",
+              "achieved": h_bytes / (h_ms * 1e-3) / 1e9 if h_ms else None, "peak": hbm, "unit": "GB/s",
+              "frac": (h_bytes / (h_ms * 1e-3) / 1e9 / hbm) if h_ms else None, "traffic": None,
+              "ms_per_step": h_ms,
+              "work": "8 B per member weight in + one pdf row per star out; the kernel is bound by "
+                      "shared-memory updates, not by HBM: %.3g histogram updates per step = %.3g per second"
+                      % (upd, upd / (h_ms * 1e-3) if h_ms else 0.0),
+              "updates_per_s": upd / (h_ms * 1e-3) if h_ms else None}
+    kernels = [r_dense, r_weights, r_hist]
+    dominant = max(kernels, key=lambda r: r["ms_per_step"] or 0.0)
+    roofline = dict(dominant)
+    roofline["kernels"] = kernels
+    roofline["hbm_gbs_peak"] = hbm
+    stage_sum = sum(stage_tot.values()) or 1.0
+    roofline["stage_ms_per_step"] = dict(stage_tot)
+    roofline["stage_share_of_step"] = {k: v / stage_sum for k, v in stage_tot.items()}
+    roofline["stage_note"] = ("stage times from one extra step in which bf_fit_batch synchronises after every "
+                              "stage; their sum is %.1f ms against %.1f ms for the timed step" % (stage_sum, ms_step))
+    # the metric BASELINE.json states: fraction of the FP32 pipe peak for the whole fit
+    roofline["frac_of_fp32_peak"] = flop_per_eval * stars * nm / (ms_step * 1e-3) / 1e12 / peak_tf
 
     # ---- the step before the fit: trim_models flags pass, HBM-bound (fitting/trim_grid.py) -----
     trim_info = None
@@ -353,35 +436,44 @@ def run_ours(args, rank, world, local_rank):
         nbytes = 4 * t_seds.numel() * 8 + 4 * len(g)
         best = min(ms[1:])
         trim_info = {"kernel": "trim_flags_kernel", "models": len(g), "ms": best,
-                     "achieved_gbs": nbytes / best / 1e6, "peak_gbs": peaks.get("hbm_gbs"),
-                     "frac": nbytes / best / 1e6 / float(peaks.get("hbm_gbs", 6650.0)), "bound": "hbm"}
+                     "achieved_gbs": nbytes / best / 1e6, "peak_gbs": hbm,
+                     "frac": nbytes / best / 1e6 / hbm, "bound": "hbm"}
         del t_seds, t_bias, t_unc, t_cmp
     except Exception as exc:  # the fit numbers above stand on their own
         trim_info = {"error": repr(exc)}
 
     cpu = None
     if world == 1 and not args.no_cpu_baseline:
-        rates, cores, sample = cpu_reference_run(g, nz, obs, args.max_nbins, args.cpu_stars_per_core, 1, 1)
-        cpu = {"value": rates[0][0], "unit": "star*model/s", "cores": cores, "kind": "port",
+        rates, cores, sample, kind = cpu_reference_run(g, nz, obs, args.max_nbins, args.cpu_stars_per_core, 1, 1)
+        cpu = {"value": rates[0][0], "unit": "star*model/s", "cores": cores, "kind": kind,
                "sample": sample, "seconds": rates[0][1]}
 
+    cfg = workload_config(args, nm, stars)
+    if strong:
+        cfg["parallelism"] = "1e6 stars split over the GPUs, grid replicated"
+        cfg["total_stars"] = stars * world
     line = {
         "metric": "star-model lnP evaluations per second", "value": value, "unit": "star*model/s",
         "stars_per_s": value / nm, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
-        "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-        "dtype": "f32 dense sweep + f64 exact pass", "data": "synthetic",
-        "config": workload_config(args, nm, stars),
+        "ms_per_step": ms_step, "higher_is_better": True, "scaling": "strong" if strong else "weak",
+        "vs_baseline": None, "dtype": "f32 dense sweep + f64 exact pass", "data": "synthetic",
+        "config": cfg,
         "clocks": sampler.summary(),
-        "e2e": {"value": world * stars * nm / e2e_s, "unit": "star*model/s",
-                "stars_per_s": world * stars / e2e_s, "seconds_per_step": e2e_s,
-                "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h)},
+        "e2e": {"value": world * e2e_stars * nm / e2e_s, "unit": "star*model/s",
+                "stars_per_s": world * e2e_stars / e2e_s, "seconds_per_step": e2e_s,
+                "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h), "stars": e2e_stars,
+                "call": "beast_b200.fit.Q_all_memory(prev_result, obs, sedgrid, obsmodel, keys, p=[16,50,84], "
+                        "max_nbins=%d, lnp_npts=%d, threshold=%g, engine=<resident grid>, keep_lnp=True): host "
+                        "objects in, the reference's result arrays (stats, pdf1d, sparse lnP) back on the host, "
+                        "no files" % (args.max_nbins, LNP_NPTS, THRESHOLD),
+                "with_files_on_tmpfs_seconds": files_s},
         "gpu_launches": int(launches),
         "roofline": roofline,
         "cpu_baseline": cpu,
         "trim": trim_info,
         "setup_seconds": setup_s,
-        "mean_sparse_set": float(np.mean(res.n_sparse)),
-        "mean_groups_selected": float(np.mean(res.n_groups_selected)),
+        "mean_sparse_set": mean_sparse,
+        "mean_groups_selected": mean_groups,
     }
     _OUT.write(json.dumps(line) + "\n")
     _OUT.flush()

@@ -331,6 +331,106 @@ int bf_pdf2d_from_weights(int64_t ld_model, int n_pairs, const int32_t* pair_bin
                           int64_t n_entries, double* pdf2d, void* stream);
 
 /* ---------------------------------------------------------------------------
+ * The whole fit of one batch of stars behind one call: the star loop of Q_all_memory
+ * (fitting/fit.py:637-762) -- likelihood of every model, prior, sparse selection, normalisation,
+ * best fit, chi2 minimum, expectations, 1D PDFs, percentiles, optional 2D PDFs and sparse lnP
+ * records -- for n_stars stars against the grid described by `plan`.  It runs the entry points
+ * above in sequence (plus the ordering, layout and copy kernels between them) inside a
+ * caller-provided workspace; nothing is allocated.  The host synchronises the stream once (the
+ * list sizes decide the memory layout), twice with sparse_mode 1.
+ *
+ * plan    : the resident grid (device pointers; the struct itself is host memory)
+ *   tiles / tiles_coarse : see bf_dense_chi2; tiles_coarse (every 32nd model, may be NULL) is
+ *                   swept first to order the stars by where their best models lie -- results
+ *                   come back in the caller's order either way
+ *   inv_band_scale [nb] : 1 / s_b (device), turns flux64 into the FP32 fluxes of the dense pass
+ *   pair_bin / pair_off / pair_len : 2D PDF tables (bf_pdf2d_accumulate), pair_len = pair_off[n_pairs]
+ *   force_legacy  : 1 = do not use the class-split kernels even if `params` carries the split
+ * flux64  : [n_stars][nb] observed fluxes, device memory, or host memory with flux_on_host = 1
+ * percentiles_host : [3] host doubles, in percent
+ * sparse_mode : 0 no sparse records; 1 all members of every star's sparse set (ascending model
+ *               index); 2 min(|S|, lnp_npts) members drawn by the keyed permutation of
+ *               bf_sparse_sample_ranks with (seed, star_base + star index) -- fit.py:693-709
+ * out     : device pointers, one row per star in the caller's order; pdf2d, n_groups_selected and
+ *           the sparse_* members may be NULL when not wanted.  sparse_off [n_stars + 1] gives the
+ *           record range of every star inside sparse_j / sparse_lnp / sparse_chi2
+ *           (sparse_capacity records of room; mode 2 needs n_stars * lnp_npts)
+ * state   : optional out; what a follow-up call needs (bf_fit_sparse_records), valid until the
+ *           workspace is written again
+ * Returns BF_ERR_TOO_LARGE when the workspace (or sparse_capacity) is too small;
+ * bf_fit_workspace_bytes gives a size from the expected total of listed groups.
+ * ------------------------------------------------------------------------- */
+typedef struct {
+  int nb;
+  int full_cov;
+  int64_t n_groups;
+  int64_t n_tiles;
+  const float* tiles;
+  int64_t n_tiles_coarse;
+  const float* tiles_coarse;
+  const double* inv_band_scale;
+  float err_a, err_b;
+  bf_exact_grid grid;
+  bf_param_tables params;
+  int n_pairs;
+  const int32_t* pair_bin;
+  const int64_t* pair_off;
+  int64_t pair_len;
+  int sm_count;
+  int force_legacy;
+} bf_fit_plan;
+
+typedef struct {
+  double* pmax;             /* fit.py:727 */
+  int64_t* pmax_j;          /* fit.py:719 (filtered model index) */
+  double* total_log_norm;
+  double* chi2min;
+  int64_t* chi2min_j;
+  uint32_t* n_sparse;
+  int64_t* n_groups_selected;
+  double* exp_vals;         /* [n_stars][n_q] */
+  double* pdf1d;            /* [n_stars][total_bins] */
+  double* per_vals;         /* [n_stars][n_q][3] */
+  double* pdf2d;            /* [n_stars][pair_len] or NULL */
+  int64_t* sparse_off;
+  int64_t* sparse_j;
+  float* sparse_lnp;
+  float* sparse_chi2;
+  int64_t sparse_capacity;
+} bf_fit_outputs;
+
+typedef struct {
+  const double* flux64;           /* fluxes in the order the batch was fitted in */
+  const uint32_t* offsets;
+  const uint32_t* list;
+  const uint32_t* member_mask;
+  const uint32_t* member_prefix;
+  const int32_t* perm;            /* fit order -> caller's order, NULL = the same */
+  const uint32_t* n_sparse_sorted;
+  int64_t n_list;                 /* listed groups of the batch */
+  int64_t n_records;              /* sparse records wanted when sparse_capacity was too small */
+  int64_t launches;               /* kernels launched by the call */
+  int split;                      /* 1: the class-split kernels ran */
+  int want_timing;                /* in: 1 = fill stage_ms (the call then synchronises the stream
+                                     after every stage; for measurements) */
+  float stage_ms[12];             /* device time per stage: presort, dense, select, exact_max,
+                                     group_order, exact_weights, histograms, expectations, pdf2d,
+                                     reorder, sparse_records */
+} bf_fit_state;
+
+int64_t bf_fit_workspace_bytes(const bf_fit_plan* plan, int64_t n_stars, int64_t list_entries_hint);
+int bf_fit_batch(const bf_fit_plan* plan, int64_t n_stars, const double* flux64, int flux_on_host,
+                 double threshold, const double* percentiles_host, int sparse_mode, int64_t lnp_npts,
+                 uint64_t seed, int64_t star_base, void* workspace, size_t workspace_bytes,
+                 const bf_fit_outputs* out, bf_fit_state* state, void* stream, void* aux_stream);
+/* Sparse records for ranks drawn by the caller (np.random.choice on the host, fit.py:696) after a
+ * bf_fit_batch with sparse_mode 0: rec_off [n_stars + 1] and ranks in the caller's star order;
+ * ranks == NULL takes positions 0 .. rec_off[s+1]-rec_off[s]-1 of every star's sparse set. */
+int bf_fit_sparse_records(const bf_fit_plan* plan, const bf_fit_state* state, int64_t n_stars,
+                          const int64_t* rec_off, const uint32_t* ranks, int64_t* out_j,
+                          float* out_lnp, float* out_chi2, void* stream);
+
+/* ---------------------------------------------------------------------------
  * Subgrid merge (tools/subgridding_tools.py:392-527), device part.  Each rank holds the
  * results of its own subgrid for the same stars; after the caller all-gathers
  * total_log_norm / Pmax into [n_sub][n_stars] arrays these kernels produce the merged rows.

@@ -160,15 +160,45 @@ def test_weights_kernel_instantiations_are_bit_identical(monkeypatch):
 
 
 def test_pdf2d_entry_points_agree():
-    """bf_pdf2d_from_weights (weights left by the sparse pass) and bf_pdf2d_accumulate (models
-    evaluated again) build the same 2D PDFs; both match the reference's (golden case)"""
+    """bf_pdf2d_from_weights (weights left by the sparse pass, used inside bf_fit_batch) and the
+    stand-alone bf_pdf2d_accumulate (models evaluated again) build the same 2D PDFs; both match
+    the reference's (golden case)"""
+    import ctypes as C
+
+    import torch
+
+    from beast_b200 import _cabi
+
     g, nz, obs, args, ref = util.load_golden("tiny_thr10_pdf2d")
     setup, eng = _engine(g, nz, args)
+    eng.presort = False  # the lists bf_fit_batch leaves behind are then in catalog order
     a = eng.fit(obs.fluxes, threshold=args["threshold"], want_pdf2d=True, sparse="all")
-    eng.pdf2d_reevaluate = True
-    b = eng.fit(obs.fluxes, threshold=args["threshold"], want_pdf2d=True, sparse="all")
-    util.compare_to_reference(setup, b, ref, n_pdf2d=len(setup.pairs))
-    np.testing.assert_allclose(a.pdf2d, b.pdf2d, rtol=1e-12, atol=1e-300)
+    util.compare_to_reference(setup, a, ref, n_pdf2d=len(setup.pairs))
+    plan, state = eng.last_state
+    n = len(obs)
+    dev = eng.device
+    pmax = torch.from_numpy(a.Pmax.copy()).to(dev)
+    tln = torch.from_numpy(a.total_log_norm.copy()).to(dev)
+    pdf2d = torch.zeros((n, int(setup.pair_off[-1])), dtype=torch.float64, device=dev)
+    P = lambda x: C.c_void_p(x.data_ptr())  # noqa: E731
+    _cabi.call("bf_pdf2d_accumulate", C.byref(eng.grid), len(setup.pairs), P(eng.d_pair_bin),
+               P(eng.d_pair_off), n, C.c_void_p(state.flux64), P(pmax), P(tln), float(args["threshold"]),
+               C.c_void_p(state.offsets), C.c_void_p(state.list), P(pdf2d),
+               C.c_void_p(torch.cuda.current_stream(dev).cuda_stream))
+    torch.cuda.synchronize(dev)
+    np.testing.assert_allclose(a.pdf2d[:n], pdf2d.cpu().numpy(), rtol=1e-12, atol=1e-300)
+
+
+def test_fit_batch_is_one_c_call_and_presort_is_invisible():
+    """a whole fit through bf_fit_batch: with and without the presort (stars fitted in another
+    order and put back) every output agrees bit for bit, sparse records included"""
+    g, nz, obs, args, ref = util.load_golden("small_thr10")
+    setup, eng = _engine(g, nz, args)
+    a = eng.fit(obs.fluxes, threshold=args["threshold"], sparse=20, lnp_rng="device", seed=5)
+    eng.presort = False
+    b = eng.fit(obs.fluxes, threshold=args["threshold"], sparse=20, lnp_rng="device", seed=5)
+    _same_everything(a, b, ALL_OUT + ("sparse_off", "n_groups_selected"))
+    util.compare_to_reference(setup, a, ref)
 
 
 def _same_everything(a, b, names):
