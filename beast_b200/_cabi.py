@@ -196,6 +196,7 @@ PROTOTYPES = {
     "bf_trim_compact": (C.c_int, [i64, c_void_p, c_void_p, c_void_p, c_void_p]),
     "bf_merge_weights": (C.c_int, [C.c_int, i64, c_void_p, c_void_p, c_void_p, c_void_p]),
     "bf_scale_rows": (C.c_int, [i64, i64, c_void_p, c_void_p, c_void_p]),
+    "bf_axpy_rows": (C.c_int, [i64, i64, c_void_p, c_void_p, c_void_p, C.c_int, c_void_p]),
     "bf_merge_finalize": (C.c_int, [C.POINTER(ParamTables), i64, c_void_p, C.POINTER(C.c_double),
                                     c_void_p, c_void_p]),
 }

@@ -38,6 +38,19 @@ __global__ void scale_rows_kernel(int64_t n_stars, int64_t row_len,
   rows[i] *= weight[i / row_len];
 }
 
+// dst[s][:] = (accumulate ? dst[s][:] : 0) + weight[s] * src[s][:]  -- a subgrid's rows, scaled
+// by its weight, join the sum that then crosses the ranks (:421-426, :462-470)
+__global__ void axpy_rows_kernel(int64_t n_stars, int64_t row_len, const double* __restrict__ weight,
+                                 const double* __restrict__ src, double* __restrict__ dst,
+                                 int accumulate) {
+  const int64_t i = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x;
+  if (i >= n_stars * row_len) return;
+  const double w = weight[i / row_len];
+  // a subgrid whose weight is exactly 0 must not turn the sum into NaN (inf * 0)
+  const double v = w != 0.0 ? w * src[i] : 0.0;
+  dst[i] = accumulate ? dst[i] + v : v;
+}
+
 constexpr int kFinWarps = 4;
 
 // one block per star, one warp per parameter
@@ -102,5 +115,18 @@ extern "C" int bf_merge_finalize(const bf_param_tables* params, int64_t n_stars,
                           static_cast<cudaStream_t>(stream)>>>(
       *params, pdf1d, percentiles_host[0], percentiles_host[1], percentiles_host[2], per_vals);
   BF_CHECK_LAUNCH("merge_finalize_kernel");
+  return BF_OK;
+}
+
+extern "C" int bf_axpy_rows(int64_t n_stars, int64_t row_len, const double* weight, const double* src,
+                            double* dst, int accumulate, void* stream) {
+  using namespace bf;
+  BF_REQUIRE(n_stars > 0 && row_len > 0, "bf_axpy_rows: bad sizes");
+  BF_REQUIRE(weight && src && dst, "bf_axpy_rows: null pointer");
+  const int64_t n = n_stars * row_len;
+  BF_REQUIRE((n + 255) / 256 < (1LL << 31), "bf_axpy_rows: too large");
+  axpy_rows_kernel<<<static_cast<unsigned>((n + 255) / 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(
+      n_stars, row_len, weight, src, dst, accumulate);
+  BF_CHECK_LAUNCH("axpy_rows_kernel");
   return BF_OK;
 }

@@ -38,6 +38,36 @@ __all__ = [
 ]
 
 
+class LnpRecords:
+    """The reference's ``save_lnp_vals`` list (fit.py:701-709) for stars [lo, hi): entry i is
+    ``[e, full-grid indices int64, lnp float32, chi2 float32, sed column (nb, 1)]``.  Built on
+    access from the flat arrays the GPU results were copied into -- a catalog of 1e5 stars
+    would otherwise cost half a second of list building per call."""
+
+    def __init__(self, res, g0_indxs, fluxes, start_pos, lo, hi):
+        self._res, self._g0, self._flux, self._start = res, g0_indxs, fluxes, start_pos
+        self._lo, self._hi = lo, hi
+
+    def __len__(self):
+        return self._hi - self._lo
+
+    def __getitem__(self, i):
+        if isinstance(i, slice):
+            return [self[j] for j in range(*i.indices(len(self)))]
+        if i < 0:
+            i += len(self)
+        if not 0 <= i < len(self):
+            raise IndexError(i)
+        e = self._lo + i
+        r, off = self._res, self._res.sparse_off
+        a, b = off[e], off[e + 1]
+        return [e, self._g0[r.sparse_j[a:b]], r.sparse_lnp[a:b], r.sparse_chi2[a:b],
+                self._flux[e - self._start].reshape(-1, 1)]
+
+    def __iter__(self):
+        return (self[i] for i in range(len(self)))
+
+
 class FitOutputs:
     """arrays exactly as the reference hands them to its writers (fit.py:468-478, 507, 569)"""
 
@@ -373,9 +403,10 @@ def Q_all_memory(prev_result, obs, sedgrid, obsmodel, qnames_in, p=[16.0, 50.0, 
                                for k, pr in enumerate(setup.pairs)]
     for name in ("Pmax", "Pmax_j", "total_log_norm", "chi2min", "chi2min_j", "exp_vals", "per_vals"):
         getattr(res, name)[...] = 0  # rows not fitted yet read as zeros, as in the reference
-    res.pdf1d[:nobs] = 0
-    if pair_len:
-        res.pdf2d[:nobs] = 0
+    if resume or save_every_npts is not None:  # (otherwise every row is written before it is read)
+        res.pdf1d[:nobs] = 0
+        if pair_len:
+            res.pdf2d[:nobs] = 0
 
     start_pos = 0
     if resume:
@@ -424,13 +455,7 @@ def Q_all_memory(prev_result, obs, sedgrid, obsmodel, qnames_in, p=[16.0, 50.0, 
             out.best_vals[lo:hi, k] = setup.qcols[k][best_full]
 
     def lnp_records(lo, hi):
-        """save_lnp_vals entries of stars [lo, hi) (fit.py:701-709), views of the flat arrays"""
-        off = res.sparse_off
-        full_idx = g0i[res.sparse_j[off[lo]:off[hi]]]
-        base = off[lo]
-        return [[e, full_idx[off[e] - base:off[e + 1] - base],
-                 res.sparse_lnp[off[e]:off[e + 1]], res.sparse_chi2[off[e]:off[e + 1]],
-                 fluxes[e - start_pos].reshape(-1, 1)] for e in range(lo, hi)]
+        return LnpRecords(res, g0i, fluxes, start_pos, lo, hi)
 
     def write_files(upto):
         if pdf1d_outname is not None:

@@ -119,6 +119,13 @@ class CudaMergeMath:
                    C.c_void_p(rows.data_ptr()), self._stream(rows))
         return rows
 
+    def axpy_rows(self, w, src, dst, accumulate):
+        """dst = (dst if accumulate else 0) + w[:, None] * src, in place on the device"""
+        ns = src.shape[0]
+        _cabi.call("bf_axpy_rows", ns, src.numel() // ns, C.c_void_p(w.contiguous().data_ptr()),
+                   C.c_void_p(src.contiguous().data_ptr()), C.c_void_p(dst.data_ptr()),
+                   int(bool(accumulate)), self._stream(src))
+
     def finalize(self, pdf):
         """normalise every parameter's pdf row and recompute the percentiles; returns per_vals"""
         torch = self.torch
@@ -198,6 +205,134 @@ def merge_subgrids(local, math, group=None, rank=0, world=1):
         "Pmax_indx": pidx, "best_gridsub_tag": owner, "chi2min": reduce_min("chi2min"),
         "total_log_norm": merged_tln,
     }
+
+
+class SubgridFit:
+    """Subgrid mode without files (docs/subgrid_parallelism.rst:77-143, on device): every process
+    holds one or more row slices of the grid resident on its GPU (``engines``: FitEngine objects
+    built with ``do_not_normalize=True`` and the shared ``grid_info_dict``), all processes fit the
+    same batch of stars, and the per-star partial results are merged while they are still in HBM:
+
+        all_gather   total_log_norm, Pmax, chi2min of every subgrid  -> weights, owner, minima
+        local sum    weight_g * pdf1d_g, weight_g * Exp_g, owner-masked Best / Pmax_indx
+                     over the subgrids of this process (bf_axpy_rows)
+        reduce_scatter(SUM) by star of those sums (NCCL over NVLink): every process ends up with
+                     the merged rows of its share of the batch's stars
+        normalise + percentiles on that share (bf_merge_finalize)
+
+    -- the arithmetic of merge_pdf1d_stats (subgridding_tools.py:392-527) with the reference's
+    files replaced by one collective per batch.  Subgrid g of the run is local subgrid
+    g - rank * len(engines) of process rank."""
+
+    def __init__(self, engines, math, group=None, rank=0, world=1):
+        self.engines, self.math = list(engines), math
+        self.group, self.rank, self.world = group, rank, world
+        self.collective_bytes = 0   # payload this process put into reduce_scatter / all_gather
+        self.collective_ms = 0.0    # device time of the collectives when ``time_collectives``
+        self.time_collectives = False
+        self._cache = {}
+
+    def _tables(self, setup, dev):
+        """device copies of a subgrid's g0_indxs and parameter columns (Best values), made once"""
+        import torch
+
+        key = id(setup)
+        if key not in self._cache:
+            self._cache[key] = (torch.from_numpy(setup.g0_indxs).to(dev),
+                                torch.from_numpy(np.stack([np.asarray(c, dtype=np.float64)
+                                                           for c in setup.qcols])).to(dev))
+        return self._cache[key]
+
+    def share(self, n):
+        """rows [lo, hi) of a batch of n stars that this process ends up with"""
+        per = -(-n // self.world)
+        return min(n, self.rank * per), min(n, (self.rank + 1) * per)
+
+    def fit_batch(self, flux, threshold=-10.0, **kw):
+        outs = [eng.fit_batch(flux, threshold, **kw) for eng in self.engines]
+        return self.merge_batch(outs, [eng.setup for eng in self.engines])
+
+    def merge_batch(self, outs, setups):
+        """outs[l]: the dict of device tensors FitEngine.fit_batch returned for local subgrid l"""
+        import torch
+        import torch.distributed as dist
+
+        L, W = len(outs), self.world
+        n = outs[0]["Pmax"].shape[0]
+        dev = outs[0]["Pmax"].device
+        per = -(-n // W)
+        npad = per * W
+        loc = torch.stack([torch.stack([o["total_log_norm"], o["Pmax"], o["chi2min"]]) for o in outs])  # [L,3,n]
+        if W > 1:
+            allv = torch.empty((W,) + tuple(loc.shape), dtype=loc.dtype, device=dev)
+            self._timed(lambda: dist.all_gather_into_tensor(allv, loc.contiguous(), group=self.group)
+                        if dist.get_backend(self.group) != "gloo" else
+                        dist.all_gather(list(allv.unbind(0)), loc.contiguous(), group=self.group))
+            self.collective_bytes += loc.numel() * 8
+            allv = allv.reshape(W * L, 3, n)
+        else:
+            allv = loc
+        tln_all, pmax_all, chi2_all = allv[:, 0].contiguous(), allv[:, 1].contiguous(), allv[:, 2]
+        w_all, merged_tln = self.math.weights(tln_all)
+        wsum = w_all.sum(0)
+        top = pmax_all.max(0).values
+        G = W * L
+        idx = torch.arange(G, device=dev)[:, None].expand_as(pmax_all)
+        owner = torch.where(pmax_all == top[None, :], idx, torch.full_like(idx, G)).min(0).values
+        nq = outs[0]["exp_vals"].shape[1]
+        tb = outs[0]["pdf1d"].shape[1]
+        acc_pdf = torch.zeros((npad, tb), dtype=torch.float64, device=dev)
+        acc_small = torch.zeros((npad, 2 * nq + 1), dtype=torch.float64, device=dev)
+        ex = torch.zeros((n, nq), dtype=torch.float64, device=dev)
+        for l, (o, st) in enumerate(zip(outs, setups)):
+            g = self.rank * L + l
+            w = w_all[g].contiguous()
+            mine = (owner == g).to(torch.float64)
+            self.math.axpy_rows(w, o["pdf1d"], acc_pdf[:n], l > 0)
+            self.math.axpy_rows(w, o["exp_vals"], ex, l > 0)
+            g0_d, q_d = self._tables(st, dev)
+            best_full = g0_d[o["Pmax_j"].clamp(min=0)]  # row of this subgrid (fit.py:719)
+            best_vals = q_d[:, best_full].t()
+            acc_small[:n, nq:2 * nq] += best_vals * mine[:, None]
+            acc_small[:n, 2 * nq] += best_full.to(torch.float64) * mine
+        acc_small[:n, :nq] = ex
+        if W > 1:
+            pdf = torch.empty((per, tb), dtype=torch.float64, device=dev)
+            small = torch.empty((per, 2 * nq + 1), dtype=torch.float64, device=dev)
+            if dist.get_backend(self.group) == "gloo":  # (CPU tests: gloo has no reduce_scatter)
+                dist.all_reduce(acc_pdf, group=self.group)
+                dist.all_reduce(acc_small, group=self.group)
+                pdf.copy_(acc_pdf[self.rank * per:(self.rank + 1) * per])
+                small.copy_(acc_small[self.rank * per:(self.rank + 1) * per])
+            else:
+                self._timed(lambda: (dist.reduce_scatter_tensor(pdf, acc_pdf, group=self.group),
+                                     dist.reduce_scatter_tensor(small, acc_small, group=self.group)))
+            self.collective_bytes += (acc_pdf.numel() + acc_small.numel()) * 8
+        else:
+            pdf, small = acc_pdf, acc_small
+        lo, hi = self.share(n)
+        m = hi - lo
+        pdf, small = pdf[:m], small[:m]
+        per_vals = self.math.finalize(pdf) if m else torch.zeros((0, nq, 3), dtype=torch.float64, device=dev)
+        return {
+            "rows": (lo, hi), "pdf1d": pdf, "per_vals": per_vals,
+            "exp_vals": small[:, :nq] / wsum[lo:hi, None], "best_vals": small[:, nq:2 * nq],
+            "Pmax_indx": small[:, 2 * nq].to(torch.int64), "Pmax": top[lo:hi],
+            "best_gridsub_tag": owner[lo:hi], "chi2min": chi2_all.min(0).values[lo:hi],
+            "total_log_norm": merged_tln[lo:hi],
+        }
+
+    def _timed(self, fn):
+        if not self.time_collectives:
+            return fn()
+        import torch
+
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        fn()
+        e1.record()
+        e1.synchronize()
+        self.collective_ms += e0.elapsed_time(e1)
 
 
 def local_result_tensors(setup, res, device):

@@ -441,6 +441,10 @@ int bf_merge_weights(int n_sub, int64_t n_stars, const double* tln_all, double* 
 /* in place: rows[s][:] *= weight[s]   (the scaling that feeds the cross-rank sum, :421-426) */
 int bf_scale_rows(int64_t n_stars, int64_t row_len, const double* weight, double* rows,
                   void* stream);
+/* dst[s][:] = (accumulate ? dst[s][:] : 0) + weight[s] * src[s][:]: sums the weighted rows of
+ * the subgrids one process holds before the cross-rank reduce-scatter (:421-426, :462-470) */
+int bf_axpy_rows(int64_t n_stars, int64_t row_len, const double* weight, const double* src,
+                 double* dst, int accumulate, void* stream);
 /* after the cross-rank sum: normalise each parameter's pdf to unit sum where positive
  * (:428-434) and recompute the percentiles from the merged pdf (:472-491). */
 int bf_merge_finalize(const bf_param_tables* params, int64_t n_stars, double* pdf1d,

@@ -124,3 +124,87 @@ def test_single_process_list_merge_uses_same_path():
     want = fo.merge_subgrid_results(outs)
     np.testing.assert_array_equal(merged["best_gridsub_tag"].numpy(), want["best_gridsub_tag"])
     np.testing.assert_allclose(merged["total_log_norm"].numpy(), want["total_log_norm"], rtol=1e-14)
+
+
+# ---- per-batch device merge (SubgridFit): 2 ranks x 2 resident subgrids each -----------------
+class _Setup:
+    """what SubgridFit needs of a FitSetup: identity map to subgrid rows + parameter columns"""
+
+    def __init__(self, ost):
+        self.g0_indxs = np.arange(ost.nmodels, dtype=np.int64)
+        self.qcols = [np.asarray(q, dtype=np.float64) for q in ost.qvals]
+
+
+def _four_parts():
+    from beast_b200 import subgrid, synth
+
+    g = synth.make_sedgrid("tiny", seed=51)
+    nz = synth.make_noisemodel(g)
+    obs = synth.make_observations(g, nz, 7, seed=52)  # (7 stars: the shares of 2 ranks are uneven)
+    keys = fo.default_keys(g)
+    subs = [(g.subgrid(s), {k: v[s] for k, v in nz.items()}) for s in subgrid.uniform_slices(len(g), 4)]
+    info = fo.reduce_grid_info([fo.subgrid_info(sg, sn) for sg, sn in subs])
+    outs, setups = [], []
+    for sg, sn in subs:
+        ost = fo.OracleSetup(sg, sn, keys, max_nbins=30, grid_info_dict=info, do_not_normalize=True)
+        outs.append(fo.fit_all(obs.fluxes, ost, -40.0, fast=True, keep_sparse=False))
+        setups.append(ost)
+    return outs, setups
+
+
+def _as_batch(o):
+    """an oracle subgrid result dressed as the device dict FitEngine.fit_batch returns"""
+    return {"total_log_norm": torch.from_numpy(o["total_log_norm"]), "Pmax": torch.from_numpy(o["Pmax"]),
+            "chi2min": torch.from_numpy(o["chi2min"]),
+            "Pmax_j": torch.from_numpy(o["Pmax_indx"].astype(np.int64)),
+            "exp_vals": torch.from_numpy(o["exp_vals"]),
+            "pdf1d": torch.from_numpy(np.concatenate([p[:-1] for p in o["pdf1d"]], axis=1))}
+
+
+def _fit_worker(rank, world, port, q):
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        from beast_b200 import subgrid
+        from tests.util import NumpyMergeMath as Math
+
+        outs, setups = _four_parts()
+        mine = [2 * rank, 2 * rank + 1]
+        sf = subgrid.SubgridFit([None, None], Math([b.bin_vals for b in setups[0].bins]),
+                                group=dist.group.WORLD, rank=rank, world=world)
+        m = sf.merge_batch([_as_batch(outs[i]) for i in mine], [_Setup(setups[i]) for i in mine])
+        q.put((rank, {k: (v.numpy() if hasattr(v, "numpy") else v) for k, v in m.items()}))
+    finally:
+        dist.destroy_process_group()
+
+
+def test_per_batch_merge_over_two_ranks_with_two_subgrids_each():
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        port = s.getsockname()[1]
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    procs = [ctx.Process(target=_fit_worker, args=(r, 2, port, q)) for r in range(2)]
+    for p in procs:
+        p.start()
+    got = dict(q.get(timeout=180) for _ in range(2))
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    outs, setups = _four_parts()
+    want = fo.merge_subgrid_results(outs)
+    assert got[0]["rows"] == (0, 4) and got[1]["rows"] == (4, 7)
+    for rank in (0, 1):
+        m = got[rank]
+        lo, hi = m["rows"]
+        np.testing.assert_array_equal(m["best_gridsub_tag"], want["best_gridsub_tag"][lo:hi])
+        np.testing.assert_array_equal(m["Pmax_indx"], want["Pmax_indx"][lo:hi])
+        np.testing.assert_array_equal(m["best_vals"], want["best_vals"][lo:hi])
+        np.testing.assert_array_equal(m["Pmax"], want["Pmax"][lo:hi])
+        np.testing.assert_array_equal(m["chi2min"], want["chi2min"][lo:hi])
+        np.testing.assert_allclose(m["total_log_norm"], want["total_log_norm"][lo:hi], rtol=1e-14)
+        np.testing.assert_allclose(m["exp_vals"], want["exp_vals"][lo:hi], rtol=1e-12, atol=1e-300)
+        np.testing.assert_allclose(m["pdf1d"], np.concatenate([p[lo:hi] for p in want["pdf1d"]], axis=1),
+                                   rtol=1e-12, atol=1e-300)
+        np.testing.assert_allclose(m["per_vals"], want["per_vals"][lo:hi], rtol=1e-10, atol=1e-300)

@@ -107,6 +107,13 @@ class NumpyMergeMath:
     def scale_rows(self, rows, w):
         return rows * w.reshape(-1, *([1] * (rows.dim() - 1)))
 
+    def axpy_rows(self, w, src, dst, accumulate):
+        v = src * w.reshape(-1, *([1] * (src.dim() - 1)))
+        if accumulate:
+            dst += v
+        else:
+            dst.copy_(v)
+
     def finalize(self, pdf):
         import torch
 
