@@ -175,12 +175,17 @@ class SyntheticObservations:
         return SyntheticObservations(self.fluxes[slc], self.filters, ra, dec, extra)
 
 
-def make_sedgrid(axes="C1", filters=None, lamb=None, seed=1234):
+def make_sedgrid(axes="C1", filters=None, lamb=None, seed=1234, rows=None):
     """Build the tensor-product SED grid.
 
     ``axes`` is a name from ``CONFIG_AXES`` or an explicit 7-tuple.  Row order is
     C-order over (logA, M_ini, Z, Av, Rv, f_A, distance) -- stellar parameters
     outermost, dust innermost, which is how BEAST grids are laid out.
+
+    ``rows=(r0, r1)``: only that row slice of the grid (a subgrid as ``split_grid`` cuts them,
+    tools/subgridding_tools.py:39-91), built without materialising the rest; weights are
+    normalised over the whole grid, and the seeded roughness is drawn per slice, so a slice is
+    not bit-identical to the same rows of the full grid.
     """
     if isinstance(axes, str):
         axes = CONFIG_AXES[axes]
@@ -220,6 +225,20 @@ def make_sedgrid(axes="C1", filters=None, lamb=None, seed=1234):
 
     T = 10.0**logT
     R = 10.0**logR * _RSUN
+    n_star_all = gA.size
+    n_dust_all = n_Av * n_Rv * n_fA * n_d
+    w_total = float(((gw_star / n_dust_all) * pw_star).sum() * n_dust_all)
+    nm_all = n_star_all * n_dust_all
+    s0, s1 = 0, n_star_all
+    if rows is not None:
+        r0, r1 = int(rows[0]), int(rows[1])
+        s0, s1 = r0 // n_dust_all, -(-r1 // n_dust_all)
+
+    def _cut(a):
+        return a.reshape(-1)[s0:s1]
+
+    (gA, gM, gZ, logL, logT, logR, logg, M_act, mbol, gw_star, pw_star, T, R) = [
+        _cut(a) for a in (gA, gM, gZ, logL, logT, logR, logg, M_act, mbol, gw_star, pw_star, T, R)]
     n_star = gA.size
     f0 = _planck_lambda(lamb[None, :], T.reshape(-1, 1)) * (R.reshape(-1, 1) ** 2)  # x 1/d^2 later
 
@@ -262,16 +281,19 @@ def make_sedgrid(axes="C1", filters=None, lamb=None, seed=1234):
     cols["grid_weight"] = star_col(gw_star) / n_dust
     cols["prior_weight"] = star_col(pw_star)
     w = cols["grid_weight"] * cols["prior_weight"]
-    cols["weight"] = w / w.sum() * nm
-    cols["specgrid_indx"] = star_col(np.arange(n_star, dtype=np.int64))
+    cols["weight"] = w / w_total * nm_all
+    cols["specgrid_indx"] = star_col(np.arange(s0, s1, dtype=np.int64))
 
     # a hair of seeded roughness so ties between models are not systematic
-    rng = np.random.default_rng(seed)
+    rng = np.random.default_rng(seed if rows is None else [seed, s0])
     seds = seds * (1.0 + 1e-3 * rng.standard_normal(seds.shape))
     for b, f in enumerate(filters):
         cols["log" + f + "_wd"] = np.log10(seds[:, b])
 
-    return SyntheticSEDGrid(lamb, seds, cols, filters)
+    grid = SyntheticSEDGrid(lamb, seds, cols, filters)
+    if rows is not None:
+        grid = grid.subgrid(slice(r0 - s0 * n_dust_all, r1 - s0 * n_dust_all))
+    return grid
 
 
 def make_noisemodel(sedgrid, snr_cap=100.0, depth_scale=1.0):

@@ -36,6 +36,7 @@ CONFIGS = {
     "C2": ("C2", 100000, "PHAT 6-band 4e6-model grid, 1e5 stars, stats+pdf1d+sparse lnP"),
     "C3": ("C2", 1000000, "PHAT 6-band 4e6-model grid, 1e6 stars sharded over the GPUs (grid replicated)"),
     "C4": ("C4", 200000, "8-band UV-NIR grid 1e7 models, 2e5 stars"),
+    "C5": ("C5", 1000000, "2e7-model grid as 8 subgrids, NCCL merge of lnP/pdf1d/best-fit, 1e6 stars"),
 }
 THRESHOLD = -10.0  # summary_table_memory / run_fitting default (fit.py:924, run_fitting.py:303)
 MAX_NBINS = 200    # summary_table_memory default (fit.py:928)
@@ -481,6 +482,171 @@ def run_ours(args, rank, world, local_rank):
         dist.destroy_process_group()
 
 
+def run_c5(args, rank, world, local_rank):
+    """Config C5: the 2e7-model grid as 8 row slices (subgrids), every star fitted against every
+    slice (do_not_normalize, shared grid_info_dict) and the per-star partial results merged per
+    batch on the devices -- docs/subgrid_parallelism.rst:77-143 with the files replaced by an
+    all_gather of three scalars per (star, subgrid) and a reduce_scatter by star of the weighted
+    pdf1d / expectation sums (beast_b200.subgrid.SubgridFit).  N ranks hold 8/N slices each."""
+    import torch
+    import torch.distributed as dist
+
+    from beast_b200 import subgrid, synth
+    from beast_b200.engine import FitEngine
+    from beast_b200.gridprep import SKIP_KEYS, FitSetup
+
+    n_sub = 8
+    if n_sub % world:
+        raise SystemExit("C5 needs a number of GPUs that divides 8")
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    group = dist.group.WORLD if world > 1 else None
+    L = n_sub // world
+    axes = synth.CONFIG_AXES["C5"]
+    n_total = int(np.prod(axes))
+    slices = subgrid.uniform_slices(n_total, n_sub)
+    t0 = time.perf_counter()
+    mine = []
+    for l in range(L):
+        sl = slices[rank * L + l]
+        g = synth.make_sedgrid("C5", seed=1234, rows=(sl.start, sl.stop))
+        mine.append((g, synth.make_noisemodel(g)))
+    infos = [subgrid.subgrid_info(g, nz) for g, nz in mine]
+    for i in infos:  # only the number of unique values matters beyond the bin cap
+        for q in i:
+            if len(i[q]["unique"]) > 1000:
+                i[q]["unique"] = i[q]["unique"][:1001]
+    if world > 1:
+        gathered = [None] * world
+        dist.all_gather_object(gathered, infos)
+        infos = [x for part in gathered for x in part]
+    info = subgrid.reduce_grid_info(infos)
+    keys = [k for k in mine[0][0].keys() if k not in SKIP_KEYS]
+    engines = []
+    for g, nz in mine:
+        st = FitSetup(g, nz, list(keys), max_nbins=args.max_nbins, grid_info_dict=info, do_not_normalize=True)
+        engines.append(FitEngine(st, device=dev, gmin_budget_bytes=8 << 30, scratch_budget_bytes=8 << 30,
+                                 sparse_pass=args.sparse_pass))
+    setup_s = time.perf_counter() - t0
+    stars = args.stars or 1000000
+    # the same catalog on every rank: stars drawn from rank 0's first slice
+    obs = synth.make_observations(mine[0][0], mine[0][1], stars, seed=4321, with_coords=False)
+    fl = torch.from_numpy(np.ascontiguousarray(obs.fluxes)).to(dev)
+    if world > 1:
+        dist.broadcast(fl, 0)
+    fluxes = fl.cpu().numpy()
+    bs = min(e.max_batch for e in engines)
+    batches = [(a, min(stars, a + bs)) for a in range(0, stars, bs)]
+    sf = subgrid.SubgridFit(engines, subgrid.CudaMergeMath(engines[0].setup), group, rank, world)
+    n_models = sum(e.setup.n_models for e in engines)
+    if world > 1:
+        t = torch.tensor([n_models], dtype=torch.float64, device=dev)
+        dist.all_reduce(t)
+        n_models = int(t.item())
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize(dev)
+
+    def step(host_out=None):
+        for a, b in batches:
+            m = sf.fit_batch(fl[a:b] if host_out is None else fluxes[a:b], THRESHOLD)
+            if host_out is not None:
+                lo, hi = m["rows"]
+                for name in ("pdf1d", "per_vals", "exp_vals", "best_vals", "Pmax", "total_log_norm", "chi2min"):
+                    host_out[name][a + lo:a + hi].copy_(m[name], non_blocking=True)
+
+    sampler = ClockSampler(local_rank)
+    sampler.recording = False
+    sampler.start()
+    for _ in range(args.warmup):
+        step()
+    barrier()
+    for e in engines:
+        e.launches = 0
+    sf.collective_bytes = 0
+    sampler.recording = True
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    ev0.record()
+    for _ in range(args.steps):
+        step()
+    ev1.record()
+    barrier()
+    sampler.stop_flag = True
+    t = torch.tensor([ev0.elapsed_time(ev1)], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms_step = float(t.item()) / args.steps
+    launches = sum(e.launches for e in engines)
+    coll_bytes = sf.collective_bytes / max(args.steps, 1)
+    # one more step with the collectives timed on the device (synchronising)
+    sf.time_collectives, sf.collective_ms = True, 0.0
+    step()
+    barrier()
+    coll_ms = sf.collective_ms
+    sf.time_collectives = False
+    # end to end: host fluxes in, this rank's share of the merged rows back on the host
+    st0 = engines[0].setup
+    host = {"pdf1d": torch.empty((stars, st0.total_bins), dtype=torch.float64, pin_memory=True),
+            "per_vals": torch.empty((stars, st0.n_q, 3), dtype=torch.float64, pin_memory=True)}
+    for name in ("exp_vals", "best_vals"):
+        host[name] = torch.empty((stars, st0.n_q), dtype=torch.float64, pin_memory=True)
+    for name in ("Pmax", "total_log_norm", "chi2min"):
+        host[name] = torch.empty(stars, dtype=torch.float64, pin_memory=True)
+    step(host)
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        step(host)
+    barrier()
+    e2e_s = (time.perf_counter() - t0) / args.steps
+    t = torch.tensor([e2e_s], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        dist.destroy_process_group()
+    e2e_s = float(t.item())
+    if rank != 0:
+        return
+    peaks, peak_src = measured_peaks()
+    nb = st0.nb
+    peak_tf = engines[0].sm_count * 128 * 2 * float(peaks.get("sm_max_mhz", 1965.0)) * 1e6 / 1e12
+    value = stars * n_models / (ms_step * 1e-3)
+    share = -(-stars // world)
+    line = {
+        "metric": "star-model lnP evaluations per second", "value": value, "unit": "star*model/s",
+        "stars_per_s": stars / (ms_step * 1e-3), "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+        "ms_per_step": ms_step, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
+        "dtype": "f32 dense sweep + f64 exact pass", "data": "synthetic",
+        "config": {"workload": "2e7-model grid as 8 subgrids, NCCL merge of lnP/pdf1d/best-fit, 1e6 stars",
+                   "config": "C5", "models": n_models, "subgrids": n_sub, "subgrids_per_gpu": L, "bands": nb,
+                   "stars": stars, "threshold": THRESHOLD, "max_nbins": args.max_nbins,
+                   "outputs": "merged stats+pdf1d", "parallelism": "subgrids sharded, all stars on every GPU, "
+                   "per-batch all_gather + reduce_scatter by star",
+                   "l2": "inputs larger than L2"},
+        "clocks": sampler.summary(),
+        "e2e": {"value": stars * n_models / e2e_s, "unit": "star*model/s", "seconds_per_step": e2e_s,
+                "h2d_bytes_per_step": int(fluxes.nbytes),
+                "d2h_bytes_per_step": int(share * (st0.total_bins + 5 * st0.n_q + 3) * 8)},
+        "gpu_launches": int(launches),
+        "collective": {"payload_bytes_per_step_per_rank": int(coll_bytes), "ms_per_step": coll_ms,
+                       "bus_gbs": (coll_bytes * (world - 1) / world / (coll_ms * 1e-3) / 1e9) if coll_ms and world > 1 else None,
+                       "nvlink_gbs_reference": 770.0,
+                       "note": "reduce_scatter(SUM) by star of weight-scaled pdf1d + packed expectation/best rows, "
+                               "all_gather of total_log_norm/Pmax/chi2min; bus bandwidth = payload x (N-1)/N / device time"},
+        "roofline": {"bound": "fp32", "kernel": "whole step", "achieved": (4 * nb + 2) * stars * n_models / world / (ms_step * 1e-3) / 1e12,
+                     "peak": peak_tf, "unit": "TFLOP/s",
+                     "frac": (4 * nb + 2) * stars * n_models / world / (ms_step * 1e-3) / 1e12 / peak_tf, "traffic": None,
+                     "frac_of_fp32_peak": (4 * nb + 2) * stars * n_models / world / (ms_step * 1e-3) / 1e12 / peak_tf},
+        "cpu_baseline": None, "setup_seconds": setup_s,
+    }
+    _OUT.write(json.dumps(line) + "\n")
+    _OUT.flush()
+
+
 def main():
     # keep stdout for the one JSON line: libraries (NCCL's version banner, ...) write there too
     global _OUT
@@ -492,6 +658,9 @@ def main():
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
     if args.impl == "reference":
         run_reference(args, rank, world)
+        return
+    if args.config == "C5":
+        run_c5(args, rank, world, local_rank)
         return
     run_ours(args, rank, world, local_rank)
 

@@ -58,3 +58,57 @@ def test_three_subgrids_merge_matches_oracle():
         np.testing.assert_allclose(pdf[:, a:b], want["pdf1d"][k][:-1], rtol=util.PDF_RTOL, atol=util.PDF_ATOL)
         tol = util.bin_width_tolerance(setup0.bin_val[a:b])
         assert np.max(np.abs(per[:, k, :] - want["per_vals"][:, k, :])) <= 1e-6 * tol + 1e-12
+
+
+def test_resident_subgrids_merged_per_batch_at_size():
+    """two subgrids of 2e6 models each (C2's grid cut in half), resident on one GPU, every batch
+    merged on the device by SubgridFit -- against per-subgrid oracle fits + the restated merge
+    (pinned on the reference's merge_pdf1d_stats: tests/test_merge_reference.py) on six stars"""
+    import warnings
+
+    from beast_b200 import subgrid, synth
+    from beast_b200.engine import FitEngine
+    from beast_b200.gridprep import FitSetup
+    from oracle import fit_oracle as fo
+
+    axes = synth.CONFIG_AXES["C2"]
+    n = int(np.prod(axes))
+    slices = subgrid.uniform_slices(n, 2)
+    subs = []
+    for sl in slices:
+        g = synth.make_sedgrid("C2", seed=1234, rows=(sl.start, sl.stop))
+        subs.append((g, synth.make_noisemodel(g)))
+    obs = synth.make_observations(subs[0][0], subs[0][1], 48, seed=99, with_coords=False)
+    keys = fo.default_keys(subs[0][0])
+    info = subgrid.reduce_grid_info([subgrid.subgrid_info(g, nz) for g, nz in subs])
+    engines = []
+    with warnings.catch_warnings():
+        warnings.simplefilter("ignore")
+        for g, nz in subs:
+            st = FitSetup(g, nz, list(keys), max_nbins=200, grid_info_dict=info, do_not_normalize=True)
+            assert st.n_models == 2_000_000
+            engines.append(FitEngine(st, scratch_budget_bytes=4 << 30))
+    sf = subgrid.SubgridFit(engines, subgrid.CudaMergeMath(engines[0].setup))
+    m = sf.fit_batch(obs.fluxes, -10.0)
+    assert m["rows"] == (0, len(obs))
+    pick = [0, 5, 11, 23, 40, 47]
+    oparts = []
+    for g, nz in subs:
+        ost = fo.OracleSetup(g, nz, keys, max_nbins=200, grid_info_dict=info, do_not_normalize=True)
+        oparts.append(fo.fit_all(obs.fluxes[pick], ost, -10.0, fast=True, keep_sparse=False))
+    want = fo.merge_subgrid_results(oparts)
+    got = {k: (v.cpu().numpy()[pick] if hasattr(v, "cpu") else v) for k, v in m.items()}
+    np.testing.assert_array_equal(got["best_gridsub_tag"], want["best_gridsub_tag"])
+    np.testing.assert_array_equal(got["Pmax_indx"], want["Pmax_indx"])
+    np.testing.assert_array_equal(got["best_vals"], want["best_vals"])
+    np.testing.assert_allclose(got["Pmax"], want["Pmax"], rtol=0, atol=util.LNP_ATOL)
+    np.testing.assert_allclose(got["total_log_norm"], want["total_log_norm"], rtol=0, atol=util.LNP_ATOL)
+    np.testing.assert_allclose(got["chi2min"], want["chi2min"], rtol=util.STAT_RTOL)
+    st0 = engines[0].setup
+    span = np.array([info[q]["max"] - info[q]["min"] for q in st0.qnames]) + 1e-300
+    assert np.all(np.abs(got["exp_vals"] - want["exp_vals"]) <= util.STAT_RTOL * np.abs(want["exp_vals"]) + 1e-8 * span)
+    for k in range(st0.n_q):
+        a, b = st0.bin_off[k], st0.bin_off[k + 1]
+        np.testing.assert_allclose(got["pdf1d"][:, a:b], want["pdf1d"][k][:-1], rtol=util.PDF_RTOL, atol=util.PDF_ATOL)
+        tol = util.bin_width_tolerance(st0.bin_val[a:b])
+        assert np.max(np.abs(got["per_vals"][:, k, :] - want["per_vals"][:, k, :])) <= 1e-6 * tol + 1e-12
