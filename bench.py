@@ -531,11 +531,17 @@ def run_c5(args, rank, world, local_rank):
                                  sparse_pass=args.sparse_pass))
     setup_s = time.perf_counter() - t0
     stars = args.stars or 1000000
-    # the same catalog on every rank: stars drawn from rank 0's first slice
-    obs = synth.make_observations(mine[0][0], mine[0][1], stars, seed=4321, with_coords=False)
-    fl = torch.from_numpy(np.ascontiguousarray(obs.fluxes)).to(dev)
+    # the same catalog on every rank: an equal share of the stars is drawn from every slice
+    # (model index in proportion to the prior weight, observations.py:402-422), then interleaved
+    per_sub = -(-stars // n_sub)
+    parts = [synth.make_observations(g, nz, per_sub, seed=4321 + rank * L + l, with_coords=False).fluxes
+             for l, (g, nz) in enumerate(mine)]
+    loc = torch.from_numpy(np.ascontiguousarray(np.stack(parts))).to(dev)  # [L, per_sub, nb]
     if world > 1:
-        dist.broadcast(fl, 0)
+        allf = torch.empty((world,) + tuple(loc.shape), dtype=loc.dtype, device=dev)
+        dist.all_gather_into_tensor(allf, loc)
+        loc = allf.reshape(n_sub, per_sub, -1)
+    fl = loc.permute(1, 0, 2).reshape(n_sub * per_sub, -1)[:stars].contiguous()
     fluxes = fl.cpu().numpy()
     bs = min(e.max_batch for e in engines)
     batches = [(a, min(stars, a + bs)) for a in range(0, stars, bs)]
@@ -583,12 +589,22 @@ def run_c5(args, rank, world, local_rank):
     ms_step = float(t.item()) / args.steps
     launches = sum(e.launches for e in engines)
     coll_bytes = sf.collective_bytes / max(args.steps, 1)
-    # one more step with the collectives timed on the device (synchronising)
+    # one more step with the collectives and the stages of bf_fit_batch timed on the device
+    # (synchronising: outside the timed region)
     sf.time_collectives, sf.collective_ms = True, 0.0
+    for e in engines:
+        e.profile = True
+        e.stage_ms()
     step()
     barrier()
     coll_ms = sf.collective_ms
     sf.time_collectives = False
+    stage_tot = {}
+    for e in engines:
+        tot, _ = e.stage_ms()
+        e.profile = False
+        for k, v in tot.items():
+            stage_tot[k] = stage_tot.get(k, 0.0) + v
     # end to end: host fluxes in, this rank's share of the merged rows back on the host
     st0 = engines[0].setup
     host = {"pdf1d": torch.empty((stars, st0.total_bins), dtype=torch.float64, pin_memory=True),
@@ -641,6 +657,7 @@ def run_c5(args, rank, world, local_rank):
                      "peak": peak_tf, "unit": "TFLOP/s",
                      "frac": (4 * nb + 2) * stars * n_models / world / (ms_step * 1e-3) / 1e12 / peak_tf, "traffic": None,
                      "frac_of_fp32_peak": (4 * nb + 2) * stars * n_models / world / (ms_step * 1e-3) / 1e12 / peak_tf},
+        "stage_ms_per_step_rank0": stage_tot,
         "cpu_baseline": None, "setup_seconds": setup_s,
     }
     _OUT.write(json.dumps(line) + "\n")
