@@ -361,13 +361,14 @@ int launch_weights_grouped(const bf_exact_grid& grid, const double* flux64, cons
 // (B) split histogram kernel
 // =========================================================================================
 constexpr int kSplitWarpsMax = 20;
+constexpr uint32_t kSegmentChunks = 8192;  // chunks of a star's list worked through at a time
 
 // shared memory: hist [hist_doubles] | red [2 NW] | redj [NW] | sscan (NW u32, as NW/2 doubles)
 //   | epart [NW][32] | int tables (see kernel); sized for the largest block
 constexpr int kSplitInts = 3 * 64 + 2 * 64 + 128 + 64 + 16;
 struct SplitSmem {
   static __host__ __device__ size_t bytes(int hist_doubles) {
-    return (static_cast<size_t>(hist_doubles) + 4 * kSplitWarpsMax + kSplitWarpsMax * 32) * sizeof(double) +
+    return (static_cast<size_t>(hist_doubles) + 4 * kSplitWarpsMax + kSplitWarpsMax * 32 + 64) * sizeof(double) +
            kSplitInts * sizeof(int);
   }
 };
@@ -707,7 +708,8 @@ split_hist_kernel(bf_param_tables prm, int hist_doubles, const double* __restric
   long long* redj = reinterpret_cast<long long*>(red + 2 * kSplitWarpsMax);
   uint32_t* sscan = reinterpret_cast<uint32_t*>(redj + kSplitWarpsMax);
   double* epart = red + 4 * kSplitWarpsMax;  // [NW][32]
-  int* wmin = reinterpret_cast<int*>(epart + kSplitWarpsMax * 32);  // [64]: fast 0..31, slow 32..63
+  double* esum = epart + kSplitWarpsMax * 32;  // [64] expectation sums by parameter
+  int* wmin = reinterpret_cast<int*>(esum + 64);  // [64]: fast 0..31, slow 32..63
   int* wmax = wmin + 64;
   int* kcls = wmax + 64;       // [64] by parameter: class-local index, +32 for slow (n_q <= 64)
   int* lparam = kcls + 64;     // [2][32] by class and lane: class-local parameter or -1
@@ -721,10 +723,6 @@ split_hist_kernel(bf_param_tables prm, int hist_doubles, const double* __restric
   const uint32_t e0 = offsets[s * BF_SELECT_SPLIT];
   const uint32_t e1 = offsets[(s + 1) * BF_SELECT_SPLIT];
   const double M = pmax[s];
-  for (int i = threadIdx.x; i < 64; i += blockDim.x) {
-    wmin[i] = 255;
-    wmax[i] = 0;
-  }
   for (int i = threadIdx.x; i < nf; i += blockDim.x) kcls[prm.fast_k[i]] = i;
   for (int i = threadIdx.x; i < nsl; i += blockDim.x) kcls[prm.slow_k[i]] = 32 + i;
 
@@ -784,11 +782,49 @@ split_hist_kernel(bf_param_tables prm, int hist_doubles, const double* __restric
     carry_s += tot >> 16;
   }
   const uint32_t n_mc = carry_f, n_sc = carry_s;
+  for (int i = threadIdx.x; i < 64; i += blockDim.x) esum[i] = 0.0;
+  if (threadIdx.x == 0) {
+    misc[10] = 0;
+    if (sc.star_flags) sc.star_flags[s - star_begin] = 1;
+  }
+
+  // A star with a long chunk list is worked through in segments of the list.  The list is in
+  // model order, so a segment covers a narrow stretch of the stellar axes: its bin ranges are
+  // narrower than the whole star's, the private copies smaller, and more warps get one -- a
+  // broad star as a whole leaves room for 8 fast warps of 20.  Every segment adds its merged
+  // copies to the star's pdf rows (in global memory, not normalised yet).
+  const uint32_t n_seg = n_mc > kSegmentChunks + kSegmentChunks / 2 ? (n_mc + kSegmentChunks / 2) / kSegmentChunks : 1u;
+  const uint32_t seg_len = (n_mc + n_seg - 1) / n_seg;
+  for (uint32_t seg = 0; seg < n_seg; ++seg) {
+  const uint32_t f0 = seg * seg_len;
+  const uint32_t nf_seg = n_mc - f0 < seg_len ? n_mc - f0 : seg_len;
+  for (int i = threadIdx.x; i < 64; i += blockDim.x) {
+    wmin[i] = 255;
+    wmax[i] = 0;
+  }
+  if (threadIdx.x == 0) {
+    // the slow runs of this segment: those that start before the next segment's first chunk
+    uint32_t hi = n_sc;
+    if (seg + 1 < n_seg) {
+      const uint32_t next_chunk = refs[f0 + nf_seg].x;
+      uint32_t lo = misc[10];
+      while (lo < hi) {
+        const uint32_t mid = lo + (hi - lo) / 2;
+        if (srefs[mid].x < next_chunk) lo = mid + 1; else hi = mid;
+      }
+      hi = lo;
+    }
+    misc[9] = misc[10];
+    misc[10] = hi;
+  }
   __syncthreads();  // refs (global) and the tables above are visible to the whole block
+  const uint32_t s0 = misc[9], ns_seg = misc[10] - misc[9];
+  const uint2* frefs = refs + f0;
+  const uint2* sseg = srefs + s0;
 
   // ---- occupied bin ranges -----------------------------------------------------------------
-  if (nf > 0) class_ranges<FS, true>(prm, refs, n_mc, warp, NW, lane, nf, wmin, wmax);
-  if (nsl > 0) class_ranges<SS, false>(prm, srefs, n_sc, warp, NW, lane, nsl, wmin + 32, wmax + 32);
+  if (nf > 0) class_ranges<FS, true>(prm, frefs, nf_seg, warp, NW, lane, nf, wmin, wmax);
+  if (nsl > 0) class_ranges<SS, false>(prm, sseg, ns_seg, warp, NW, lane, nsl, wmin + 32, wmax + 32);
   __syncthreads();
 
   // ---- layout: warp 0 the fast class, warp 1 the slow class ----------------------------------
@@ -825,62 +861,61 @@ split_hist_kernel(bf_param_tables prm, int hist_doubles, const double* __restric
     if (nf > 0 && F > NW - S - X) F = NW - S - X;
     misc[3] = F;
     misc[4] = S;
-    misc[8] = 0;  // chunks the first fast warp has passed
+    misc[8] = 0;  // chunks of the segment the first fast warp has passed
   }
   __syncthreads();
   const int cf = misc[1], cs = misc[2], F = misc[3], S = misc[4];
   volatile uint32_t* progress = reinterpret_cast<volatile uint32_t*>(misc + 8);
   const int used = F * cf + S * cs;
   for (int i = threadIdx.x; i < used; i += blockDim.x) hist[i] = 0.0;
-  if (threadIdx.x == 0 && sc.star_flags) sc.star_flags[s - star_begin] = 1;
   __syncthreads();
 
   // ---- accumulate ---------------------------------------------------------------------------
   double eacc = 0.0;
-  if (n_mc > 0) {
+  if (nf_seg > 0) {
     if (warp < F) {
       const int kf = lparam[lane];
       fast_accumulate<FS>(prm.fast_bin + (kf >= 0 ? kf : 0) * BF_CHUNK,
                           static_cast<uint32_t>(prm.fast_pad) * BF_CHUNK, kf >= 0 ? 0xffffffffu : 0u,
-                          sc.weights, refs, n_mc, warp, F, lane, hist + warp * cf + lcol[lane],
+                          sc.weights, frefs, nf_seg, warp, F, lane, hist + warp * cf + lcol[lane],
                           warp == 0 ? progress : nullptr);
       if (warp == 0 && lane == 0) *progress = 0xffffffffu - kPrefetchAhead;  // release the followers
     } else if (warp < F + S) {
       const int ks = lparam[32 + lane];
       const bool live = ks >= 0;
       const bool live_q = live && !(prm.q_const && prm.q_const[prm.slow_k[live ? ks : 0]]);
-      eacc = slow_accumulate<SS>(prm, sc.chunk_wsum, srefs, n_sc, warp - F, S, live ? ks : 0, live,
+      eacc = slow_accumulate<SS>(prm, sc.chunk_wsum, sseg, ns_seg, warp - F, S, live ? ks : 0, live,
                                  live_q, lane, hist + F * cf + (warp - F) * cs + lcol[32 + lane]);
     } else if (nf > 0) {
-      // warps without a private copy add up the expectation partials of the fast class that
-      // the grouped weights kernel left per list position: lane <-> (parameter, part)
-      const int pad = prm.fast_pad;
-      const int per = 32 / pad;  // list positions per warp instruction
-      const int p = lane % pad, sub = lane / pad;
-      const uint32_t stride = static_cast<uint32_t>(NW - F - S) * per;
-      const double* src = sc.exp_part + p;
-      double acc8[8];
+      if (seg == 0) {
+        // warps without a private copy add up the expectation partials of the fast class that
+        // the grouped weights kernel left per list position: lane <-> (parameter, part)
+        const int pad = prm.fast_pad;
+        const int per = 32 / pad;  // list positions per warp instruction
+        const int p = lane % pad, sub = lane / pad;
+        const uint32_t stride = static_cast<uint32_t>(NW - F - S) * per;
+        const double* src = sc.exp_part + p;
+        double acc8[8];
 #pragma unroll
-      for (int u = 0; u < 8; ++u) acc8[u] = 0.0;
-      for (uint32_t e = e0 + (warp - F - S) * per + sub; e < e1; e += 8 * stride) {
+        for (int u = 0; u < 8; ++u) acc8[u] = 0.0;
+        for (uint32_t e = e0 + (warp - F - S) * per + sub; e < e1; e += 8 * stride) {
 #pragma unroll
-        for (int u = 0; u < 8; ++u) {  // eight rows in flight per lane
-          const uint32_t eu = e + u * stride;
-          if (eu < e1) acc8[u] += __ldg(src + (static_cast<size_t>(eu) - entry_base) * pad);
+          for (int u = 0; u < 8; ++u) {  // eight rows in flight per lane
+            const uint32_t eu = e + u * stride;
+            if (eu < e1) acc8[u] += __ldg(src + (static_cast<size_t>(eu) - entry_base) * pad);
+          }
         }
+        eacc = ((acc8[0] + acc8[1]) + (acc8[2] + acc8[3])) + ((acc8[4] + acc8[5]) + (acc8[6] + acc8[7]));
       }
-      eacc = ((acc8[0] + acc8[1]) + (acc8[2] + acc8[3])) + ((acc8[4] + acc8[5]) + (acc8[6] + acc8[7]));
       if (F > 0 && NW - F - S >= 4)  // (with fewer idle warps the fast warps cover the latency)
-        prefetch_rows(prm, sc.weights, sc.chunk_wsum, refs, n_mc, srefs, n_sc, warp - F - S,
+        prefetch_rows(prm, sc.weights, sc.chunk_wsum, frefs, nf_seg, sseg, ns_seg, warp - F - S,
                       NW - F - S, lane, progress);
     }
   }
   epart[warp * 32 + lane] = eacc;
+  __syncthreads();
 
-  const double wtot = star_totals(e0, e1, entry_base, sc, M, s, red, redj, out);  // syncs
-  const bool empty = !(wtot > 0.0);
-
-  // ---- expectations of the parameters not taken from the histogram (fit.py:743) -------------
+  // ---- this segment's expectation sums (fit.py:743), by parameter ------------------------------
   const int nx = NW - F - S;
   for (int k = threadIdx.x; k < nq; k += blockDim.x) {
     if (prm.q_const && prm.q_const[k]) continue;
@@ -890,17 +925,16 @@ split_hist_kernel(bf_param_tables prm, int hist_doubles, const double* __restric
       const int p = cl & 31;
       for (int w = 0; w < S; ++w)
         for (int sl = 0; sl < SS; ++sl) e += epart[(F + w) * 32 + plane[64 + sl * 32 + p]];
-    } else {
+    } else if (seg == 0) {
       const int pad = prm.fast_pad;
       for (int w = 0; w < nx; ++w)
         for (int sub = 0; sub < 32 / pad; ++sub) e += epart[(F + S + w) * 32 + sub * pad + cl];
     }
-    out.exp_vals[s * nq + k] = empty ? __longlong_as_double(0x7ff8000000000000LL)
-                                     : prm.q_lin[2 * k] + prm.q_lin[2 * k + 1] * (e / wtot);
+    esum[k] += e;
   }
 
-  // ---- merge the private copies (fixed order), normalise; bins outside the range are 0 ------
-  const double inv = empty ? 0.0 : 1.0 / wtot;
+  // ---- merge the private copies (fixed order) into the star's rows; the first segment writes
+  // every bin (0 outside its ranges), the later ones add inside theirs ---------------------------
   for (int kq = warp; kq < nq; kq += NW) {
     const int b0 = prm.bin_off[kq];
     const int nbk = prm.bin_off[kq + 1] - b0;
@@ -915,13 +949,36 @@ split_hist_kernel(bf_param_tables prm, int hist_doubles, const double* __restric
     const int* lc = lcol + (slow ? 32 : 0);
     const int* pl = plane + (slow ? 64 : 0);
     double* row = out.pdf1d + s * tb + b0;
+    for (int b = lane; b < nbk; b += 32) {
+      const bool inside = b >= mn && b < mn + width;
+      if (!inside && seg > 0) continue;
+      double v = 0.0;
+      if (inside)
+        for (int w = 0; w < ncopy; ++w)
+          for (int sl = 0; sl < slots; ++sl) v += area[w * csize + lc[pl[sl * 32 + p]] + b * 16];
+      row[b] = seg == 0 ? v : row[b] + v;
+    }
+  }
+  __syncthreads();  // the copies and the layout tables are free for the next segment
+  }  // segments
+
+  const double wtot = star_totals(e0, e1, entry_base, sc, M, s, red, redj, out);  // syncs
+  const bool empty = !(wtot > 0.0);
+  for (int k = threadIdx.x; k < nq; k += blockDim.x) {
+    if (prm.q_const && prm.q_const[k]) continue;
+    out.exp_vals[s * nq + k] = empty ? __longlong_as_double(0x7ff8000000000000LL)
+                                     : prm.q_lin[2 * k] + prm.q_lin[2 * k + 1] * (esum[k] / wtot);
+  }
+  // ---- normalise (fit.py:690); expectations of the parameters whose bins hold one value ------
+  const double inv = empty ? 0.0 : 1.0 / wtot;
+  for (int kq = warp; kq < nq; kq += NW) {
+    const int b0 = prm.bin_off[kq];
+    const int nbk = prm.bin_off[kq + 1] - b0;
+    double* row = out.pdf1d + s * tb + b0;
     const bool from_bins = prm.q_const && prm.q_const[kq];
     double eq = 0.0;
     for (int b = lane; b < nbk; b += 32) {
-      double v = 0.0;
-      if (b >= mn && b < mn + width)
-        for (int w = 0; w < ncopy; ++w)
-          for (int sl = 0; sl < slots; ++sl) v += area[w * csize + lc[pl[sl * 32 + p]] + b * 16];
+      const double v = row[b];
       row[b] = v * inv;
       if (from_bins) eq += v * prm.bin_q[b0 + b];
     }
