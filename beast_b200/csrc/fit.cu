@@ -268,10 +268,16 @@ extern "C" int bf_fit_batch(const bf_fit_plan* plan, int64_t n_stars, const doub
 
   // ---- presort: coarse sweep, stars ordered by the group of their coarse minimum ----------------
   int32_t* perm = nullptr;  // sorted position -> input position
+  int sm_count = p.sm_count;
+  if (sm_count <= 0) {
+    int dev = 0;
+    BF_CUDA_TRY(cudaGetDevice(&dev));
+    BF_CUDA_TRY(cudaDeviceGetAttribute(&sm_count, cudaDevAttrMultiProcessorCount, dev));
+  }
   const bool cov = p.full_cov != 0;
   auto dense = [&](int64_t n_tiles, const float* tiles, float* gmin) -> int {
     starmin_init_kernel<<<blocks_for(ld), kT, 0, st>>>(ld, starmin);
-    const int tpi = bf_dense_tiles_per_item(n_tiles, n, p.sm_count > 0 ? p.sm_count : 148);
+    const int tpi = bf_dense_tiles_per_item(n_tiles, n, sm_count);
     launches += 2;
     return cov ? bf_dense_chi2_cov(nb, n_tiles, tiles, n, ld, flux32, gmin, reinterpret_cast<uint64_t*>(starmin), tpi, stream)
                : bf_dense_chi2(nb, n_tiles, tiles, n, ld, flux32, gmin, reinterpret_cast<uint64_t*>(starmin), tpi, stream);

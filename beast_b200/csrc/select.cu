@@ -7,6 +7,8 @@
 // of the exact sparse set lives in a surviving group.  The exact FP64 test happens in
 // exact.cu.
 
+#include <atomic>
+
 #include "common.cuh"
 
 namespace bf {
@@ -229,17 +231,31 @@ extern "C" int bf_exclusive_scan_u32_noalloc(int64_t n, const uint32_t* in, uint
   }
   int dev = 0;
   BF_CUDA_TRY(cudaGetDevice(&dev));
-  static uint32_t* scratch_of_device[64] = {};
+  // one slot per device ordinal; atomic because several host threads may make their first call
+  // at once (they would all store the same address)
+  static std::atomic<uint32_t*> scratch_of_device[64];
   if (dev < 0 || dev >= 64) {
     set_error("bf_exclusive_scan_u32_noalloc: device ordinal %d not supported", dev);
     return BF_ERR_UNSUPPORTED;
   }
-  if (scratch_of_device[dev] == nullptr) {
-    uint32_t* p = nullptr;
-    BF_CUDA_TRY(cudaGetSymbolAddress(reinterpret_cast<void**>(&p), g_scan_tile_sums));
-    scratch_of_device[dev] = p;
+  if (stream != nullptr) {
+    // the array that is looked up belongs to the current GPU: a stream of another GPU would run
+    // the kernels there with this GPU's address
+    int sdev = dev;
+    const cudaError_t e = cudaStreamGetDevice(static_cast<cudaStream_t>(stream), &sdev);
+    if (e == cudaSuccess && sdev != dev) {
+      set_error("bf_exclusive_scan_u32_noalloc: the stream belongs to GPU %d but GPU %d is current; "
+                "make the stream's GPU current for every call", sdev, dev);
+      return BF_ERR_INVALID;
+    }
+    if (e != cudaSuccess) (void)cudaGetLastError();  // (older drivers: no such query; rule stays documented)
+  }
+  uint32_t* scratch = scratch_of_device[dev].load(std::memory_order_acquire);
+  if (scratch == nullptr) {
+    BF_CUDA_TRY(cudaGetSymbolAddress(reinterpret_cast<void**>(&scratch), g_scan_tile_sums));
+    scratch_of_device[dev].store(scratch, std::memory_order_release);
   }
   // every tile sum of this call is written by the first kernel before the second reads it,
   // so nothing left over from an earlier call has to be cleared
-  return run_scan(n, in, out, scratch_of_device[dev], static_cast<cudaStream_t>(stream));
+  return run_scan(n, in, out, scratch, static_cast<cudaStream_t>(stream));
 }

@@ -264,7 +264,10 @@ extern "C" int bf_pdf2d_from_weights(int64_t ld_model, int n_pairs, const int32_
              "bf_pdf2d_from_weights: null pointer");
   if (n_entries == 0) return BF_OK;
   const int64_t blocks = (n_entries + kPdf2dWarps - 1) / kPdf2dWarps;
-  const int64_t cap = 148LL * 64;
+  int dev = 0, sms = 0;
+  BF_CUDA_TRY(cudaGetDevice(&dev));
+  BF_CUDA_TRY(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+  const int64_t cap = static_cast<int64_t>(sms) * 64;  // grid-stride kernel: 64 blocks per SM
   pdf2d_weights_kernel<<<static_cast<unsigned>(blocks < cap ? blocks : cap), kPdf2dWarps * 32, 0,
                          static_cast<cudaStream_t>(stream)>>>(
       ld_model, n_pairs, pair_bin, pair_off, pmax, total_log_norm, list, entry_star, member_mask,

@@ -361,7 +361,9 @@ int launch_weights_grouped(const bf_exact_grid& grid, const double* flux64, cons
 // (B) split histogram kernel
 // =========================================================================================
 constexpr int kSplitWarpsMax = 20;
-constexpr uint32_t kSegmentChunks = 8192;  // chunks of a star's list worked through at a time
+// chunks of a star's list worked through at a time (C2: 54 ms per 33,792 stars with or without
+// segments of this size; C5, whose subgrid posteriors are broad: 2.0 s -> 1.6 s per 16,384 stars)
+constexpr uint32_t kSegmentChunks = 16384;
 
 // shared memory: hist [hist_doubles] | red [2 NW] | redj [NW] | sscan (NW u32, as NW/2 doubles)
 //   | epart [NW][32] | int tables (see kernel); sized for the largest block
@@ -694,7 +696,7 @@ __device__ __forceinline__ void class_ranges(const bf_param_tables& prm, const u
 
 template <int FS, int SS>  // chunk slots per instruction of the fast / slow class (1 or 2)
 __global__ void __launch_bounds__(kSplitWarpsMax * 32, 1)
-split_hist_kernel(bf_param_tables prm, int hist_doubles, const double* __restrict__ pmax,
+split_hist_kernel(bf_param_tables prm, int hist_doubles, uint32_t seg_chunks, const double* __restrict__ pmax,
                   const uint32_t* __restrict__ offsets, const uint32_t* __restrict__ list,
                   const int32_t* __restrict__ star_order, int64_t star_begin, int64_t entry_base,
                   bf_accum_scratch sc, double p0, double p1, double p2, bf_star_outputs out) {
@@ -793,7 +795,7 @@ split_hist_kernel(bf_param_tables prm, int hist_doubles, const double* __restric
   // narrower than the whole star's, the private copies smaller, and more warps get one -- a
   // broad star as a whole leaves room for 8 fast warps of 20.  Every segment adds its merged
   // copies to the star's pdf rows (in global memory, not normalised yet).
-  const uint32_t n_seg = n_mc > kSegmentChunks + kSegmentChunks / 2 ? (n_mc + kSegmentChunks / 2) / kSegmentChunks : 1u;
+  const uint32_t n_seg = n_mc > seg_chunks + seg_chunks / 2 ? (n_mc + seg_chunks / 2) / seg_chunks : 1u;
   const uint32_t seg_len = (n_mc + n_seg - 1) / n_seg;
   for (uint32_t seg = 0; seg < n_seg; ++seg) {
   const uint32_t f0 = seg * seg_len;
@@ -1025,6 +1027,9 @@ int launch_split_hist(const bf_param_tables& prm, const double* pmax, const uint
   if (const char* env = getenv("BF_SPLIT_WARPS"))
     if (env[0] == '1' && split_fits(prm, half, kSplitWarpsMax / 2)) warps = kSplitWarpsMax / 2;
   const int hd = split_hist_doubles(warps == kSplitWarpsMax ? smem_budget : half);
+  uint32_t seg_chunks = kSegmentChunks;  // BF_SEG=<chunks>: measurements
+  if (const char* env = getenv("BF_SEG")) seg_chunks = static_cast<uint32_t>(strtoul(env, nullptr, 10));
+  if (seg_chunks < 256) seg_chunks = 256;
   const size_t smem = SplitSmem::bytes(hd);
   const int fs = prm.fast_pad == 16 ? 2 : 1, ss = prm.slow_pad == 16 ? 2 : 1;
   static bool configured[64][4] = {};
@@ -1042,7 +1047,7 @@ int launch_split_hist(const bf_param_tables& prm, const double* pmax, const uint
       configured[dev][(A - 1) * 2 + (B - 1)] = true;                                           \
     }                                                                                          \
     split_hist_kernel<A, B><<<static_cast<unsigned>(n_stars), warps * 32, smem, st>>>(         \
-        prm, hd, pmax, offsets, list, star_order, star_begin, entry_base, sc, p0, p1, p2, out); \
+        prm, hd, seg_chunks, pmax, offsets, list, star_order, star_begin, entry_base, sc, p0, p1, p2, out); \
   }
   BF_SPLIT_CASE(1, 1)
   BF_SPLIT_CASE(1, 2)

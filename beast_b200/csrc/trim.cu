@@ -62,7 +62,7 @@ extern "C" int bf_trim_flags(int nb, int64_t n_models, const double* seds, const
                              const double* min_data, const double* max_data, uint32_t* pattern,
                              uint32_t* hist, void* stream) {
   using namespace bf;
-  BF_REQUIRE(nb >= 1 && nb <= BF_MAX_BANDS, "bf_trim_flags: nb=%d out of range", nb);
+  BF_REQUIRE(nb >= 1 && nb <= 15, "bf_trim_flags: nb=%d out of range (1..15: one pattern bit per band)", nb);
   BF_REQUIRE(n_models > 0 && (n_models + 255) / 256 < (1LL << 31), "bf_trim_flags: bad n_models");
   BF_REQUIRE(seds && bias && unc && completeness && min_data && max_data && pattern && hist,
              "bf_trim_flags: null pointer");

@@ -25,7 +25,7 @@ import warnings
 
 import numpy as np
 
-from ._cabi import CHUNK, GROUP, MAX_BANDS, MAX_PARAMS, TILE_MODELS
+from ._cabi import CHUNK, GROUP, MAX_PARAMS, TILE_MODELS
 
 SKIP_KEYS = "osl keep weight grid_weight prior_weight fullgrid_idx stage specgrid_indx phase eep".split()
 LOG_SPACED_PARAMS = {"M_ini", "M_act", "radius"}
@@ -135,8 +135,8 @@ class FitSetup:
         weight = np.asarray(sedgrid["weight"], dtype=np.float64)
         filters = list(sedgrid.filters)
         nb = len(filters)
-        if nb > MAX_BANDS:
-            raise NotImplementedError("at most %d bands are supported (got %d)" % (MAX_BANDS, nb))
+        if nb > 12:  # (the dense sweep is instantiated per band count, 1..12)
+            raise NotImplementedError("at most 12 bands are supported (got %d)" % nb)
         (g0,) = np.where(weight > 0.0)
         for i in range(nb):
             if np.any(np.asarray(obsmodel["completeness"])[:, i] <= 0.0):

@@ -33,7 +33,8 @@ extern "C" {
 #define BF_GROUP 64        /* models per group minimum                            */
 #define BF_CHUNK 8         /* models per parameter-table chunk                    */
 #define BF_STAR_BLOCK 1024 /* stars per thread block of the dense pass            */
-#define BF_MAX_BANDS 16
+#define BF_MAX_BANDS 16   /* array bound; the diagonal likelihood is built for 1..12 bands,
+                             the full-covariance one for 2..8, trimming for 1..15 */
 #define BF_MAX_PARAMS 128
 #define BF_SELECT_SPLIT 16 /* model-axis splits of the group-selection pass       */
 
@@ -125,7 +126,10 @@ int bf_exclusive_scan_u32(int64_t n, const uint32_t* in, uint32_t* out, uint32_t
  *    (use bf_exclusive_scan_u32).  The array costs 256 KiB on every GPU that loads the library,
  *    for the life of the process.
  *  - The first call on each GPU looks up the array's device address (with that GPU current);
- *    make that first call before starting any stream capture.
+ *    make that first call before starting any stream capture.  The GPU that owns `stream` must
+ *    be the current one on every call (checked where the driver can tell); the address is
+ *    remembered per GPU for the life of the process, so do not call this again on a GPU after
+ *    cudaDeviceReset.
  *  - All calls on one GPU share the array.  Its previous contents never matter (each call
  *    overwrites what it later reads), but two calls that overlap on the GPU -- different streams,
  *    or different host threads -- race on it: serialise them.
@@ -282,7 +286,10 @@ int bf_group_order(int64_t n_groups, const uint32_t* list, int64_t entry_base, i
  * percentiles_host : [3] host doubles in percent.
  * aux_stream : optional second stream; when given and the full-width histogram kernel is used,
  *              the expectation kernel runs on it next to the histogram kernel (ordered by
- *              events; `stream` has joined it on return). */
+ *              events; `stream` has joined it on return).  The two events that order the streams
+ *              are created on the first such call and kept per GPU: one caller at a time per GPU
+ *              may use aux_stream (callers on different GPUs are independent).
+ * The first call on a GPU also configures the kernels' shared-memory limits (cudaFuncSetAttribute). */
 int bf_exact_accumulate(const bf_exact_grid* grid, const bf_param_tables* params,
                         int64_t star_begin, int64_t n_stars, const double* flux64, const double* pmax,
                         double threshold, const uint32_t* offsets, const uint32_t* list,
