@@ -307,6 +307,8 @@ def IAU_names_and_extra_info(obsdata, surveyname="PHAT", extraInfo=False):
 
 # ---------------------------------------------------------------------------------------
 def _load_grid(sedgrid, gridbackend):
+    if isinstance(sedgrid, str) and sedgrid.lower().endswith((".fits", ".fit")):
+        return fitsio.read_sedgrid_fits(sedgrid)  # no astropy needed (gridbackends.py:345-365)
     if isinstance(sedgrid, str):
         try:
             from beast.physicsmodel.grid import SEDGrid

@@ -22,6 +22,9 @@ BLOCK = 2880
 
 
 def _card(key, value=None, comment=""):
+    """one or more 80-character header cards.  A string that does not fit the 68 characters a
+    card offers is continued with the long-string convention (FITS 4.0 section 4.2.1.2: '&' at
+    the end of the value, CONTINUE cards after it) instead of being cut."""
     if value is None:
         s = key.ljust(8)
     elif isinstance(value, bool):
@@ -32,10 +35,26 @@ def _card(key, value=None, comment=""):
         s = "%-8s= %20s" % (key, repr(float(value)).upper())
     else:
         v = str(value).replace("'", "''")
-        s = "%-8s= '%-8s'" % (key, v)
-    if comment:
+        if len(v) <= 68:
+            s = "%-8s= '%-8s'" % (key, v)
+        else:
+            pieces, rest = [], v
+            while len(rest) > 67:
+                cut = 67
+                if rest[cut - 1] == "'" and (len(rest[:cut]) - len(rest[:cut].rstrip("'"))) % 2 == 1:
+                    cut -= 1  # never split a doubled quote
+                pieces.append(rest[:cut])
+                rest = rest[cut:]
+            pieces.append(rest)
+            cards = ["%-8s= '%s&'" % (key, pieces[0])]
+            for i, pc in enumerate(pieces[1:], start=1):
+                cards.append("CONTINUE  '%s%s'" % (pc, "&" if i < len(pieces) - 1 else ""))
+            return "".join(c.ljust(80) for c in cards)
+    if comment and len(s) + 3 + len(comment) <= 80:
         s += " / " + comment
-    return s[:80].ljust(80)
+    if len(s) > 80:
+        raise ValueError("FITS header card too long: %r" % s)
+    return s.ljust(80)
 
 
 def _header_bytes(cards):
@@ -77,8 +96,8 @@ def write_image_file(path, arrays, names):
             f.write(_pad_data(arr.astype(">f8").tobytes()))
 
 
-def _table_hdu(columns):
-    """columns: ordered dict name -> 1-D array (float / int / str)"""
+def _table_hdu(columns, extname=None, extra=None):
+    """columns: ordered dict name -> 1-D array (float / int / str); extra: header keywords"""
     names = list(columns.keys())
     nrows = len(next(iter(columns.values()))) if names else 0
     fields = []
@@ -103,6 +122,10 @@ def _table_hdu(columns):
     for i, f in enumerate(fields):
         cards.append(_card("TTYPE%d" % (i + 1), f[0]))
         cards.append(_card("TFORM%d" % (i + 1), f[1]))
+    if extname is not None:
+        cards.append(_card("EXTNAME", extname, "extension name"))
+    for k, v in (extra or {}).items():
+        cards.append(_card(k.upper()[:8], v))
     return _header_bytes(cards) + _pad_data(rec.tobytes())
 
 
@@ -116,6 +139,21 @@ def write_table_file(path, tables):
 
 
 # ------------------------------------------------------------------------------
+def _quoted(v):
+    """text of a quoted FITS string whose opening quote has been consumed"""
+    out, j = "", 0
+    while j < len(v):
+        if v[j] == "'":
+            if j + 1 < len(v) and v[j + 1] == "'":
+                out += "'"
+                j += 2
+                continue
+            break
+        out += v[j]
+        j += 1
+    return out.rstrip()
+
+
 def _parse_header(buf, pos):
     cards = {}
     order = []
@@ -129,22 +167,18 @@ def _parse_header(buf, pos):
             if key == "END":
                 done = True
                 break
+            if key == "CONTINUE" and order and isinstance(cards.get(order[-1]), str):
+                prev = cards[order[-1]]
+                if prev.endswith("&"):  # long-string convention
+                    v = c[8:].lstrip()
+                    piece = _quoted(v[1:]) if v.startswith("'") else ""
+                    cards[order[-1]] = prev[:-1] + piece
+                continue
             if c[8:10] != "= ":
                 continue
             val = c[10:]
             if val.lstrip().startswith("'"):
-                v = val.lstrip()[1:]
-                out, j = "", 0
-                while j < len(v):
-                    if v[j] == "'":
-                        if j + 1 < len(v) and v[j + 1] == "'":
-                            out += "'"
-                            j += 2
-                            continue
-                        break
-                    out += v[j]
-                    j += 1
-                cards[key] = out.rstrip()
+                cards[key] = _quoted(val.lstrip()[1:])
             else:
                 v = val.split("/")[0].strip()
                 if v in ("T", "F"):
@@ -194,3 +228,63 @@ def read_fits(path):
             data = None
         hdus.append((hdr, data))
     return hdus
+
+
+# ------------------------------------------------------------------------------
+# SED grid files in the reference's FITS layout (physicsmodel/helpers/gridbackends.py:151-177
+# write, 345-365 read): primary HDU = wavelengths, IMAGE "seds" (n_models x n_bands), optional
+# IMAGE "covdiag" / "covoffdiag", BINTABLE "grid" with one column per model property and the
+# filter names in its header keyword FILTERS (space separated).
+class FitsSEDGrid:
+    """what the fit touches of a SEDGrid (fit.py:396-463), read from a FITS grid file"""
+
+    def __init__(self, lamb, seds, cols, filters, cov_diag=None, cov_offdiag=None, header=None):
+        self.lamb = np.asarray(lamb, dtype=float)
+        self.seds = np.asarray(seds, dtype=float)
+        self._cols = dict(cols)
+        self.filters = list(filters) if filters is not None else None
+        self.cov_diag, self.cov_offdiag = cov_diag, cov_offdiag
+        self.header = dict(header or {})
+
+    def keys(self):
+        return list(self._cols.keys())
+
+    def __getitem__(self, name):
+        return self._cols[name]
+
+    def __contains__(self, name):
+        return name in self._cols
+
+    def __len__(self):
+        return self.seds.shape[0]
+
+
+def read_sedgrid_fits(path):
+    """read a SED grid written by the reference's ``writeFITS`` (or by ``write_sedgrid_fits``)"""
+    hdus = read_fits(path)
+    by_name = {str(h.get("EXTNAME", "")).strip().lower(): (h, d) for h, d in hdus[1:]}
+    if "seds" not in by_name or "grid" not in by_name:
+        raise ValueError("%s is not a SED grid in the seds/grid FITS layout" % path)
+    ghdr, gtab = by_name["grid"]
+    filters = str(ghdr["FILTERS"]).split() if "FILTERS" in ghdr else None
+    return FitsSEDGrid(hdus[0][1], by_name["seds"][1], gtab, filters,
+                       by_name.get("covdiag", (None, None))[1], by_name.get("covoffdiag", (None, None))[1],
+                       {k: v for k, v in ghdr.items()})
+
+
+def write_sedgrid_fits(path, grid):
+    """write ``grid`` (lamb, seds, keys()/[name], filters) in the same layout"""
+    with open(path, "wb") as f:
+        lamb = np.asarray(grid.lamb, dtype=np.float64)
+        f.write(_header_bytes(_image_cards(lamb, True)))
+        f.write(_pad_data(lamb.astype(">f8").tobytes()))
+        images = [("seds", grid.seds)]
+        for name in ("cov_diag", "cov_offdiag"):
+            if getattr(grid, name, None) is not None:
+                images.append((name.replace("_", ""), getattr(grid, name)))
+        for name, arr in images:
+            arr = np.asarray(arr, dtype=np.float64)
+            f.write(_header_bytes(_image_cards(arr, False) + [_card("EXTNAME", name, "extension name")]))
+            f.write(_pad_data(arr.astype(">f8").tobytes()))
+        extra = {"FILTERS": " ".join(grid.filters)} if getattr(grid, "filters", None) else None
+        f.write(_table_hdu({k: grid[k] for k in grid.keys()}, extname="grid", extra=extra))
