@@ -120,17 +120,20 @@ def save_pdf2d(pdf2d_outname, save_pdf2d_vals, qname_pairs):
 
 def _lnp_backend():
     try:
-        import tables  # noqa: F401
+        import tables
 
-        return "tables"
+        if callable(getattr(tables, "open_file", None)) and hasattr(tables, "__version__"):
+            return "tables"
     except Exception:
         pass
     try:
-        import h5py  # noqa: F401
+        import h5py
 
-        return "h5py"
+        if hasattr(h5py, "File") and hasattr(h5py, "__version__"):
+            return "h5py"
     except Exception:
-        return "npz"
+        pass
+    return "npz"
 
 
 def _lnp_create(lnp_outname, grid_waves, obs_filters):

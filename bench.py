@@ -144,6 +144,45 @@ def _cpu_worker(args):
     return time.perf_counter() - t
 
 
+def _ref_worker(args):
+    lo, hi, block = args
+    from oracle import ref_shim
+
+    return ref_shim.time_reference_star_loop(_CPU["flux"][lo:hi], _CPU["g"], _CPU["nz"], _CPU["keys"],
+                                             block, THRESHOLD, _CPU["max_nbins"])
+
+
+def cpu_reference_itself(g, nz, obs, max_nbins, stars_per_core, steps, warmup):
+    """time the star loop of the UNMODIFIED reference (its files under oracle/_ref, or the tree
+    at /root/reference) on all host cores: one process per core runs ``Q_all_memory`` once over
+    its own stars; the loop is timed block by block from inside (oracle/ref_shim.py), so the
+    setup of the bins is outside the timed region, as for the GPU arm."""
+    import multiprocessing as mp
+
+    from oracle import fit_oracle as fo
+    from oracle import ref_shim
+
+    if not ref_shim.reference_available():
+        raise RuntimeError("no reference files (oracle/_ref is built by oracle/make_ref.py)")
+    cores = len(os.sched_getaffinity(0))
+    per = (warmup + steps) * stars_per_core
+    if len(obs) < cores * per:
+        raise RuntimeError("catalog too small for the CPU sample")
+    _CPU.update(g=g, nz=nz, keys=fo.default_keys(g), flux=obs.fluxes, max_nbins=max_nbins)
+    nm = int(np.count_nonzero(g["weight"] > 0))
+    ctx = mp.get_context("fork")
+    with ctx.Pool(cores) as pool:
+        blocks = pool.map(_ref_worker, [(c * per, (c + 1) * per, stars_per_core) for c in range(cores)])
+    rates = []
+    for it in range(warmup, warmup + steps):
+        dt = max(float(b[it]) for b in blocks)  # the step ends when the slowest core is done
+        rates.append((cores * stars_per_core * nm / dt, dt))
+    sample = ("%d stars (%d per core x %d cores) of the same catalog against the full %d-model grid per step, "
+              "fitted by the reference's own Q_all_memory (star loop timed from inside, setup excluded)"
+              % (cores * stars_per_core, stars_per_core, cores, nm))
+    return rates, cores, sample, "reference"
+
+
 def cpu_reference_run(g, nz, obs, max_nbins, stars_per_core, steps, warmup):
     """time the oracle's faithful star loop on all host cores; returns (evals/s per step list,
     cores, sample description).  Setup (bins, index lists) is outside the timed region."""
@@ -151,6 +190,10 @@ def cpu_reference_run(g, nz, obs, max_nbins, stars_per_core, steps, warmup):
 
     from oracle import fit_oracle as fo
 
+    try:  # the reference itself where its files are at hand, else the port
+        return cpu_reference_itself(g, nz, obs, max_nbins, stars_per_core, steps, warmup)
+    except Exception as exc:
+        sys.stderr.write("bench: reference files not usable (%r), timing the port\n" % (exc,))
     cores = len(os.sched_getaffinity(0))
     keys = fo.default_keys(g)
     st = fo.OracleSetup(g, nz, keys, max_nbins=max_nbins)
@@ -298,6 +341,8 @@ def run_ours(args, rank, world, local_rank):
     e2e_stars = stars
     if args.pdf2d:  # 2D PDFs of a whole catalog do not fit host memory (1 MB per star)
         e2e_stars = min(stars, 16384)
+    # the result arrays are page-locked host memory: at most ~16 GB of 1D PDFs per call
+    e2e_stars = int(min(e2e_stars, max(1024, (16 << 30) // (setup.total_bins * 8))))
     e2e_obs = obs if e2e_stars == stars else obs.subset(slice(0, e2e_stars))
     eng.reuse_buffers = True  # page-locked result arrays are kept across calls (not re-pinned)
     qkw = dict(p=[16.0, 50.0, 84.0], max_nbins=args.max_nbins, lnp_npts=LNP_NPTS, threshold=THRESHOLD,

@@ -27,6 +27,11 @@ import types
 import numpy as np
 
 REFERENCE_ROOT = os.environ.get("BEAST_REFERENCE_ROOT", "/root/reference")
+if not os.path.isfile(os.path.join(REFERENCE_ROOT, "beast", "fitting", "fit.py")):
+    # the GPU box: the files oracle/make_ref.py took from the reference tree
+    _vendored = os.path.join(os.path.dirname(os.path.abspath(__file__)), "_ref")
+    if os.path.isfile(os.path.join(_vendored, "beast", "fitting", "fit.py")):
+        REFERENCE_ROOT = _vendored
 
 
 def reference_available():
@@ -486,3 +491,44 @@ def run_reference_merge_stats(tables_by_name, filters_tab=None, reorder_tag_list
         fmod.__dict__.update(saved_f)
         sys.modules.pop("beast.tools.merge_beast_stats", None)
     return n, captured["hdus"]
+
+
+class _TimedObs:
+    """duck-typed observations whose ``enumobs`` notes the time whenever the reference's star
+    loop asks for the first star of a block: the loop (fit.py:637-762) is then timed block by
+    block from inside the unmodified ``Q_all_memory``, setup excluded"""
+
+    def __init__(self, fluxes, filters, block):
+        self.fluxes, self.filters, self.block, self.marks = fluxes, list(filters), block, []
+
+    def __len__(self):
+        return len(self.fluxes)
+
+    def getFilters(self):
+        return self.filters
+
+    def enumobs(self):
+        import time
+
+        for k in range(len(self.fluxes)):
+            if k % self.block == 0:
+                self.marks.append(time.perf_counter())
+            yield k, self.fluxes[k].copy()
+        self.marks.append(time.perf_counter())
+
+
+def time_reference_star_loop(fluxes, sedgrid, obsmodel, qnames, block, threshold=-10.0, max_nbins=200):
+    """run the unmodified reference ``Q_all_memory`` once over ``fluxes`` and return the seconds
+    its star loop spent on every block of ``block`` stars (writers replaced by no-ops)"""
+    fit = load_reference_fit()
+    obs = _TimedObs(fluxes, sedgrid.filters, block)
+    saved = (fit.save_stats, fit.save_pdf1d, fit.save_pdf2d, fit.save_lnp)
+    fit.save_stats = fit.save_pdf1d = fit.save_pdf2d = fit.save_lnp = lambda *a, **k: None
+    try:
+        with contextlib.redirect_stdout(io.StringIO()), contextlib.redirect_stderr(io.StringIO()):
+            fit.Q_all_memory({}, obs, sedgrid, obsmodel, list(qnames), p=[16.0, 50.0, 84.0],
+                             max_nbins=max_nbins, stats_outname="none", pdf1d_outname="none",
+                             lnp_outname=None, threshold=threshold)
+    finally:
+        fit.save_stats, fit.save_pdf1d, fit.save_pdf2d, fit.save_lnp = saved
+    return list(np.diff(obs.marks))

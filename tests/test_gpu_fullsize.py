@@ -137,3 +137,49 @@ def test_full_size_split_and_legacy_kernels_agree(c2):
         a, b = setup.bin_off[k], setup.bin_off[k + 1]
         width = util.bin_width_tolerance(setup.bin_val[a:b])
         assert np.all(np.abs(res.per_vals[:, k, :] - alt.per_vals[:, k, :]) <= width), k
+
+
+def test_c4_size_with_pdf2d_over_several_ranges():
+    """BASELINE.json configs[3] shape: 1e7 models x 8 bands, 38 parameters, 2D PDFs of three
+    parameters; the scratch is kept small so that the sparse pass (and bf_pdf2d_from_weights with
+    it) runs over several ranges of stars.  Six stars against the oracle, all 48 for consistency."""
+    from beast_b200 import synth
+    from beast_b200.engine import FitEngine
+    from beast_b200.gridprep import FitSetup
+    from oracle import fit_oracle as fo
+
+    g = synth.make_sedgrid("C4", synth.UVNIR_FILTERS, synth.UVNIR_LAMB, seed=1234)
+    nz = synth.make_noisemodel(g)
+    obs = synth.make_observations(g, nz, 48, seed=77, with_coords=False)
+    keys = fo.default_keys(g)
+    p2d = ["Av", "M_ini", "logT"]
+    with warnings.catch_warnings():
+        warnings.simplefilter("ignore")
+        setup = FitSetup(g, nz, list(keys), max_nbins=200, pdf2d_param_list=p2d, make_pdf2d=True)
+    assert setup.n_models == 10_000_000 and setup.nb == 8 and setup.n_q == 38 and len(setup.pairs) == 3
+    eng = FitEngine(setup, scratch_budget_bytes=3 << 30)
+    assert eng.split and setup.fast_pad == 32  # 19 fast parameters: one chunk per instruction
+    res = eng.fit(obs.fluxes, threshold=-10.0, want_pdf2d=True, sparse="all")
+    n_list = int(eng.last_state[1].n_list)
+    per_entry = 64 * 8 + 24 + 4 + 128 + 64 + 8 * 32
+    assert n_list * per_entry > 1.2 * (3 << 30), "the lists fit one range: lower the scratch budget"
+    pick = [0, 7, 13, 21, 34, 47]
+    ost = fo.OracleSetup(g, nz, keys, max_nbins=200, pdf2d_param_list=p2d)
+    want = fo.fit_all(obs.fluxes[pick], ost, -10.0, fast=True)
+
+    class Sub:
+        pass
+
+    sub = Sub()
+    for name in ("Pmax", "Pmax_j", "total_log_norm", "chi2min", "chi2min_j", "exp_vals", "pdf1d", "per_vals",
+                 "pdf2d"):
+        setattr(sub, name, getattr(res, name)[pick])
+    util.compare_to_reference(setup, sub, want, n_pdf2d=3)
+    np.testing.assert_array_equal(res.n_sparse[pick], [len(s[0]) for s in want["sparse"]])
+    for i, e in enumerate(pick):
+        a, b = res.sparse_off[e], res.sparse_off[e + 1]
+        np.testing.assert_array_equal(setup.g0_indxs[res.sparse_j[a:b]], want["sparse"][i][0])
+    # every 2D PDF is a normalised histogram of the same weights as the 1D ones
+    for k, pr in enumerate(setup.pairs):
+        blk = res.pdf2d[:, setup.pair_off[k]:setup.pair_off[k + 1]]
+        np.testing.assert_allclose(blk.sum(axis=1), 1.0, rtol=0, atol=1e-9)
