@@ -164,7 +164,7 @@ def test_c4_size_with_pdf2d_over_several_ranges():
     per_entry = 64 * 8 + 24 + 4 + 128 + 64 + 8 * 32
     assert n_list * per_entry > 1.2 * (3 << 30), "the lists fit one range: lower the scratch budget"
     pick = [0, 7, 13, 21, 34, 47]
-    ost = fo.OracleSetup(g, nz, keys, max_nbins=200, pdf2d_param_list=p2d)
+    ost = fo.OracleSetup(g, nz, keys, max_nbins=200, pdf2d_param_list=p2d, make_pdf2d=True)
     want = fo.fit_all(obs.fluxes[pick], ost, -10.0, fast=True)
 
     class Sub:
