@@ -138,6 +138,7 @@ class FitState(C.Structure):
         ("n_records", i64),
         ("launches", i64),
         ("split", C.c_int),
+        ("n_ranges", C.c_int),
         ("want_timing", C.c_int),
         ("stage_ms", C.c_float * 12),
     ]

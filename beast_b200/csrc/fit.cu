@@ -412,7 +412,9 @@ extern "C" int bf_fit_batch(const bf_fit_plan* plan, int64_t n_stars, const doub
   bf_star_outputs so = {s_tln, s_chi2, s_chi2_j, s_nsp, s_exp, s_pdf, s_per, mask, prefix};
   listed_keys_kernel<<<blocks_for(n), kT, 0, st>>>(n, n_listed, okeys);
   launches += 1;
+  int n_ranges = 0;
   for (int64_t a0 = 0; a0 < n;) {
+    ++n_ranges;
     int64_t b0 = a0 + 1;
     while (b0 < n && static_cast<int64_t>(off_host[b0 + 1]) - off_host[a0] <= max_entries) ++b0;
     const int64_t base = off_host[a0], cnt = static_cast<int64_t>(off_host[b0]) - off_host[a0];
@@ -514,6 +516,7 @@ extern "C" int bf_fit_batch(const bf_fit_plan* plan, int64_t n_stars, const doub
     state->n_list = total;
     state->launches = launches;
     state->split = split ? 1 : 0;
+    state->n_ranges = n_ranges;
   }
 #undef BF_WS
   return BF_OK;

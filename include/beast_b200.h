@@ -418,6 +418,7 @@ typedef struct {
   int64_t n_records;              /* sparse records wanted when sparse_capacity was too small */
   int64_t launches;               /* kernels launched by the call */
   int split;                      /* 1: the class-split kernels ran */
+  int n_ranges;                   /* ranges of stars the sparse pass was cut into */
   int want_timing;                /* in: 1 = fill stage_ms (the call then synchronises the stream
                                      after every stage; for measurements) */
   float stage_ms[12];             /* device time per stage: presort, dense, select, exact_max,

@@ -157,12 +157,10 @@ def test_c4_size_with_pdf2d_over_several_ranges():
         warnings.simplefilter("ignore")
         setup = FitSetup(g, nz, list(keys), max_nbins=200, pdf2d_param_list=p2d, make_pdf2d=True)
     assert setup.n_models == 10_000_000 and setup.nb == 8 and setup.n_q == 38 and len(setup.pairs) == 3
-    eng = FitEngine(setup, scratch_budget_bytes=3 << 30)
+    eng = FitEngine(setup, scratch_budget_bytes=40 << 20)
     assert eng.split and setup.fast_pad == 32  # 19 fast parameters: one chunk per instruction
     res = eng.fit(obs.fluxes, threshold=-10.0, want_pdf2d=True, sparse="all")
-    n_list = int(eng.last_state[1].n_list)
-    per_entry = 64 * 8 + 24 + 4 + 128 + 64 + 8 * 32
-    assert n_list * per_entry > 1.2 * (3 << 30), "the lists fit one range: lower the scratch budget"
+    assert eng.last_state[1].n_ranges >= 3, "the lists fit one range: lower the scratch budget"
     pick = [0, 7, 13, 21, 34, 47]
     ost = fo.OracleSetup(g, nz, keys, max_nbins=200, pdf2d_param_list=p2d, make_pdf2d=True)
     want = fo.fit_all(obs.fluxes[pick], ost, -10.0, fast=True)
