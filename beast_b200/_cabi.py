@@ -115,6 +115,7 @@ class FitPlan(C.Structure):
         ("pair_len", i64),
         ("sm_count", C.c_int),
         ("force_legacy", C.c_int),
+        ("max_range_entries", i64),
     ]
 
 

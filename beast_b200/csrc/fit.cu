@@ -394,6 +394,8 @@ extern "C" int bf_fit_batch(const bf_fit_plan* plan, int64_t n_stars, const doub
               workspace_bytes, static_cast<long long>(max_entries), static_cast<long long>(longest));
     return BF_ERR_TOO_LARGE;
   }
+  if (p.max_range_entries > 0 && max_entries > p.max_range_entries)
+    max_entries = p.max_range_entries > longest ? p.max_range_entries : longest;
   if (max_entries > total) max_entries = tot1;
   bf_accum_scratch scr = {};
   scr.weights = ar.take<double>(static_cast<size_t>(max_entries) * BF_GROUP);

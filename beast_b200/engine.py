@@ -182,6 +182,7 @@ class FitEngine:
             p.pair_bin, p.pair_off = self.d_pair_bin.data_ptr(), self.d_pair_off.data_ptr()
         p.sm_count = self.sm_count
         p.force_legacy = int(self.force_legacy or not self.split)
+        p.max_range_entries = int(getattr(self, "max_range_entries", 0))
         return p
 
     def _workspace_for(self, plan, n):

@@ -353,6 +353,8 @@ int bf_pdf2d_from_weights(int64_t ld_model, int n_pairs, const int32_t* pair_bin
  *   inv_band_scale [nb] : 1 / s_b (device), turns flux64 into the FP32 fluxes of the dense pass
  *   pair_bin / pair_off / pair_len : 2D PDF tables (bf_pdf2d_accumulate), pair_len = pair_off[n_pairs]
  *   force_legacy  : 1 = do not use the class-split kernels even if `params` carries the split
+ *   max_range_entries : the sparse pass works on ranges of stars whose lists fit the scratch;
+ *                   this caps a range further (0 = no cap; a star's own list is never cut)
  * flux64  : [n_stars][nb] observed fluxes, device memory, or host memory with flux_on_host = 1
  * percentiles_host : [3] host doubles, in percent
  * sparse_mode : 0 no sparse records; 1 all members of every star's sparse set (ascending model
@@ -385,6 +387,7 @@ typedef struct {
   int64_t pair_len;
   int sm_count;
   int force_legacy;
+  int64_t max_range_entries; /* 0, or a cap on the listed groups the sparse pass takes at a time */
 } bf_fit_plan;
 
 typedef struct {

@@ -157,7 +157,8 @@ def test_c4_size_with_pdf2d_over_several_ranges():
         warnings.simplefilter("ignore")
         setup = FitSetup(g, nz, list(keys), max_nbins=200, pdf2d_param_list=p2d, make_pdf2d=True)
     assert setup.n_models == 10_000_000 and setup.nb == 8 and setup.n_q == 38 and len(setup.pairs) == 3
-    eng = FitEngine(setup, scratch_budget_bytes=40 << 20)
+    eng = FitEngine(setup, scratch_budget_bytes=1 << 30)
+    eng.max_range_entries = 30000  # (48 stars list about 110,000 groups)
     assert eng.split and setup.fast_pad == 32  # 19 fast parameters: one chunk per instruction
     res = eng.fit(obs.fluxes, threshold=-10.0, want_pdf2d=True, sparse="all")
     assert eng.last_state[1].n_ranges >= 3, "the lists fit one range: lower the scratch budget"
