@@ -602,13 +602,17 @@ def run_c5(args, rank, world, local_rank):
             dist.barrier()
         torch.cuda.synchronize(dev)
 
-    def step(host_out=None):
+    def step(host_out=None, upto=None):
+        pos = 0
         for a, b in batches:
+            if upto is not None and a >= upto:
+                break
             m = sf.fit_batch(fl[a:b] if host_out is None else fluxes[a:b], THRESHOLD)
-            if host_out is not None:
+            if host_out is not None:  # this rank's share of the batch's merged rows
                 lo, hi = m["rows"]
                 for name in ("pdf1d", "per_vals", "exp_vals", "best_vals", "Pmax", "total_log_norm", "chi2min"):
-                    host_out[name][a + lo:a + hi].copy_(m[name], non_blocking=True)
+                    host_out[name][pos:pos + hi - lo].copy_(m[name], non_blocking=True)
+                pos += hi - lo
 
     sampler = ClockSampler(local_rank)
     sampler.recording = False
@@ -652,17 +656,22 @@ def run_c5(args, rank, world, local_rank):
             stage_tot[k] = stage_tot.get(k, 0.0) + v
     # end to end: host fluxes in, this rank's share of the merged rows back on the host
     st0 = engines[0].setup
-    host = {"pdf1d": torch.empty((stars, st0.total_bins), dtype=torch.float64, pin_memory=True),
-            "per_vals": torch.empty((stars, st0.n_q, 3), dtype=torch.float64, pin_memory=True)}
+    # (page-locked result arrays for this rank's share: at most ~16 GB, i.e. whole batches of stars)
+    cap_rows = max(1, (16 << 30) // (st0.total_bins * 8))
+    e2e_batches = max(1, min(len(batches), cap_rows * world // bs))
+    e2e_stars = min(stars, batches[e2e_batches - 1][1])
+    rows = sum(-(-(b - a) // world) for a, b in batches[:e2e_batches])
+    host = {"pdf1d": torch.empty((rows, st0.total_bins), dtype=torch.float64, pin_memory=True),
+            "per_vals": torch.empty((rows, st0.n_q, 3), dtype=torch.float64, pin_memory=True)}
     for name in ("exp_vals", "best_vals"):
-        host[name] = torch.empty((stars, st0.n_q), dtype=torch.float64, pin_memory=True)
+        host[name] = torch.empty((rows, st0.n_q), dtype=torch.float64, pin_memory=True)
     for name in ("Pmax", "total_log_norm", "chi2min"):
-        host[name] = torch.empty(stars, dtype=torch.float64, pin_memory=True)
-    step(host)
+        host[name] = torch.empty(rows, dtype=torch.float64, pin_memory=True)
+    step(host, e2e_stars)
     barrier()
     t0 = time.perf_counter()
     for _ in range(args.steps):
-        step(host)
+        step(host, e2e_stars)
     barrier()
     e2e_s = (time.perf_counter() - t0) / args.steps
     t = torch.tensor([e2e_s], dtype=torch.float64, device=dev)
@@ -689,9 +698,11 @@ def run_c5(args, rank, world, local_rank):
                    "per-batch all_gather + reduce_scatter by star",
                    "l2": "inputs larger than L2"},
         "clocks": sampler.summary(),
-        "e2e": {"value": stars * n_models / e2e_s, "unit": "star*model/s", "seconds_per_step": e2e_s,
-                "h2d_bytes_per_step": int(fluxes.nbytes),
-                "d2h_bytes_per_step": int(share * (st0.total_bins + 5 * st0.n_q + 3) * 8)},
+        "e2e": {"value": e2e_stars * n_models / e2e_s, "unit": "star*model/s", "seconds_per_step": e2e_s,
+                "stars": e2e_stars, "h2d_bytes_per_step": int(fluxes[:e2e_stars].nbytes),
+                "d2h_bytes_per_step": int(rows * (st0.total_bins + 5 * st0.n_q + 3) * 8),
+                "call": "SubgridFit.fit_batch per batch: host fluxes in, this rank's share of the merged rows "
+                        "(pdf1d, percentiles, expectations, best values, Pmax, total_log_norm, chi2min) back on the host"},
         "gpu_launches": int(launches),
         "collective": {"payload_bytes_per_step_per_rank": int(coll_bytes), "ms_per_step": coll_ms,
                        "bus_gbs": (coll_bytes * (world - 1) / world / (coll_ms * 1e-3) / 1e9) if coll_ms and world > 1 else None,
