@@ -488,8 +488,8 @@ __device__ __forceinline__ void fast_consume(uint32_t row_bytes, uint32_t bin_of
   }
 }
 
-// A warp without a private copy fills the rings, one step of all fast warps at a time (lane <->
-// fast warp; the warps of this kind take the steps in turn).  A lane waits until the fast warp has released the stage (round r-1 of it), announces
+// A warp without a private copy fills the rings of its share of the fast warps (lane <-> fast
+// warp), one step at a time.  A lane waits until the fast warp has released the stage (round r-1 of it), announces
 // the bytes on the "full" mbarrier and issues one bulk copy per row.  A slot past the end of the
 // list gets zero weights and the last chunk's bins.
 template <int SLOTS>
@@ -502,10 +502,12 @@ __device__ __forceinline__ void fast_produce(const bf_param_tables& prm, const d
   const uint32_t slot_bytes = 64u + row_bytes;
   const uint32_t step = nfw * SLOTS;
   const uint32_t n_steps_max = (n_mc + step - 1) / step;  // steps of fast warp 0
-  // all lanes of an iteration work on the same step (lane <-> fast warp): a lane then only waits
-  // for stages that earlier iterations filled
-  const uint32_t f = static_cast<uint32_t>(lane);
-  for (uint32_t t = first; t < n_steps_max; t += n_prod) {
+  // Every fast warp is served by one lane of one producer warp, step after step: the stages of a
+  // ring are then filled in order, which is what the parity of its mbarriers can tell apart.  All
+  // lanes of an iteration work on the same step, so a lane only waits for stages that earlier
+  // iterations filled.
+  const uint32_t f = first + static_cast<uint32_t>(lane) * n_prod;
+  for (uint32_t t = 0; t < n_steps_max; ++t) {
     const uint32_t base = f * SLOTS + t * step;
     if (f >= nfw || base >= n_mc) continue;  // no such fast warp / it has fewer steps
     const uint32_t stage = t % kRingStages, round = t / kRingStages;
