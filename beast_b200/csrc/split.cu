@@ -372,7 +372,7 @@ constexpr int kSplitInts = 3 * 64 + 2 * 64 + 128 + 64 + 16;
 // that the warps without a private copy issue (8 weights + the bin bytes of every chunk slot),
 // one "full" and one "empty" mbarrier per (fast warp, stage).  The rings sit behind the private
 // copies in the histogram area (1.5 KB per fast warp).
-constexpr int kRingStages = 4;
+constexpr int kRingStages = 6;
 constexpr int kRingStageBytes = 384;  // 2 slots x (64 B weights + 128 B bins) or 1 x (64 + 256)
 constexpr int kRingDoubles = kRingStages * kRingStageBytes / 8;  // per fast warp
 struct SplitSmem {
@@ -507,9 +507,30 @@ __device__ __forceinline__ void fast_produce(const bf_param_tables& prm, const d
   // lanes of an iteration work on the same step, so a lane only waits for stages that earlier
   // iterations filled.
   const uint32_t f = first + static_cast<uint32_t>(lane) * n_prod;
+  if (f >= nfw) return;
+  // chunk references three steps ahead of the copies that need them as addresses
+  constexpr int kAhead = 3;
+  uint2 rq[kAhead][SLOTS];
+  auto fetch = [&](uint32_t t, uint2* r) {
+#pragma unroll
+    for (int sl = 0; sl < SLOTS; ++sl) {
+      const uint32_t i = f * SLOTS + t * step + sl;
+      r[sl] = refs[i < n_mc ? i : n_mc - 1];
+    }
+  };
+#pragma unroll
+  for (int a = 0; a < kAhead; ++a) fetch(a, rq[a]);
   for (uint32_t t = 0; t < n_steps_max; ++t) {
+    uint2 cur[SLOTS];
+#pragma unroll
+    for (int sl = 0; sl < SLOTS; ++sl) cur[sl] = rq[0][sl];
+#pragma unroll
+    for (int a = 0; a + 1 < kAhead; ++a)
+#pragma unroll
+      for (int sl = 0; sl < SLOTS; ++sl) rq[a][sl] = rq[a + 1][sl];
+    fetch(t + kAhead, rq[kAhead - 1]);
     const uint32_t base = f * SLOTS + t * step;
-    if (f >= nfw || base >= n_mc) continue;  // no such fast warp / it has fewer steps
+    if (base >= n_mc) break;  // this fast warp has no more steps
     const uint32_t stage = t % kRingStages, round = t / kRingStages;
     uint64_t* full = full_all + f * kRingStages + stage;
     if (round > 0) mbar_wait(empty_all + f * kRingStages + stage, (round - 1) & 1u);
@@ -517,13 +538,11 @@ __device__ __forceinline__ void fast_produce(const bf_param_tables& prm, const d
     mbar_expect_tx(full, SLOTS * slot_bytes);
 #pragma unroll
     for (int sl = 0; sl < SLOTS; ++sl) {
-      const uint32_t i = base + sl;
-      const bool valid = i < n_mc;
-      const uint2 ref = refs[valid ? i : n_mc - 1];
-      const void* wsrc = valid ? static_cast<const void*>(weights + static_cast<size_t>(ref.y) * BF_CHUNK)
+      const bool valid = base + sl < n_mc;
+      const void* wsrc = valid ? static_cast<const void*>(weights + static_cast<size_t>(cur[sl].y) * BF_CHUNK)
                                : static_cast<const void*>(g_zero_weights);
       tma_load_1d(dst + sl * slot_bytes, wsrc, 64, full);
-      tma_load_1d(dst + sl * slot_bytes + 64, prm.fast_bin + static_cast<size_t>(ref.x) * row_bytes, row_bytes, full);
+      tma_load_1d(dst + sl * slot_bytes + 64, prm.fast_bin + static_cast<size_t>(cur[sl].x) * row_bytes, row_bytes, full);
     }
   }
 }
