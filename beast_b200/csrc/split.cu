@@ -368,17 +368,16 @@ constexpr uint32_t kSegmentChunks = 16384;
 // shared memory: hist [hist_doubles] | red [2 NW] | redj [NW] | sscan (NW u32, as NW/2 doubles)
 //   | epart [NW][32] | int tables (see kernel); sized for the largest block
 constexpr int kSplitInts = 3 * 64 + 2 * 64 + 128 + 64 + 16;
-// Row ring of the fast warps: kRingStages steps of rows per fast warp, filled by TMA bulk copies
-// that the warps without a private copy issue (8 weights + the bin bytes of every chunk slot),
-// one "full" and one "empty" mbarrier per (fast warp, stage).  The rings sit behind the private
-// copies in the histogram area (1.5 KB per fast warp).
+// Row ring of a fast warp: kRingStages steps of rows (8 weights + the bin bytes of every chunk
+// slot), filled by the warp's own cp.async copies.  The rings sit behind the private copies in the
+// histogram area (2.3 KB per fast warp).
 constexpr int kRingStages = 6;
 constexpr int kRingStageBytes = 384;  // 2 slots x (64 B weights + 128 B bins) or 1 x (64 + 256)
 constexpr int kRingDoubles = kRingStages * kRingStageBytes / 8;  // per fast warp
 struct SplitSmem {
   static __host__ __device__ size_t bytes(int hist_doubles) {
     return (static_cast<size_t>(hist_doubles) + 4 * kSplitWarpsMax + kSplitWarpsMax * 32 + 64) * sizeof(double) +
-           static_cast<size_t>(kSplitWarpsMax) * kRingStages * 16 + kSplitInts * sizeof(int);
+           kSplitInts * sizeof(int);
   }
 };
 
@@ -453,28 +452,72 @@ __device__ __forceinline__ void add_chunk(uint32_t col_s, const FastRows& r) {
 }
 
 // A fast warp: chunks first*SLOTS + h, then every nfw*SLOTS-th, of the star's member chunks.
-// Its rows (8 weights and the bin bytes of each chunk slot) arrive in its ring in shared memory:
-// warps without a private copy issue the TMA bulk copies (fast_producer below), the fast warp
-// waits for a stage's "full" mbarrier, reads the rows with shared-memory latency, updates its
-// columns and hands the stage back through the "empty" mbarrier.  bin_off = byte offset of
-// this lane's bins inside a slot's rows, bin_mask = 0 for a lane without a parameter (it then
-// adds into the one-bin column it owns).
+// The rows of a step (8 weights + the bin bytes of every chunk slot: 384 B) are copied into the
+// warp's own ring in shared memory by one cp.async instruction (SASS LDGSTS: 24 lanes x 16 B, each
+// with its own source address) kRingStages-1 steps before they are used, so the accumulation reads
+// them with shared-memory latency and no register holds a row in flight.  The chunk references
+// the copies need as addresses are requested three steps earlier still, in registers.
+// bin_off = byte offset of this lane's bins inside a slot's rows, bin_mask = 0 for a lane without
+// a parameter (it then adds into the one-bin column it owns).  A slot past the end of the list
+// gets zero weights and the last chunk's bins.
+// (A ring filled by TMA bulk copies from the warps without a private copy, with full / empty
+// mbarriers per stage, was built and measured: 43 / 27 / 18 ms for the three ranges of a batch
+// against 29 / 16 / 9 -- four bulk copies of 64..128 B per step and fast warp are too many small
+// requests for one or two producer warps to issue.)
 template <int SLOTS>
-__device__ __forceinline__ void fast_consume(uint32_t row_bytes, uint32_t bin_off, uint32_t bin_mask,
-                                             uint32_t n_mc, uint32_t first, uint32_t nfw, int lane,
-                                             double* col, const unsigned char* ring, uint64_t* full,
-                                             uint64_t* empty) {
+__device__ __forceinline__ void fast_accumulate(const bf_param_tables& prm, const double* __restrict__ weights,
+                                                const uint2* refs, uint32_t n_mc, uint32_t first,
+                                                uint32_t nfw, uint32_t bin_off, uint32_t bin_mask, int lane,
+                                                double* col, unsigned char* ring) {
   const uint32_t h = SLOTS == 2 ? static_cast<uint32_t>(lane >> 4) : 0u;
   const uint32_t step = nfw * SLOTS;
   const uint32_t col_s = static_cast<uint32_t>(__cvta_generic_to_shared(col));
   const uint32_t start = first * SLOTS;
   if (start >= n_mc) return;
   const uint32_t n_steps = (n_mc - start + step - 1) / step;
+  const uint32_t row_bytes = static_cast<uint32_t>(prm.fast_pad) * BF_CHUNK;
   const uint32_t slot_bytes = 64u + row_bytes;
+  // copy role of this lane: piece q (16 B) of chunk slot cslot
+  const uint32_t pieces = slot_bytes / 16;
+  const uint32_t cslot = static_cast<uint32_t>(lane) / pieces, q = static_cast<uint32_t>(lane) % pieces;
+  const bool copier = cslot < static_cast<uint32_t>(SLOTS);
+  const uint32_t ring_s = static_cast<uint32_t>(__cvta_generic_to_shared(ring)) + cslot * slot_bytes + q * 16;
+  const unsigned char* wbase = reinterpret_cast<const unsigned char*>(weights) + q * 16;
+  const unsigned char* bbase = prm.fast_bin + (q - 4) * 16;
+  const unsigned char* zbase = reinterpret_cast<const unsigned char*>(g_zero_weights) + (q & 3) * 16;
+  const uint32_t last = n_mc - 1;
+  auto fetch_ref = [&](uint32_t t, bool& valid) {  // reference of step t for this lane's copy slot
+    const uint32_t i = start + t * step + (copier ? cslot : 0u);
+    valid = i <= last;
+    return refs[valid ? i : last];
+  };
+  auto issue = [&](uint32_t t, uint2 ref, bool valid) {  // rows of step t -> stage t % kRingStages
+    if (copier && t < n_steps) {
+      const unsigned char* src = q < 4 ? (valid ? wbase + static_cast<size_t>(ref.y) * 64 : zbase)
+                                       : bbase + static_cast<size_t>(ref.x) * row_bytes;
+      asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(ring_s + (t % kRingStages) * kRingStageBytes),
+                   "l"(src));
+    }
+    asm volatile("cp.async.commit_group;" ::: "memory");
+  };
+  // references: r0 is the one of the step issued next, r1 / r2 follow
+  bool v0, v1, v2;
+  uint2 r0 = fetch_ref(0, v0), r1 = fetch_ref(1, v1), r2 = fetch_ref(2, v2);
+  uint32_t t_issue = 0;
+  auto issue_next = [&]() {
+    issue(t_issue, r0, v0);
+    r0 = r1; v0 = v1;
+    r1 = r2; v1 = v2;
+    r2 = fetch_ref(t_issue + 3, v2);
+    ++t_issue;
+  };
+#pragma unroll 1
+  for (int a = 0; a < kRingStages - 1; ++a) issue_next();
   for (uint32_t t = 0; t < n_steps; ++t) {
-    const uint32_t stage = t % kRingStages;
-    mbar_wait(full + stage, (t / kRingStages) & 1u);
-    const unsigned char* rows = ring + stage * kRingStageBytes + h * slot_bytes;
+    issue_next();  // step t + kRingStages - 1 (an empty group past the end keeps the count)
+    asm volatile("cp.async.wait_group %0;" ::"n"(kRingStages - 1) : "memory");
+    __syncwarp();  // the copies of all lanes for step t have landed
+    const unsigned char* rows = ring + (t % kRingStages) * kRingStageBytes + h * slot_bytes;
     FastRows r;
     const double2* wp = reinterpret_cast<const double2*>(rows);
     const double2 a = wp[0], b = wp[1], c = wp[2], d = wp[3];
@@ -482,69 +525,10 @@ __device__ __forceinline__ void fast_consume(uint32_t row_bytes, uint32_t bin_of
     r.bins = make_uint2(bb.x & bin_mask, bb.y & bin_mask);
     r.w[0] = a.x; r.w[1] = a.y; r.w[2] = b.x; r.w[3] = b.y;
     r.w[4] = c.x; r.w[5] = c.y; r.w[6] = d.x; r.w[7] = d.y;
-    __syncwarp();  // every lane has read the stage
-    if (lane == 0) mbar_arrive(empty + stage);
+    __syncwarp();  // every lane has read the stage before the next copy overwrites it
     add_chunk(col_s, r);
   }
-}
-
-// A warp without a private copy fills the rings of its share of the fast warps (lane <-> fast
-// warp), one step at a time.  A lane waits until the fast warp has released the stage (round r-1 of it), announces
-// the bytes on the "full" mbarrier and issues one bulk copy per row.  A slot past the end of the
-// list gets zero weights and the last chunk's bins.
-template <int SLOTS>
-__device__ __forceinline__ void fast_produce(const bf_param_tables& prm, const double* weights,
-                                             const uint2* refs, uint32_t n_mc, uint32_t nfw,
-                                             uint32_t first, uint32_t n_prod, int lane,
-                                             unsigned char* ring_all, uint64_t* full_all,
-                                             uint64_t* empty_all) {
-  const uint32_t row_bytes = static_cast<uint32_t>(prm.fast_pad) * BF_CHUNK;
-  const uint32_t slot_bytes = 64u + row_bytes;
-  const uint32_t step = nfw * SLOTS;
-  const uint32_t n_steps_max = (n_mc + step - 1) / step;  // steps of fast warp 0
-  // Every fast warp is served by one lane of one producer warp, step after step: the stages of a
-  // ring are then filled in order, which is what the parity of its mbarriers can tell apart.  All
-  // lanes of an iteration work on the same step, so a lane only waits for stages that earlier
-  // iterations filled.
-  const uint32_t f = first + static_cast<uint32_t>(lane) * n_prod;
-  if (f >= nfw) return;
-  // chunk references three steps ahead of the copies that need them as addresses
-  constexpr int kAhead = 3;
-  uint2 rq[kAhead][SLOTS];
-  auto fetch = [&](uint32_t t, uint2* r) {
-#pragma unroll
-    for (int sl = 0; sl < SLOTS; ++sl) {
-      const uint32_t i = f * SLOTS + t * step + sl;
-      r[sl] = refs[i < n_mc ? i : n_mc - 1];
-    }
-  };
-#pragma unroll
-  for (int a = 0; a < kAhead; ++a) fetch(a, rq[a]);
-  for (uint32_t t = 0; t < n_steps_max; ++t) {
-    uint2 cur[SLOTS];
-#pragma unroll
-    for (int sl = 0; sl < SLOTS; ++sl) cur[sl] = rq[0][sl];
-#pragma unroll
-    for (int a = 0; a + 1 < kAhead; ++a)
-#pragma unroll
-      for (int sl = 0; sl < SLOTS; ++sl) rq[a][sl] = rq[a + 1][sl];
-    fetch(t + kAhead, rq[kAhead - 1]);
-    const uint32_t base = f * SLOTS + t * step;
-    if (base >= n_mc) break;  // this fast warp has no more steps
-    const uint32_t stage = t % kRingStages, round = t / kRingStages;
-    uint64_t* full = full_all + f * kRingStages + stage;
-    if (round > 0) mbar_wait(empty_all + f * kRingStages + stage, (round - 1) & 1u);
-    unsigned char* dst = ring_all + (f * kRingStages + stage) * kRingStageBytes;
-    mbar_expect_tx(full, SLOTS * slot_bytes);
-#pragma unroll
-    for (int sl = 0; sl < SLOTS; ++sl) {
-      const bool valid = base + sl < n_mc;
-      const void* wsrc = valid ? static_cast<const void*>(weights + static_cast<size_t>(cur[sl].y) * BF_CHUNK)
-                               : static_cast<const void*>(g_zero_weights);
-      tma_load_1d(dst + sl * slot_bytes, wsrc, 64, full);
-      tma_load_1d(dst + sl * slot_bytes + 64, prm.fast_bin + static_cast<size_t>(cur[sl].x) * row_bytes, row_bytes, full);
-    }
-  }
+  asm volatile("cp.async.wait_group 0;" ::: "memory");
 }
 
 constexpr int kSlowBatch = 4;  // runs per lane and step of a slow warp
@@ -699,8 +683,6 @@ split_hist_kernel(bf_param_tables prm, int hist_doubles, uint32_t seg_chunks, co
   int* plane = lcol + 64;      // [2][64] by class, slot*32 + parameter: lane
   int* tmpw = plane + 128;     // [2][32]
   int* misc = tmpw + 64;       // [1] fast copy, [2] slow copy, [3] fast warps, [4] slow warps
-  uint64_t* ring_full = reinterpret_cast<uint64_t*>(misc + 16);       // [NW][kRingStages]
-  uint64_t* ring_empty = ring_full + kSplitWarpsMax * kRingStages;   // [NW][kRingStages]
 
 
   const int64_t s =
@@ -846,17 +828,6 @@ split_hist_kernel(bf_param_tables prm, int hist_doubles, uint32_t seg_chunks, co
     if (nf > 0 && F > NW - S - X) F = NW - S - X;
     misc[3] = F;
     misc[4] = S;
-    // the row rings of this segment's fast warps: one arrival each (the producer lane that
-    // announces the bytes / lane 0 of the fast warp that releases the stage)
-    for (int i = 0; i < F * kRingStages; ++i) {
-      if (seg > 0) {
-        asm volatile("mbarrier.inval.shared::cta.b64 [%0];" ::"r"(smem_u32(ring_full + i)) : "memory");
-        asm volatile("mbarrier.inval.shared::cta.b64 [%0];" ::"r"(smem_u32(ring_empty + i)) : "memory");
-      }
-      mbar_init(ring_full + i, 1);
-      mbar_init(ring_empty + i, 1);
-    }
-    mbar_fence_init();
   }
   __syncthreads();
   const int cf = misc[1], cs = misc[2], F = misc[3], S = misc[4];
@@ -870,10 +841,9 @@ split_hist_kernel(bf_param_tables prm, int hist_doubles, uint32_t seg_chunks, co
   if (nf_seg > 0) {
     if (warp < F) {
       const int kf = lparam[lane];
-      fast_consume<FS>(static_cast<uint32_t>(prm.fast_pad) * BF_CHUNK, (kf >= 0 ? kf : 0) * BF_CHUNK,
-                       kf >= 0 ? 0xffffffffu : 0u, nf_seg, warp, F, lane, hist + warp * cf + lcol[lane],
-                       ring + warp * kRingStages * kRingStageBytes, ring_full + warp * kRingStages,
-                       ring_empty + warp * kRingStages);
+      fast_accumulate<FS>(prm, sc.weights, frefs, nf_seg, warp, F, (kf >= 0 ? kf : 0) * BF_CHUNK,
+                          kf >= 0 ? 0xffffffffu : 0u, lane, hist + warp * cf + lcol[lane],
+                          ring + warp * kRingStages * kRingStageBytes);
     } else if (warp < F + S) {
       const int ks = lparam[32 + lane];
       const bool live = ks >= 0;
@@ -881,15 +851,10 @@ split_hist_kernel(bf_param_tables prm, int hist_doubles, uint32_t seg_chunks, co
       eacc = slow_accumulate<SS>(prm, sc.chunk_wsum, sseg, ns_seg, warp - F, S, live ? ks : 0, live,
                                  live_q, lane, hist + F * cf + (warp - F) * cs + lcol[32 + lane]);
     } else if (nf > 0) {
-      // Warps without a private copy.  In the first segment the last of them adds up the
+      // Warps without a private copy: in the first segment the last of them adds up the
       // expectation partials of the fast class that the grouped weights kernel left per list
-      // position (lane <-> (parameter, part)); the others -- all of them in later segments --
-      // feed the fast warps' row rings.
-      const int nx = NW - F - S, x = warp - F - S;
-      const bool sums = seg == 0 && (x == nx - 1);
-      const int n_prod = (seg == 0 && nx > 1) ? nx - 1 : nx;
-      if (F > 0 && (!sums || nx == 1))
-        fast_produce<FS>(prm, sc.weights, frefs, nf_seg, F, x, n_prod, lane, ring, ring_full, ring_empty);
+      // position (lane <-> (parameter, part)).
+      const bool sums = seg == 0 && warp == NW - 1;
       if (sums) {
         const int pad = prm.fast_pad;
         const int per = 32 / pad;  // list positions per warp instruction
