@@ -368,12 +368,6 @@ constexpr uint32_t kSegmentChunks = 16384;
 // shared memory: hist [hist_doubles] | red [2 NW] | redj [NW] | sscan (NW u32, as NW/2 doubles)
 //   | epart [NW][32] | int tables (see kernel); sized for the largest block
 constexpr int kSplitInts = 3 * 64 + 2 * 64 + 128 + 64 + 16;
-// Row ring of a fast warp: kRingStages steps of rows (8 weights + the bin bytes of every chunk
-// slot), filled by the warp's own cp.async copies.  The rings sit behind the private copies in the
-// histogram area (2.3 KB per fast warp).
-constexpr int kRingStages = 6;
-constexpr int kRingStageBytes = 384;  // 2 slots x (64 B weights + 128 B bins) or 1 x (64 + 256)
-constexpr int kRingDoubles = kRingStages * kRingStageBytes / 8;  // per fast warp
 struct SplitSmem {
   static __host__ __device__ size_t bytes(int hist_doubles) {
     return (static_cast<size_t>(hist_doubles) + 4 * kSplitWarpsMax + kSplitWarpsMax * 32 + 64) * sizeof(double) +
@@ -452,83 +446,89 @@ __device__ __forceinline__ void add_chunk(uint32_t col_s, const FastRows& r) {
 }
 
 // A fast warp: chunks first*SLOTS + h, then every nfw*SLOTS-th, of the star's member chunks.
-// The rows of a step (8 weights + the bin bytes of every chunk slot: 384 B) are copied into the
-// warp's own ring in shared memory by one cp.async instruction (SASS LDGSTS: 24 lanes x 16 B, each
-// with its own source address) kRingStages-1 steps before they are used, so the accumulation reads
-// them with shared-memory latency and no register holds a row in flight.  The chunk references
-// the copies need as addresses are requested three steps earlier still, in registers.
-// bin_off = byte offset of this lane's bins inside a slot's rows, bin_mask = 0 for a lane without
-// a parameter (it then adds into the one-bin column it owns).  A slot past the end of the list
-// gets zero weights and the last chunk's bins.
-// (A ring filled by TMA bulk copies from the warps without a private copy, with full / empty
-// mbarriers per stage, was built and measured: 43 / 27 / 18 ms for the three ranges of a batch
-// against 29 / 16 / 9 -- four bulk copies of 64..128 B per step and fast warp are too many small
-// requests for one or two producer warps to issue.)
+// Software pipeline in registers: the chunk reference is read four steps ahead, the rows (8 bin
+// bytes + 8 weights) three steps ahead of their use, so that three steps' rows are in flight
+// per warp.  bins_lane = fast_bin + this lane's parameter, bin_mask = 0 for a lane without a
+// parameter (it then adds into the one-bin column it owns); a lane whose slot has run past the
+// end of the list re-reads the last chunk's bins with zero weights.
 template <int SLOTS>
-__device__ __forceinline__ void fast_accumulate(const bf_param_tables& prm, const double* __restrict__ weights,
+__device__ __forceinline__ void fast_accumulate(const uint8_t* __restrict__ bins_lane, uint32_t row_bytes,
+                                                uint32_t bin_mask, const double* __restrict__ weights,
                                                 const uint2* refs, uint32_t n_mc, uint32_t first,
-                                                uint32_t nfw, uint32_t bin_off, uint32_t bin_mask, int lane,
-                                                double* col, unsigned char* ring) {
+                                                uint32_t nfw, int lane, double* col,
+                                                volatile uint32_t* progress) {
   const uint32_t h = SLOTS == 2 ? static_cast<uint32_t>(lane >> 4) : 0u;
   const uint32_t step = nfw * SLOTS;
   const uint32_t col_s = static_cast<uint32_t>(__cvta_generic_to_shared(col));
-  const uint32_t start = first * SLOTS;
+  const uint32_t start = first * SLOTS;  // warp-uniform position of slot 0
   if (start >= n_mc) return;
   const uint32_t n_steps = (n_mc - start + step - 1) / step;
-  const uint32_t row_bytes = static_cast<uint32_t>(prm.fast_pad) * BF_CHUNK;
-  const uint32_t slot_bytes = 64u + row_bytes;
-  // copy role of this lane: piece q (16 B) of chunk slot cslot
-  const uint32_t pieces = slot_bytes / 16;
-  const uint32_t cslot = static_cast<uint32_t>(lane) / pieces, q = static_cast<uint32_t>(lane) % pieces;
-  const bool copier = cslot < static_cast<uint32_t>(SLOTS);
-  const uint32_t ring_s = static_cast<uint32_t>(__cvta_generic_to_shared(ring)) + cslot * slot_bytes + q * 16;
-  const unsigned char* wbase = reinterpret_cast<const unsigned char*>(weights) + q * 16;
-  const unsigned char* bbase = prm.fast_bin + (q - 4) * 16;
-  const unsigned char* zbase = reinterpret_cast<const unsigned char*>(g_zero_weights) + (q & 3) * 16;
   const uint32_t last = n_mc - 1;
-  auto fetch_ref = [&](uint32_t t, bool& valid) {  // reference of step t for this lane's copy slot
-    const uint32_t i = start + t * step + (copier ? cslot : 0u);
+  uint32_t i = start + h;  // this lane's position of the step whose reference is read next
+  auto next_ref = [&](bool& valid) {
     valid = i <= last;
-    return refs[valid ? i : last];
+    const uint2 r = refs[valid ? i : last];
+    i += step;
+    return r;
   };
-  auto issue = [&](uint32_t t, uint2 ref, bool valid) {  // rows of step t -> stage t % kRingStages
-    if (copier && t < n_steps) {
-      const unsigned char* src = q < 4 ? (valid ? wbase + static_cast<size_t>(ref.y) * 64 : zbase)
-                                       : bbase + static_cast<size_t>(ref.x) * row_bytes;
-      asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(ring_s + (t % kRingStages) * kRingStageBytes),
-                   "l"(src));
-    }
-    asm volatile("cp.async.commit_group;" ::: "memory");
-  };
-  // references: r0 is the one of the step issued next, r1 / r2 follow
-  bool v0, v1, v2;
-  uint2 r0 = fetch_ref(0, v0), r1 = fetch_ref(1, v1), r2 = fetch_ref(2, v2);
-  uint32_t t_issue = 0;
-  auto issue_next = [&]() {
-    issue(t_issue, r0, v0);
-    r0 = r1; v0 = v1;
-    r1 = r2; v1 = v2;
-    r2 = fetch_ref(t_issue + 3, v2);
-    ++t_issue;
-  };
-#pragma unroll 1
-  for (int a = 0; a < kRingStages - 1; ++a) issue_next();
-  for (uint32_t t = 0; t < n_steps; ++t) {
-    issue_next();  // step t + kRingStages - 1 (an empty group past the end keeps the count)
-    asm volatile("cp.async.wait_group %0;" ::"n"(kRingStages - 1) : "memory");
-    __syncwarp();  // the copies of all lanes for step t have landed
-    const unsigned char* rows = ring + (t % kRingStages) * kRingStageBytes + h * slot_bytes;
-    FastRows r;
-    const double2* wp = reinterpret_cast<const double2*>(rows);
-    const double2 a = wp[0], b = wp[1], c = wp[2], d = wp[3];
-    const uint2 bb = *reinterpret_cast<const uint2*>(rows + 64 + bin_off);
+  auto load = [&](uint2 ref, bool valid, FastRows& r) {
+    const double2* wp = valid ? reinterpret_cast<const double2*>(weights + static_cast<size_t>(ref.y) * BF_CHUNK)
+                              : reinterpret_cast<const double2*>(g_zero_weights);
+    const double2 a = __ldg(wp), b = __ldg(wp + 1), c = __ldg(wp + 2), d = __ldg(wp + 3);
+    const uint2 bb = __ldg(reinterpret_cast<const uint2*>(bins_lane + static_cast<size_t>(ref.x) * row_bytes));
     r.bins = make_uint2(bb.x & bin_mask, bb.y & bin_mask);
     r.w[0] = a.x; r.w[1] = a.y; r.w[2] = b.x; r.w[3] = b.y;
     r.w[4] = c.x; r.w[5] = c.y; r.w[6] = d.x; r.w[7] = d.y;
-    __syncwarp();  // every lane has read the stage before the next copy overwrites it
-    add_chunk(col_s, r);
+  };
+  // Three row sets in rotation, each refilled (for three steps later) right after it has been
+  // consumed, and two sets of three chunk references in turn, requested a whole round before
+  // they are needed as addresses: no register copy and no address ever waits for a load that
+  // was issued less than three steps earlier.
+  FastRows r0, r1, r2;
+  uint2 qa0, qa1, qa2, qb0, qb1, qb2;
+  bool va0, va1, va2, vb0, vb1, vb2;
+  {
+    bool v;
+    uint2 ref = next_ref(v);
+    load(ref, v, r0);
+    ref = next_ref(v);
+    load(ref, v, r1);
+    ref = next_ref(v);
+    load(ref, v, r2);
   }
-  asm volatile("cp.async.wait_group 0;" ::: "memory");
+  qa0 = next_ref(va0);
+  qa1 = next_ref(va1);
+  qa2 = next_ref(va2);
+  for (uint32_t t = 0; t < n_steps; t += 6) {
+    if (progress && lane == 0) *progress = start + t * step;  // (the prefetching warps follow it)
+    qb0 = next_ref(vb0);
+    qb1 = next_ref(vb1);
+    qb2 = next_ref(vb2);
+    add_chunk(col_s, r0);
+    load(qa0, va0, r0);
+    if (t + 1 < n_steps) {
+      add_chunk(col_s, r1);
+      load(qa1, va1, r1);
+    }
+    if (t + 2 < n_steps) {
+      add_chunk(col_s, r2);
+      load(qa2, va2, r2);
+    }
+    if (t + 3 >= n_steps) break;
+    qa0 = next_ref(va0);
+    qa1 = next_ref(va1);
+    qa2 = next_ref(va2);
+    add_chunk(col_s, r0);
+    load(qb0, vb0, r0);
+    if (t + 4 < n_steps) {
+      add_chunk(col_s, r1);
+      load(qb1, vb1, r1);
+    }
+    if (t + 5 < n_steps) {
+      add_chunk(col_s, r2);
+      load(qb2, vb2, r2);
+    }
+  }
 }
 
 constexpr int kSlowBatch = 4;  // runs per lane and step of a slow warp
@@ -612,6 +612,42 @@ __device__ __forceinline__ double slow_accumulate(const bf_param_tables& prm,
   return eacc;
 }
 
+// Warps without a private copy run ahead of the fast warps and pull the rows those will need
+// (a chunk's 8 weights and its bin bytes) into L2: the weights are read once per star, so
+// without this every row request of a fast warp goes to HBM.  kPrefetchAhead bounds the distance
+// in chunks (the chunks in flight over all SMs must stay well inside L2).
+constexpr uint32_t kPrefetchAhead = 1024;
+
+__device__ __forceinline__ void prefetch_l2(const void* p) {
+  asm volatile("prefetch.global.L2 [%0];" ::"l"(p));
+}
+
+__device__ __forceinline__ void prefetch_rows(const bf_param_tables& prm, const double* weights,
+                                              const double* chunk_wsum, const uint2* refs,
+                                              uint32_t n_mc, const uint2* srefs, uint32_t n_sc,
+                                              uint32_t first, uint32_t n_warps, int lane,
+                                              const volatile uint32_t* progress) {
+  const uint32_t row_bytes = static_cast<uint32_t>(prm.fast_pad) * BF_CHUNK;
+  for (uint32_t base = first * 32; base < n_mc; base += n_warps * 32) {
+    while (base >= *progress + kPrefetchAhead) __nanosleep(200);  // warp-uniform
+    const uint32_t i = base + lane;
+    if (i < n_mc) {
+      const uint2 ref = refs[i];
+      prefetch_l2(weights + static_cast<size_t>(ref.y) * BF_CHUNK);
+      const uint8_t* row = prm.fast_bin + static_cast<size_t>(ref.x) * row_bytes;
+      prefetch_l2(row);
+      if (row_bytes > 128) prefetch_l2(row + 128);
+    }
+  }
+  // the slow warp's rows (run sums, bin bytes, values): a fraction of the above, no throttle
+  for (uint32_t i = first * 32 + lane; i < n_sc; i += n_warps * 32) {
+    const uint2 ref = srefs[i];
+    prefetch_l2(chunk_wsum + ref.y);
+    prefetch_l2(prm.slow_bin + static_cast<size_t>(ref.x) * prm.slow_pad);
+    prefetch_l2(prm.slow_q + static_cast<size_t>(ref.x) * prm.slow_pad);
+  }
+}
+
 // occupied bin range of the class parameters over the star's member chunks (four chunks per
 // lane in flight: this walk waits on L2 only)
 template <int SLOTS, bool FAST>
@@ -683,7 +719,6 @@ split_hist_kernel(bf_param_tables prm, int hist_doubles, uint32_t seg_chunks, co
   int* plane = lcol + 64;      // [2][64] by class, slot*32 + parameter: lane
   int* tmpw = plane + 128;     // [2][32]
   int* misc = tmpw + 64;       // [1] fast copy, [2] slow copy, [3] fast warps, [4] slow warps
-
 
   const int64_t s =
       star_begin + (star_order ? star_order[blockIdx.x] : static_cast<int64_t>(blockIdx.x));
@@ -811,15 +846,15 @@ split_hist_kernel(bf_param_tables prm, int hist_doubles, uint32_t seg_chunks, co
       S = hist_doubles / cs;
       if (S > NW) S = NW;
     } else if (nsl == 0) {
-      F = hist_doubles / (cf + kRingDoubles);
+      F = hist_doubles / cf;
     } else {
       // a slow warp moves a sixteenth of what a fast warp moves per chunk: one is enough up to
       // a dozen fast warps
       S = 1;
-      F = (hist_doubles - cs) / (cf + kRingDoubles);
-      if (F > 12 && (hist_doubles - 2 * cs) / (cf + kRingDoubles) >= 12 && NW > 15) {
+      F = (hist_doubles - cs) / cf;
+      if (F > 12 && (hist_doubles - 2 * cs) / cf >= 12 && NW > 15) {
         S = 2;
-        F = (hist_doubles - 2 * cs) / (cf + kRingDoubles);
+        F = (hist_doubles - 2 * cs) / cf;
       }
       if (F < 1) F = 1;  // cannot happen: the host checked the worst case
     }
@@ -828,11 +863,12 @@ split_hist_kernel(bf_param_tables prm, int hist_doubles, uint32_t seg_chunks, co
     if (nf > 0 && F > NW - S - X) F = NW - S - X;
     misc[3] = F;
     misc[4] = S;
+    misc[8] = 0;  // chunks of the segment the first fast warp has passed
   }
   __syncthreads();
   const int cf = misc[1], cs = misc[2], F = misc[3], S = misc[4];
+  volatile uint32_t* progress = reinterpret_cast<volatile uint32_t*>(misc + 8);
   const int used = F * cf + S * cs;
-  unsigned char* ring = reinterpret_cast<unsigned char*>(hist + ((used + 1) & ~1));  // 16-byte aligned
   for (int i = threadIdx.x; i < used; i += blockDim.x) hist[i] = 0.0;
   __syncthreads();
 
@@ -841,9 +877,11 @@ split_hist_kernel(bf_param_tables prm, int hist_doubles, uint32_t seg_chunks, co
   if (nf_seg > 0) {
     if (warp < F) {
       const int kf = lparam[lane];
-      fast_accumulate<FS>(prm, sc.weights, frefs, nf_seg, warp, F, (kf >= 0 ? kf : 0) * BF_CHUNK,
-                          kf >= 0 ? 0xffffffffu : 0u, lane, hist + warp * cf + lcol[lane],
-                          ring + warp * kRingStages * kRingStageBytes);
+      fast_accumulate<FS>(prm.fast_bin + (kf >= 0 ? kf : 0) * BF_CHUNK,
+                          static_cast<uint32_t>(prm.fast_pad) * BF_CHUNK, kf >= 0 ? 0xffffffffu : 0u,
+                          sc.weights, frefs, nf_seg, warp, F, lane, hist + warp * cf + lcol[lane],
+                          warp == 0 ? progress : nullptr);
+      if (warp == 0 && lane == 0) *progress = 0xffffffffu - kPrefetchAhead;  // release the followers
     } else if (warp < F + S) {
       const int ks = lparam[32 + lane];
       const bool live = ks >= 0;
@@ -851,20 +889,18 @@ split_hist_kernel(bf_param_tables prm, int hist_doubles, uint32_t seg_chunks, co
       eacc = slow_accumulate<SS>(prm, sc.chunk_wsum, sseg, ns_seg, warp - F, S, live ? ks : 0, live,
                                  live_q, lane, hist + F * cf + (warp - F) * cs + lcol[32 + lane]);
     } else if (nf > 0) {
-      // Warps without a private copy: in the first segment the last of them adds up the
-      // expectation partials of the fast class that the grouped weights kernel left per list
-      // position (lane <-> (parameter, part)).
-      const bool sums = seg == 0 && warp == NW - 1;
-      if (sums) {
+      if (seg == 0) {
+        // warps without a private copy add up the expectation partials of the fast class that
+        // the grouped weights kernel left per list position: lane <-> (parameter, part)
         const int pad = prm.fast_pad;
         const int per = 32 / pad;  // list positions per warp instruction
         const int p = lane % pad, sub = lane / pad;
-        const uint32_t stride = static_cast<uint32_t>(per);
+        const uint32_t stride = static_cast<uint32_t>(NW - F - S) * per;
         const double* src = sc.exp_part + p;
         double acc8[8];
 #pragma unroll
         for (int u = 0; u < 8; ++u) acc8[u] = 0.0;
-        for (uint32_t e = e0 + sub; e < e1; e += 8 * stride) {
+        for (uint32_t e = e0 + (warp - F - S) * per + sub; e < e1; e += 8 * stride) {
 #pragma unroll
           for (int u = 0; u < 8; ++u) {  // eight rows in flight per lane
             const uint32_t eu = e + u * stride;
@@ -873,6 +909,9 @@ split_hist_kernel(bf_param_tables prm, int hist_doubles, uint32_t seg_chunks, co
         }
         eacc = ((acc8[0] + acc8[1]) + (acc8[2] + acc8[3])) + ((acc8[4] + acc8[5]) + (acc8[6] + acc8[7]));
       }
+      if (F > 0 && NW - F - S >= 4)  // (with fewer idle warps the fast warps cover the latency)
+        prefetch_rows(prm, sc.weights, sc.chunk_wsum, frefs, nf_seg, sseg, ns_seg, warp - F - S,
+                      NW - F - S, lane, progress);
     }
   }
   epart[warp * 32 + lane] = eacc;
@@ -890,7 +929,8 @@ split_hist_kernel(bf_param_tables prm, int hist_doubles, uint32_t seg_chunks, co
         for (int sl = 0; sl < SS; ++sl) e += epart[(F + w) * 32 + plane[64 + sl * 32 + p]];
     } else if (seg == 0) {
       const int pad = prm.fast_pad;
-      for (int sub = 0; sub < 32 / pad; ++sub) e += epart[(NW - 1) * 32 + sub * pad + cl];
+      for (int w = 0; w < nx; ++w)
+        for (int sub = 0; sub < 32 / pad; ++sub) e += epart[(F + S + w) * 32 + sub * pad + cl];
     }
     esum[k] += e;
   }
