@@ -116,6 +116,7 @@ class FitPlan(C.Structure):
         ("sm_count", C.c_int),
         ("force_legacy", C.c_int),
         ("max_range_entries", i64),
+        ("boxes", c_void_p),
     ]
 
 
@@ -155,6 +156,8 @@ PROTOTYPES = {
     "bf_device_info": (C.c_int, [C.c_int, C.POINTER(C.c_int), C.POINTER(C.c_int), C.POINTER(C.c_int)]),
     "bf_dense_chi2": (C.c_int, [C.c_int, i64, c_void_p, i64, i64, c_void_p, c_void_p, c_void_p,
                                 C.c_int, c_void_p]),
+    "bf_dense_chi2_pruned": (C.c_int, [C.c_int, i64, c_void_p, c_void_p, i64, i64, c_void_p, c_void_p, c_void_p,
+                                       c_void_p, C.c_int, c_void_p]),
     "bf_dense_chi2_cov": (C.c_int, [C.c_int, i64, c_void_p, i64, i64, c_void_p, c_void_p, c_void_p,
                                     C.c_int, c_void_p]),
     "bf_dense_tiles_per_item": (C.c_int, [i64, i64, C.c_int]),

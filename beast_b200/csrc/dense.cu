@@ -17,6 +17,15 @@
 // This pass is a *filter*: the exact FP64 pass (exact.cu) re-evaluates every model of
 // every selected group, so FP32 rounding here only has to stay inside the selection
 // margin ("margins").
+//
+// Pruned sweep (PRUNE): with a per-star ceiling `cut` on the selection threshold (from the
+// coarse sweep: the minimum over a subset of the models is an upper bound of the minimum) and a
+// box around each group's models (per band: the range of model fluxes m = a / r and the smallest
+// r; the smallest c2),
+//   acc(s, m) = sum_b r_mb^2 (f_sb - m_mb)^2 + c2_m >= sum_b rlo_b^2 dist(f_sb, [mlo_b, mhi_b])^2 + c2min
+// a warp skips a group that none of its 256 stars can select and reports +inf for it.  The
+// group lists that follow are the same ones: a skipped group's minimum is above the star's
+// selection threshold, and the group of the star's minimum is never skipped.
 
 #include "common.cuh"
 
@@ -29,33 +38,50 @@ constexpr int kNPair = BF_STAR_BLOCK / kDenseThreads / 2;  // star pairs per thr
 // then carries, per model, -m'_b = -(sed+bias)/s_b, D_b = icov_diag_b s_b^2, the packed upper
 // triangle O_kl = 2 icov_offdiag_kl s_k s_l (k<l, row-major) and c2, and
 //   acc = sum_b t_b^2 D_b + sum_k t_k sum_{l>k} O_kl t_l + c2,   t_b = f_b/s_b - m'_b.
-template <int NB, bool COV>
+template <int NB, bool COV, bool PRUNE = false>
 struct DenseSmem {
   static constexpr int kRows = COV ? 2 * NB + NB * (NB - 1) / 2 + 1 : 2 * NB + 1;
   static constexpr int kStages = COV ? 3 : 4;
   static constexpr int kPrefetch = COV ? 1 : 2;  // tiles in flight ahead of the consumer
   static constexpr uint32_t kTileBytes = kRows * BF_TILE_MODELS * sizeof(float);
-  static constexpr uint32_t kBytes = kStages * kTileBytes + 2 * kStages * sizeof(uint64_t);
+  // group boxes of a tile: per group mlo[NB], mhi[NB], rlo[NB], c2min, padded to 16 bytes
+  static constexpr int kBoxFloats = BF_BOX_FLOATS(NB);
+  static constexpr uint32_t kBoxBytes = PRUNE ? (BF_TILE_MODELS / BF_GROUP) * kBoxFloats * sizeof(float) : 0;
+  static constexpr uint32_t kCutBytes = PRUNE ? BF_STAR_BLOCK * sizeof(float) : 0;
+  static constexpr uint32_t kBytes =
+      kStages * (kTileBytes + kBoxBytes) + kCutBytes + 2 * kStages * sizeof(uint64_t);
 };
 
-template <int NB, bool COV>
+// Stars of a thread: star0 + warp * 256 + q * 32 + lane, q = 0..2*NPAIR-1 (pair p = (2p, 2p+1)):
+// a warp owns 256 consecutive stars -- neighbours after the presort, which is what lets a whole
+// warp skip a group.
+template <int NB, bool COV, bool PRUNE>
 __global__ void __launch_bounds__(kDenseThreads, COV ? 2 : 3)
 dense_chi2_kernel(const float* __restrict__ tiles, int64_t n_tiles, int tiles_per_item,
                   const float* __restrict__ flux, int64_t ld_star, float* __restrict__ gmin,
-                  unsigned long long* __restrict__ starmin) {
+                  unsigned long long* __restrict__ starmin, const float* __restrict__ boxes,
+                  const float* __restrict__ cut) {
   constexpr int TM = BF_TILE_MODELS;
-  constexpr int ROWS = DenseSmem<NB, COV>::kRows;
-  constexpr int kDenseStages = DenseSmem<NB, COV>::kStages;
-  constexpr int kDensePrefetch = DenseSmem<NB, COV>::kPrefetch;
-  constexpr uint32_t TILE_BYTES = DenseSmem<NB, COV>::kTileBytes;
+  using Smem = DenseSmem<NB, COV, PRUNE>;
+  constexpr int ROWS = Smem::kRows;
+  constexpr int kDenseStages = Smem::kStages;
+  constexpr int kDensePrefetch = Smem::kPrefetch;
+  constexpr uint32_t TILE_BYTES = Smem::kTileBytes;
+  constexpr uint32_t BOX_BYTES = Smem::kBoxBytes;
+  constexpr int BOXF = Smem::kBoxFloats;
   constexpr int GROUPS_PER_TILE = TM / BF_GROUP;
 
   extern __shared__ __align__(128) unsigned char smem_raw[];
   float* stage_buf = reinterpret_cast<float*>(smem_raw);
-  uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem_raw + kDenseStages * TILE_BYTES);
+  float* box_buf = reinterpret_cast<float*>(smem_raw + kDenseStages * TILE_BYTES);
+  float* cut_s = reinterpret_cast<float*>(smem_raw + kDenseStages * (TILE_BYTES + BOX_BYTES));
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem_raw + kDenseStages * (TILE_BYTES + BOX_BYTES) +
+                                                   Smem::kCutBytes);
   uint64_t* empty_bar = full_bar + kDenseStages;
 
   const int tid = threadIdx.x;
+  const int lane = tid & 31;
+  const int wbase = (tid >> 5) * (2 * kNPair * 32) + lane;  // first star of this thread in the block
   const int64_t star0 = static_cast<int64_t>(blockIdx.y) * BF_STAR_BLOCK;
   const int64_t t_begin = static_cast<int64_t>(blockIdx.x) * tiles_per_item;
   const int nt = static_cast<int>(min(static_cast<int64_t>(tiles_per_item), n_tiles - t_begin));
@@ -71,26 +97,35 @@ dense_chi2_kernel(const float* __restrict__ tiles, int64_t n_tiles, int tiles_pe
   __syncthreads();
 
   const float* tile_src = tiles + t_begin * static_cast<int64_t>(ROWS * TM);
+  const float* box_src = PRUNE ? boxes + t_begin * static_cast<int64_t>(GROUPS_PER_TILE * BOXF) : nullptr;
+  auto load_tile = [&](int j, int js) {  // tile j of this item (and its group boxes) -> stage js
+    mbar_expect_tx(&full_bar[js], TILE_BYTES + BOX_BYTES);
+    tma_load_1d(stage_buf + js * (ROWS * TM), tile_src + static_cast<int64_t>(j) * (ROWS * TM),
+                TILE_BYTES, &full_bar[js]);
+    if constexpr (PRUNE)
+      tma_load_1d(box_buf + js * (GROUPS_PER_TILE * BOXF),
+                  box_src + static_cast<int64_t>(j) * (GROUPS_PER_TILE * BOXF), BOX_BYTES, &full_bar[js]);
+  };
   if (tid == 0) {
 #pragma unroll
     for (int j = 0; j < kDensePrefetch; ++j) {
-      if (j < nt) {
-        mbar_expect_tx(&full_bar[j], TILE_BYTES);
-        tma_load_1d(stage_buf + j * (ROWS * TM), tile_src + static_cast<int64_t>(j) * (ROWS * TM),
-                    TILE_BYTES, &full_bar[j]);
-      }
+      if (j < nt) load_tile(j, j);
     }
   }
 
-  // this thread's stars: star0 + q*128 + tid, q = 0..2*NPAIR-1; pair p = (q=2p, q=2p+1)
   f32x2 f[kNPair][NB];
 #pragma unroll
   for (int p = 0; p < kNPair; ++p) {
 #pragma unroll
     for (int b = 0; b < NB; ++b) {
-      const float* fb = flux + static_cast<int64_t>(b) * ld_star + star0 + tid;
-      f[p][b] = pack2(fb[(2 * p) * kDenseThreads], fb[(2 * p + 1) * kDenseThreads]);
+      const float* fb = flux + static_cast<int64_t>(b) * ld_star + star0 + wbase;
+      f[p][b] = pack2(fb[(2 * p) * 32], fb[(2 * p + 1) * 32]);
     }
+  }
+  if constexpr (PRUNE) {
+#pragma unroll
+    for (int q = 0; q < 2 * kNPair; ++q) cut_s[wbase + q * 32] = cut[star0 + wbase + q * 32];
+    __syncwarp();  // a thread reads back only what it wrote; the fence keeps the order explicit
   }
 
   const float kInf = __int_as_float(0x7f800000);
@@ -112,9 +147,7 @@ dense_chi2_kernel(const float* __restrict__ tiles, int64_t n_tiles, int tiles_pe
         const int js = j % kDenseStages;
         const int use = j / kDenseStages;
         if (use > 0) mbar_wait(&empty_bar[js], (use - 1) & 1);
-        mbar_expect_tx(&full_bar[js], TILE_BYTES);
-        tma_load_1d(stage_buf + js * (ROWS * TM), tile_src + static_cast<int64_t>(j) * (ROWS * TM),
-                    TILE_BYTES, &full_bar[js]);
+        load_tile(j, js);
       }
     }
     mbar_wait(&full_bar[stage], (i / kDenseStages) & 1);
@@ -122,6 +155,35 @@ dense_chi2_kernel(const float* __restrict__ tiles, int64_t n_tiles, int tiles_pe
     const float* sb = stage_buf + stage * (ROWS * TM);
 #pragma unroll 1
     for (int g = 0; g < GROUPS_PER_TILE; ++g) {
+      const int64_t gidx = (t_begin + i) * GROUPS_PER_TILE + g;
+      float* gp = gmin + gidx * ld_star + star0 + wbase;
+      if constexpr (PRUNE) {
+        // can any star of this warp select a model of the group?  lower bound of acc per star
+        const float* bx = box_buf + stage * (GROUPS_PER_TILE * BOXF) + g * BOXF;
+        bool need = false;
+#pragma unroll
+        for (int p = 0; p < kNPair; ++p) {
+          float lo = bx[3 * NB], hi = lo;
+#pragma unroll
+          for (int b = 0; b < NB; ++b) {
+            float fl, fh;
+            unpack2(f[p][b], fl, fh);
+            const float mlo = bx[b], mhi = bx[NB + b], rlo = bx[2 * NB + b];
+            const float dl = fmaxf(fmaxf(mlo - fl, fl - mhi), 0.0f) * rlo;
+            const float dh = fmaxf(fmaxf(mlo - fh, fh - mhi), 0.0f) * rlo;
+            lo = fmaf(dl, dl, lo);
+            hi = fmaf(dh, dh, hi);
+          }
+          // 1 - 2^-16 covers the FP32 rounding of both this bound and the accumulators below
+          need |= lo * 0.99998474f < cut_s[wbase + (2 * p) * 32];
+          need |= hi * 0.99998474f < cut_s[wbase + (2 * p + 1) * 32];
+        }
+        if (!__any_sync(0xffffffffu, need)) {
+#pragma unroll
+          for (int q = 0; q < 2 * kNPair; ++q) gp[q * 32] = kInf;
+          continue;
+        }
+      }
       if constexpr (!COV) {
 #pragma unroll 2
         for (int m = g * BF_GROUP; m < (g + 1) * BF_GROUP; m += 2) {
@@ -190,11 +252,9 @@ dense_chi2_kernel(const float* __restrict__ tiles, int64_t n_tiles, int tiles_pe
           }
         }
       }
-      const int64_t gidx = (t_begin + i) * GROUPS_PER_TILE + g;
-      float* gp = gmin + gidx * ld_star + star0 + tid;
 #pragma unroll
       for (int q = 0; q < 2 * kNPair; ++q) {
-        gp[q * kDenseThreads] = rmin[q];
+        gp[q * 32] = rmin[q];
         if (rmin[q] < smin[q]) {
           smin[q] = rmin[q];
           sgrp[q] = static_cast<unsigned int>(gidx);
@@ -213,28 +273,28 @@ dense_chi2_kernel(const float* __restrict__ tiles, int64_t n_tiles, int tiles_pe
     if (smin[q] < kInf) {
       const unsigned long long packed =
           (static_cast<unsigned long long>(__float_as_uint(smin[q])) << 32) | sgrp[q];
-      atomicMin(starmin + star0 + q * kDenseThreads + tid, packed);
+      atomicMin(starmin + star0 + wbase + q * 32, packed);
     }
   }
 }
 
-template <int NB, bool COV>
+template <int NB, bool COV, bool PRUNE = false>
 static int launch_dense(int64_t n_tiles, const float* tiles, int64_t ld_star, const float* flux,
                         float* gmin, unsigned long long* starmin, int tiles_per_item,
-                        cudaStream_t st) {
-  auto kern = dense_chi2_kernel<NB, COV>;
+                        cudaStream_t st, const float* boxes = nullptr, const float* cut = nullptr) {
+  auto kern = dense_chi2_kernel<NB, COV, PRUNE>;
   static bool configured[64] = {};
   int dev = 0;
   BF_CUDA_TRY(cudaGetDevice(&dev));
   if (dev < 64 && !configured[dev]) {
     BF_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                     DenseSmem<NB, COV>::kBytes));
+                                     DenseSmem<NB, COV, PRUNE>::kBytes));
     configured[dev] = true;
   }
   const int64_t n_items = (n_tiles + tiles_per_item - 1) / tiles_per_item;
   dim3 grid(static_cast<unsigned>(n_items), static_cast<unsigned>(ld_star / BF_STAR_BLOCK));
-  kern<<<grid, kDenseThreads, DenseSmem<NB, COV>::kBytes, st>>>(
-      tiles, n_tiles, tiles_per_item, flux, ld_star, gmin, starmin);
+  kern<<<grid, kDenseThreads, DenseSmem<NB, COV, PRUNE>::kBytes, st>>>(
+      tiles, n_tiles, tiles_per_item, flux, ld_star, gmin, starmin, boxes, cut);
   BF_CHECK_LAUNCH("dense_chi2_kernel");
   return BF_OK;
 }
@@ -304,4 +364,30 @@ extern "C" int bf_dense_chi2_cov(int nb, int64_t n_tiles, const float* tiles, in
                                  uint64_t* starmin, int tiles_per_item, void* stream) {
   return dense_entry(true, nb, n_tiles, tiles, n_stars, ld_star, flux, gmin, starmin,
                      tiles_per_item, stream);
+}
+
+extern "C" int bf_dense_chi2_pruned(int nb, int64_t n_tiles, const float* tiles, const float* boxes,
+                                    int64_t n_stars, int64_t ld_star, const float* flux,
+                                    const float* cut, float* gmin, uint64_t* starmin,
+                                    int tiles_per_item, void* stream) {
+  using namespace bf;
+  BF_REQUIRE(nb >= 1 && nb <= 12, "bf_dense_chi2_pruned: nb=%d not instantiated (1..12)", nb);
+  BF_REQUIRE(n_tiles > 0 && n_stars > 0, "bf_dense_chi2_pruned: empty problem");
+  BF_REQUIRE(ld_star >= n_stars && ld_star % BF_STAR_BLOCK == 0,
+             "bf_dense_chi2_pruned: ld_star must be a multiple of %d and >= n_stars", BF_STAR_BLOCK);
+  BF_REQUIRE(tiles_per_item > 0, "bf_dense_chi2_pruned: tiles_per_item must be positive");
+  BF_REQUIRE(tiles && boxes && flux && cut && gmin && starmin, "bf_dense_chi2_pruned: null pointer");
+  BF_REQUIRE((reinterpret_cast<uintptr_t>(boxes) & 15) == 0, "bf_dense_chi2_pruned: boxes must be 16-byte aligned");
+  BF_REQUIRE(ld_star / BF_STAR_BLOCK <= 65535, "bf_dense_chi2_pruned: too many stars per call");
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  unsigned long long* sm = reinterpret_cast<unsigned long long*>(starmin);
+  switch (nb) {
+#define BF_CASE(N) \
+  case N:          \
+    return launch_dense<N, false, true>(n_tiles, tiles, ld_star, flux, gmin, sm, tiles_per_item, st, boxes, cut);
+    BF_CASE(1) BF_CASE(2) BF_CASE(3) BF_CASE(4) BF_CASE(5) BF_CASE(6) BF_CASE(7) BF_CASE(8)
+    BF_CASE(9) BF_CASE(10) BF_CASE(11) BF_CASE(12)
+#undef BF_CASE
+  }
+  return BF_ERR_UNSUPPORTED;
 }

@@ -14,6 +14,7 @@
 
 #include <cub/device/device_radix_sort.cuh>
 
+#include <cstdlib>
 #include <vector>
 
 #include "accum_common.cuh"
@@ -113,6 +114,16 @@ __global__ void argmin_keys_kernel(int64_t n, const unsigned long long* __restri
   vals[i] = static_cast<int32_t>(i);
 }
 
+// Ceiling of every star's selection threshold, in sorted order, from the coarse sweep's minima
+// (a minimum over some of the models bounds the minimum over all of them from above).
+__global__ void prune_cut_kernel(int64_t n, int64_t ld, const int32_t* __restrict__ perm,
+                                 const unsigned long long* __restrict__ starmin, float tau, float err_a,
+                                 float err_b, float* __restrict__ cut) {
+  const int64_t i = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x;
+  if (i >= ld) return;
+  cut[i] = i < n ? select_threshold(starmin_value(starmin[perm[i]]), tau, err_a, err_b) : -1.0f;
+}
+
 __global__ void iota_kernel(int64_t n, int32_t* vals) {
   const int64_t i = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x;
   if (i < n) vals[i] = static_cast<int32_t>(i);
@@ -201,7 +212,7 @@ extern "C" int64_t bf_fit_workspace_bytes(const bf_fit_plan* plan, int64_t n_sta
   b += 2 * static_cast<size_t>(n_stars) * p.nb * 8;            // flux copies
   b += static_cast<size_t>(p.nb) * ld * 4;                      // flux32
   b += static_cast<size_t>(p.n_tiles) * (BF_TILE_MODELS / BF_GROUP) * ld * 4;  // group minima
-  b += static_cast<size_t>(ld) * 8;                             // starmin
+  b += static_cast<size_t>(ld) * 12;                            // starmin, selection ceilings
   b += (2 * static_cast<size_t>(n_stars) * BF_SELECT_SPLIT + 2) * 4 + bf_scan_scratch_elems(n_stars * BF_SELECT_SPLIT) * 4;
   b += static_cast<size_t>(n_stars) * (4 * 4 + 4 + 8 + 4) + 2 * sort_temp_bytes(n_stars);
   // results in sorted order
@@ -275,10 +286,15 @@ extern "C" int bf_fit_batch(const bf_fit_plan* plan, int64_t n_stars, const doub
     BF_CUDA_TRY(cudaDeviceGetAttribute(&sm_count, cudaDevAttrMultiProcessorCount, dev));
   }
   const bool cov = p.full_cov != 0;
-  auto dense = [&](int64_t n_tiles, const float* tiles, float* gmin) -> int {
+  const float tau = static_cast<float>(-2.0 * threshold);
+  const float* cut = nullptr;  // set by the presort when the dense sweep may skip groups
+  auto dense = [&](int64_t n_tiles, const float* tiles, float* gmin, bool prune) -> int {
     starmin_init_kernel<<<blocks_for(ld), kT, 0, st>>>(ld, starmin);
     const int tpi = bf_dense_tiles_per_item(n_tiles, n, sm_count);
     launches += 2;
+    if (prune)
+      return bf_dense_chi2_pruned(nb, n_tiles, tiles, p.boxes, n, ld, flux32, cut, gmin,
+                                  reinterpret_cast<uint64_t*>(starmin), tpi, stream);
     return cov ? bf_dense_chi2_cov(nb, n_tiles, tiles, n, ld, flux32, gmin, reinterpret_cast<uint64_t*>(starmin), tpi, stream)
                : bf_dense_chi2(nb, n_tiles, tiles, n, ld, flux32, gmin, reinterpret_cast<uint64_t*>(starmin), tpi, stream);
   };
@@ -288,7 +304,7 @@ extern "C" int bf_fit_batch(const bf_fit_plan* plan, int64_t n_stars, const doub
     flux_prepare_kernel<<<blocks_for(ld * nb), kT, 0, st>>>(nb, n, ld, flux_in, p.inv_band_scale, flux32);
     float* cg = ar.take_top<float>(static_cast<size_t>(p.n_tiles_coarse) * (BF_TILE_MODELS / BF_GROUP) * ld);
     BF_WS(cg);
-    int rc = dense(p.n_tiles_coarse, p.tiles_coarse, cg);
+    int rc = dense(p.n_tiles_coarse, p.tiles_coarse, cg, false);
     if (rc != BF_OK) return rc;
     ar.hi = workspace_bytes & ~static_cast<size_t>(255);  // the coarse map is not needed any more
     uint32_t* keys = ar.take<uint32_t>(n);
@@ -303,6 +319,14 @@ extern "C" int bf_fit_batch(const bf_fit_plan* plan, int64_t n_stars, const doub
     gather_rows_kernel<<<blocks_for(n * nb), kT, 0, st>>>(n, nb, perm, flux_in, d_flux_sorted);
     flux_run = d_flux_sorted;
     launches += 5;
+    static const bool no_prune = std::getenv("BF_NO_PRUNE") != nullptr;
+    if (p.boxes && !cov && nb <= 12 && !no_prune) {
+      float* c = ar.take<float>(ld);
+      BF_WS(c);
+      prune_cut_kernel<<<blocks_for(ld), kT, 0, st>>>(n, ld, perm, starmin, tau, p.err_a, p.err_b, c);
+      cut = c;
+      ++launches;
+    }
   }
   tm.end(0);
   tm.begin();
@@ -312,7 +336,7 @@ extern "C" int bf_fit_batch(const bf_fit_plan* plan, int64_t n_stars, const doub
   // ---- dense sweep, group selection -----------------------------------------------------------
   float* gmin = ar.take_top<float>(static_cast<size_t>(p.n_groups) * ld);
   BF_WS(gmin);
-  int rc = dense(p.n_tiles, p.tiles, gmin);
+  int rc = dense(p.n_tiles, p.tiles, gmin, cut != nullptr);
   if (rc != BF_OK) return rc;
   tm.end(1);
   tm.begin();
@@ -323,7 +347,6 @@ extern "C" int bf_fit_batch(const bf_fit_plan* plan, int64_t n_stars, const doub
   uint32_t* off_star = ar.take<uint32_t>(n + 1);
   int64_t* n_listed = ar.take<int64_t>(n);
   BF_WS(n_listed);
-  const float tau = static_cast<float>(-2.0 * threshold);
   rc = bf_select_count(p.n_groups, n, ld, gmin, reinterpret_cast<uint64_t*>(starmin), tau, p.err_a, p.err_b, counts, stream);
   if (rc != BF_OK) return rc;
   rc = bf_exclusive_scan_u32(nc, counts, offsets, scan_tmp, stream);

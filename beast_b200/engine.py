@@ -104,6 +104,7 @@ class FitEngine:
         with torch.cuda.device(self.device):
             self.d_tiles = up(s.tiles)
             self.d_tiles_coarse = up(s.tiles_coarse)
+            self.d_boxes = up(s.boxes) if s.boxes is not None else None
             self.d_msb, self.d_ivar = up(s.msb), up(s.ivar)
             self.d_lnq, self.d_lnw = up(s.lnq), up(s.lnw)
             self.d_cov_off = up(s.cov_off) if s.cov_off is not None else None
@@ -155,6 +156,7 @@ class FitEngine:
         # per listed group: 64 weights + partials (+ the group order and the chunk lists)
         self.scratch_budget_bytes = int(scratch_budget_bytes)
         self.presort = True          # coarse sweep + star ordering inside bf_fit_batch
+        self.prune = True            # the dense sweep skips groups no star of a warp can select
         self.force_legacy = False    # True: never the class-split kernels (tests, measurements)
         self.launches = 0            # kernels launched by this engine (bench.py reports it)
         self._result_cache = {}
@@ -174,6 +176,8 @@ class FitEngine:
         p.n_tiles, p.tiles = int(self.d_tiles.shape[0]), self.d_tiles.data_ptr()
         if self.presort:
             p.n_tiles_coarse, p.tiles_coarse = int(self.d_tiles_coarse.shape[0]), self.d_tiles_coarse.data_ptr()
+            if self.prune and self.d_boxes is not None:
+                p.boxes = self.d_boxes.data_ptr()
         p.inv_band_scale = self.d_inv_scale.data_ptr()
         p.err_a, p.err_b = s.err_a, s.err_b
         p.grid, p.params = self.grid, self.params

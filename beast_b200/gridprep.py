@@ -126,6 +126,49 @@ def _pad_to(n, mult):
     return ((n + mult - 1) // mult) * mult
 
 
+def box_floats(nb):
+    """BF_BOX_FLOATS(nb) of include/beast_b200.h"""
+    return (3 * nb + 1 + 3) // 4 * 4
+
+
+def _group_boxes(rows, nm, nb):
+    """Per group of GROUP models a box around what the dense pass reads for them (the FP32 tile
+    rows r_b, -a_b, c2): the range of m_b = a_b / r_b, the smallest r_b and the smallest c2, each
+    rounded outwards, so that  acc >= sum_b rlo_b^2 dist(f_b, [mlo_b, mhi_b])^2 + c2min  for every
+    model of the group (bf_dense_chi2_pruned).  Padding models (c2 = 3e38) stay out of the box."""
+    nmp = rows.shape[1]
+    ng = nmp // GROUP
+    r = rows[:nb].astype(np.float64)
+    a = -rows[nb:2 * nb].astype(np.float64)
+    with np.errstate(divide="ignore", invalid="ignore"):
+        m = a / r
+    valid = np.arange(nmp) < nm
+    usable = valid[None, :] & np.isfinite(m)   # r = 0: the band does not constrain, rlo = 0 covers it
+    big = np.finfo(np.float32).max
+    mlo = np.where(usable, m, np.inf).reshape(nb, ng, GROUP).min(axis=2)
+    mhi = np.where(usable, m, -np.inf).reshape(nb, ng, GROUP).max(axis=2)
+    rlo = np.where(valid[None, :], r, np.inf).reshape(nb, ng, GROUP).min(axis=2)
+    c2min = rows[2 * nb].reshape(ng, GROUP).min(axis=1)
+    empty = ~np.isfinite(mlo) | ~np.isfinite(mhi)
+    mlo = np.where(empty, -big, mlo)
+    mhi = np.where(empty, big, mhi)
+    rlo = np.where(np.isfinite(rlo) & ~empty, rlo, 0.0)
+    lo32 = np.clip(mlo, -big, big).astype(np.float32)
+    hi32 = np.clip(mhi, -big, big).astype(np.float32)
+    with np.errstate(over="ignore"):
+        lo32 = np.where(lo32.astype(np.float64) > mlo, np.nextafter(lo32, np.float32(-np.inf)), lo32)
+        hi32 = np.where(hi32.astype(np.float64) < mhi, np.nextafter(hi32, np.float32(np.inf)), hi32)
+        # one more step outwards: the kernel's r and a are the FP32 values, but a / r above is rounded
+        lo32 = np.maximum(np.nextafter(lo32, np.float32(-np.inf)), -big).astype(np.float32)
+        hi32 = np.minimum(np.nextafter(hi32, np.float32(np.inf)), big).astype(np.float32)
+    out = np.zeros((ng, box_floats(nb)), dtype=np.float32)
+    out[:, :nb] = lo32.T
+    out[:, nb:2 * nb] = hi32.T
+    out[:, 2 * nb:3 * nb] = rlo.astype(np.float32).T   # r is FP32 already: exact
+    out[:, 3 * nb] = c2min
+    return out
+
+
 class FitSetup:
     """All star-independent inputs of the kernels, as NumPy arrays."""
 
@@ -279,6 +322,7 @@ class FitSetup:
         crow[:, :sub.shape[1]] = sub
         self.tiles_coarse = np.ascontiguousarray(
             crow.reshape(nrows, ncp // TILE_MODELS, TILE_MODELS).transpose(1, 0, 2))
+        self.boxes = None if self.full_cov else _group_boxes(rows, nm, nb)
         a_max = float(np.abs(a).max())
         # cross terms: every residual meets up to nb-1 others, with |O_kl| <= sqrt(D_k D_l)
         cov_factor = float(nb) if self.full_cov else 1.0

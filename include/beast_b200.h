@@ -33,6 +33,8 @@ extern "C" {
 #define BF_GROUP 64        /* models per group minimum                            */
 #define BF_CHUNK 8         /* models per parameter-table chunk                    */
 #define BF_STAR_BLOCK 1024 /* stars per thread block of the dense pass            */
+/* floats per group box of the pruned dense pass: mlo[nb], mhi[nb], rlo[nb], c2min, padded to 16 B */
+#define BF_BOX_FLOATS(nb) ((3 * (nb) + 1 + 3) / 4 * 4)
 #define BF_MAX_BANDS 16   /* array bound; the diagonal likelihood is built for 1..12 bands,
                              the full-covariance one for 2..8, trimming for 1..15 */
 #define BF_MAX_PARAMS 128
@@ -72,6 +74,26 @@ int bf_device_info(int device, int* sm_count, int* smem_optin_bytes, int* clock_
 int bf_dense_chi2(int nb, int64_t n_tiles, const float* tiles, int64_t n_stars,
                   int64_t ld_star, const float* flux, float* gmin, uint64_t* starmin,
                   int tiles_per_item, void* stream);
+
+/* The same sweep, leaving out what cannot matter.  A warp of the kernel owns 256 neighbouring
+ * stars; it skips a group when a lower bound of acc over the group's models is above the
+ * selection threshold of every one of them, and reports +inf for that group.  The bound comes
+ * from a box per group,
+ *   boxes : [n_tiles*BF_TILE_MODELS/BF_GROUP][BF_BOX_FLOATS(nb)] float, 16-byte aligned:
+ *           mlo_b <= a_b / r_b <= mhi_b and rlo_b <= r_b for every model of the group and band b,
+ *           c2min <= c2  (rounded outwards), so that
+ *           acc >= sum_b rlo_b^2 dist(f_b, [mlo_b, mhi_b])^2 + c2min;
+ *   cut   : [ld_star] float, per star a ceiling of its selection threshold on the acc scale
+ *           (bf_select_count's tau and error terms applied to any upper bound of the star's
+ *           minimum, e.g. the minimum over the coarse tiles); -1 for padding stars, +inf to
+ *           keep everything.
+ * Groups that bf_select_* would list get the same minimum as from bf_dense_chi2, the others
+ * +inf or their true minimum (both above the threshold), and starmin is the same, so the lists
+ * are identical.  Pays off when neighbouring stars are alike (bf_fit_batch orders them).
+ * No counterpart in the reference, which evaluates every model for every star. */
+int bf_dense_chi2_pruned(int nb, int64_t n_tiles, const float* tiles, const float* boxes,
+                         int64_t n_stars, int64_t ld_star, const float* flux, const float* cut,
+                         float* gmin, uint64_t* starmin, int tiles_per_item, void* stream);
 
 /* Same sweep for the full-covariance likelihood (N_covar_logLikelihood / N_covar_chi2,
  * fitting/fit_metrics/likelihood.py:58-106, 170-218; selected at fit.py:432-444).
@@ -351,6 +373,8 @@ int bf_pdf2d_from_weights(int64_t ld_model, int n_pairs, const int32_t* pair_bin
  *                   swept first to order the stars by where their best models lie -- results
  *                   come back in the caller's order either way
  *   inv_band_scale [nb] : 1 / s_b (device), turns flux64 into the FP32 fluxes of the dense pass
+ *   boxes         : see bf_dense_chi2_pruned; used when tiles_coarse is given too (its minima
+ *                   bound the selection thresholds), diagonal likelihood only
  *   pair_bin / pair_off / pair_len : 2D PDF tables (bf_pdf2d_accumulate), pair_len = pair_off[n_pairs]
  *   force_legacy  : 1 = do not use the class-split kernels even if `params` carries the split
  *   max_range_entries : the sparse pass works on ranges of stars whose lists fit the scratch;
@@ -388,6 +412,7 @@ typedef struct {
   int sm_count;
   int force_legacy;
   int64_t max_range_entries; /* 0, or a cap on the listed groups the sparse pass takes at a time */
+  const float* boxes;        /* group boxes for bf_dense_chi2_pruned, or NULL: sweep everything */
 } bf_fit_plan;
 
 typedef struct {

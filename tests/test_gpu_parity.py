@@ -201,6 +201,81 @@ def test_fit_batch_is_one_c_call_and_presort_is_invisible():
     util.compare_to_reference(setup, a, ref)
 
 
+def test_pruned_dense_sweep_leaves_the_fit_unchanged():
+    """the dense sweep that skips groups no star of a warp can select: the same lists, hence the
+    same fit bit for bit, on C1-sized stars (where most of the grid is skipped) and on the golden"""
+    from beast_b200 import synth
+
+    g, nz, obs, args, ref = util.load_golden("small_thr10")
+    setup, eng = _engine(g, nz, args)
+    assert eng.prune and eng.d_boxes is not None
+    a = eng.fit(obs.fluxes, threshold=args["threshold"], sparse=20, lnp_rng="device", seed=5)
+    eng.prune = False
+    b = eng.fit(obs.fluxes, threshold=args["threshold"], sparse=20, lnp_rng="device", seed=5)
+    _same_everything(a, b, ALL_OUT + ("sparse_off", "n_groups_selected"))
+
+    g, nz, obs = synth.make_config("C1", nstars=3000)
+    from beast_b200.engine import FitEngine
+    from beast_b200.gridprep import FitSetup
+    from oracle import fit_oracle as fo
+
+    setup = FitSetup(g, nz, list(fo.default_keys(g)), max_nbins=50)
+    eng = FitEngine(setup)
+    a = eng.fit(obs.fluxes, threshold=-10.0, sparse="all")
+    eng.prune = False
+    b = eng.fit(obs.fluxes, threshold=-10.0, sparse="all")
+    _same_everything(a, b, ALL_OUT + ("sparse_off", "n_groups_selected"))
+
+
+def test_pruned_dense_entry_point():
+    """bf_dense_chi2_pruned against bf_dense_chi2 on the same tiles: a group is either reported as
+    before or skipped (+inf), skipped only where its minimum is at or above the star's ceiling,
+    and the star minima (value and group) are the same"""
+    import torch
+
+    from beast_b200 import _cabi, synth
+    from beast_b200.gridprep import FitSetup
+
+    g, nz, obs = synth.make_config("C1", nstars=2048)
+    setup = FitSetup(g, nz, ["Av", "M_ini", "logT"], max_nbins=20)
+    dev = torch.device("cuda")
+    nb, n, ld = setup.nb, len(obs), 2048
+    # stars ordered by brightness so that a warp's 256 stars are alike
+    order = np.argsort(obs.fluxes.sum(axis=1))
+    flux = torch.from_numpy(np.ascontiguousarray((obs.fluxes[order] / setup.band_scale).T.astype(np.float32))).to(dev)
+    tiles = torch.from_numpy(setup.tiles).to(dev)
+    boxes = torch.from_numpy(setup.boxes).to(dev)
+    ng = setup.n_groups
+
+    def sweep(cut):
+        gmin = torch.empty((ng, ld), dtype=torch.float32, device=dev)
+        smin = torch.full((ld,), 0x7f800000ffffffff, dtype=torch.int64, device=dev)
+        st = torch.cuda.current_stream().cuda_stream
+        if cut is None:
+            _cabi.call("bf_dense_chi2", nb, setup.n_tiles, tiles.data_ptr(), n, ld, flux.data_ptr(),
+                       gmin.data_ptr(), smin.data_ptr(), 4, st)
+        else:
+            _cabi.call("bf_dense_chi2_pruned", nb, setup.n_tiles, tiles.data_ptr(), boxes.data_ptr(), n, ld,
+                       flux.data_ptr(), cut.data_ptr(), gmin.data_ptr(), smin.data_ptr(), 4, st)
+        torch.cuda.synchronize()
+        return gmin.cpu().numpy(), smin.cpu().numpy()
+
+    full, smin_full = sweep(None)
+    star_min = full.min(axis=0)
+    cut = torch.from_numpy((star_min + 25.0).astype(np.float32)).to(dev)
+    pruned, smin_pruned = sweep(cut)
+    np.testing.assert_array_equal(smin_pruned, smin_full)
+    skipped = np.isinf(pruned) & ~np.isinf(full)
+    assert skipped.mean() > 0.3            # the sweep does leave things out
+    np.testing.assert_array_equal(pruned[~skipped], full[~skipped])
+    assert np.all(full[skipped] >= np.broadcast_to(cut.cpu().numpy()[None, :], full.shape)[skipped])
+    # a ceiling of +inf keeps everything, -1 (padding stars) skips everything
+    same, _ = sweep(torch.full((ld,), float("inf"), device=dev))
+    np.testing.assert_array_equal(same, full)
+    none, _ = sweep(torch.full((ld,), -1.0, device=dev))
+    assert np.all(np.isinf(none))
+
+
 def _same_everything(a, b, names):
     for name in names:
         np.testing.assert_array_equal(getattr(a, name), getattr(b, name), err_msg=name)

@@ -66,6 +66,38 @@ def test_device_layouts(small):
     assert st.err_a > 0 and st.err_b > 0
 
 
+def test_group_boxes_bound_the_accumulator(small):
+    """the boxes of the pruned dense pass: for every star and group, the bound the kernel forms in
+    FP32 (times its 1 - 2^-16 slack) stays below the smallest accumulator of the group's models"""
+    from beast_b200 import gridprep
+
+    g, nz, obs = small
+    st = FitSetup(g, nz, ["Av", "M_ini", "logT"], max_nbins=20)
+    nb, nm = st.nb, st.n_models
+    ng = st.ld_model // gridprep.GROUP
+    assert st.boxes.shape == (ng, gridprep.box_floats(nb)) and st.boxes.dtype == np.float32
+    rows = st.tiles.transpose(1, 0, 2).reshape(2 * nb + 1, -1)
+    rng = np.random.default_rng(5)
+    stars = np.concatenate([obs.fluxes, obs.fluxes * rng.uniform(0.2, 5.0, obs.fluxes.shape),
+                            -obs.fluxes[:2], np.zeros((1, nb))])
+    f32 = np.float32
+    for f in stars:
+        fs = (f / st.band_scale).astype(f32)
+        acc = rows[2 * nb].astype(np.float64).copy()
+        for b in range(nb):
+            acc += (fs[b].astype(np.float64) * rows[b] + rows[nb + b]) ** 2
+        gmin = acc.reshape(ng, gridprep.GROUP).min(axis=1)
+        bx = st.boxes
+        lb = bx[:, 3 * nb].copy()
+        for b in range(nb):
+            u = np.maximum(np.maximum(bx[:, b] - fs[b], fs[b] - bx[:, nb + b]), f32(0))
+            d = (u * bx[:, 2 * nb + b]).astype(f32)
+            lb = (d.astype(np.float64) * d + lb).astype(f32)   # fmaf
+        assert np.all(lb.astype(np.float64) * 0.99998474 <= gmin * (1 + 1e-6) + 1e-30)
+    # the boxes are not vacuous: a star far from a group is bounded away from it
+    assert np.median(lb) > 10.0
+
+
 def test_bin_constant_parameters_regroup_the_expectation(small):
     """parameters whose bins each hold one value: sum_m w_m q_m = sum_b (sum_{m in b} w_m) q_b, the
     identity behind taking their expectation from the histogram (fit.py:743 vs pdf1d.py:142-147)"""
