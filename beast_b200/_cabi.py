@@ -117,6 +117,7 @@ class FitPlan(C.Structure):
         ("force_legacy", C.c_int),
         ("max_range_entries", i64),
         ("boxes", c_void_p),
+        ("sort_band", C.c_int),
     ]
 
 

@@ -23,7 +23,8 @@
 // box around each group's models (per band: the range of model fluxes m = a / r and the smallest
 // r; the smallest c2),
 //   acc(s, m) = sum_b r_mb^2 (f_sb - m_mb)^2 + c2_m >= sum_b rlo_b^2 dist(f_sb, [mlo_b, mhi_b])^2 + c2min
-// a warp skips a group that none of its 256 stars can select and reports +inf for it.  The
+// a warp skips a group that none of its 256 stars can select and reports +inf for it; within a
+// group it evaluates only those of its four star pairs (64 stars each) that hold such a star.  The
 // group lists that follow are the same ones: a skipped group's minimum is above the star's
 // selection threshold, and the group of the star's minimum is never skipped.
 
@@ -157,10 +158,11 @@ dense_chi2_kernel(const float* __restrict__ tiles, int64_t n_tiles, int tiles_pe
     for (int g = 0; g < GROUPS_PER_TILE; ++g) {
       const int64_t gidx = (t_begin + i) * GROUPS_PER_TILE + g;
       float* gp = gmin + gidx * ld_star + star0 + wbase;
+      unsigned need_mask = (1u << kNPair) - 1;
       if constexpr (PRUNE) {
         // can any star of this warp select a model of the group?  lower bound of acc per star
         const float* bx = box_buf + stage * (GROUPS_PER_TILE * BOXF) + g * BOXF;
-        bool need = false;
+        need_mask = 0;
 #pragma unroll
         for (int p = 0; p < kNPair; ++p) {
           float lo = bx[3 * NB], hi = lo;
@@ -175,10 +177,11 @@ dense_chi2_kernel(const float* __restrict__ tiles, int64_t n_tiles, int tiles_pe
             hi = fmaf(dh, dh, hi);
           }
           // 1 - 2^-16 covers the FP32 rounding of both this bound and the accumulators below
-          need |= lo * 0.99998474f < cut_s[wbase + (2 * p) * 32];
-          need |= hi * 0.99998474f < cut_s[wbase + (2 * p + 1) * 32];
+          const bool need = lo * 0.99998474f < cut_s[wbase + (2 * p) * 32] ||
+                            hi * 0.99998474f < cut_s[wbase + (2 * p + 1) * 32];
+          if (__any_sync(0xffffffffu, need)) need_mask |= 1u << p;  // the pair's 64 stars are evaluated
         }
-        if (!__any_sync(0xffffffffu, need)) {
+        if (need_mask == 0) {
 #pragma unroll
           for (int q = 0; q < 2 * kNPair; ++q) gp[q * 32] = kInf;
           continue;
@@ -196,6 +199,7 @@ dense_chi2_kernel(const float* __restrict__ tiles, int64_t n_tiles, int tiles_pe
           const float2 c2 = *reinterpret_cast<const float2*>(sb + 2 * NB * TM + m);
 #pragma unroll
           for (int p = 0; p < kNPair; ++p) {
+            if (PRUNE && !((need_mask >> p) & 1)) continue;  // warp-uniform
             f32x2 acc0 = pack2(c2.x, c2.x);
             f32x2 acc1 = pack2(c2.y, c2.y);
 #pragma unroll

@@ -124,6 +124,17 @@ __global__ void prune_cut_kernel(int64_t n, int64_t ld, const int32_t* __restric
   cut[i] = i < n ? select_threshold(starmin_value(starmin[perm[i]]), tau, err_a, err_b) : -1.0f;
 }
 
+// sort key = the star's flux in one band (IEEE bits made monotone; NaN last)
+__global__ void flux_keys_kernel(int64_t n, int nb, int band, const double* __restrict__ flux,
+                                 uint32_t* keys, int32_t* vals) {
+  const int64_t i = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const float v = static_cast<float>(flux[i * nb + band]);
+  const uint32_t u = __float_as_uint(v);
+  keys[i] = v != v ? 0xffffffffu : ((u & 0x80000000u) ? ~u : (u | 0x80000000u));
+  vals[i] = static_cast<int32_t>(i);
+}
+
 __global__ void iota_kernel(int64_t n, int32_t* vals) {
   const int64_t i = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x;
   if (i < n) vals[i] = static_cast<int32_t>(i);
@@ -314,7 +325,12 @@ extern "C" int bf_fit_batch(const bf_fit_plan* plan, int64_t n_stars, const doub
     size_t tbytes = sort_temp_bytes(n);
     void* temp = ar.take<char>(tbytes);
     BF_WS(temp);
-    argmin_keys_kernel<<<blocks_for(n), kT, 0, st>>>(n, starmin, keys, vals);
+    static const char* sort_env = std::getenv("BF_SORT_BAND");
+    const int sort_band = sort_env ? std::atoi(sort_env) : p.sort_band;
+    if (sort_band >= 0 && sort_band < nb)
+      flux_keys_kernel<<<blocks_for(n), kT, 0, st>>>(n, nb, sort_band, flux_in, keys, vals);
+    else
+      argmin_keys_kernel<<<blocks_for(n), kT, 0, st>>>(n, starmin, keys, vals);
     BF_CUDA_TRY(cub::DeviceRadixSort::SortPairs(temp, tbytes, keys, keys_out, vals, perm, static_cast<int>(n), 0, 32, st));
     gather_rows_kernel<<<blocks_for(n * nb), kT, 0, st>>>(n, nb, perm, flux_in, d_flux_sorted);
     flux_run = d_flux_sorted;

@@ -157,6 +157,7 @@ class FitEngine:
         self.scratch_budget_bytes = int(scratch_budget_bytes)
         self.presort = True          # coarse sweep + star ordering inside bf_fit_batch
         self.prune = True            # the dense sweep skips groups no star of a warp can select
+        self.sort_band = setup.sort_band if not setup.full_cov else -1   # -1: by coarse arg-min group
         self.force_legacy = False    # True: never the class-split kernels (tests, measurements)
         self.launches = 0            # kernels launched by this engine (bench.py reports it)
         self._result_cache = {}
@@ -185,6 +186,7 @@ class FitEngine:
             p.n_pairs, p.pair_len = len(s.pairs), int(s.pair_off[-1])
             p.pair_bin, p.pair_off = self.d_pair_bin.data_ptr(), self.d_pair_off.data_ptr()
         p.sm_count = self.sm_count
+        p.sort_band = self.sort_band
         p.force_legacy = int(self.force_legacy or not self.split)
         p.max_range_entries = int(getattr(self, "max_range_entries", 0))
         return p

@@ -323,6 +323,9 @@ class FitSetup:
         self.tiles_coarse = np.ascontiguousarray(
             crow.reshape(nrows, ncp // TILE_MODELS, TILE_MODELS).transpose(1, 0, 2))
         self.boxes = None if self.full_cov else _group_boxes(rows, nm, nb)
+        # the band whose flux orders the stars of a batch: the one the models are most significant
+        # in (stars differ most there in units of the noise, so neighbours rule out the same groups)
+        self.sort_band = int(np.argmax(np.median(np.abs(a), axis=0)))
         a_max = float(np.abs(a).max())
         # cross terms: every residual meets up to nb-1 others, with |O_kl| <= sqrt(D_k D_l)
         cov_factor = float(nb) if self.full_cov else 1.0

@@ -375,6 +375,9 @@ int bf_pdf2d_from_weights(int64_t ld_model, int n_pairs, const int32_t* pair_bin
  *   inv_band_scale [nb] : 1 / s_b (device), turns flux64 into the FP32 fluxes of the dense pass
  *   boxes         : see bf_dense_chi2_pruned; used when tiles_coarse is given too (its minima
  *                   bound the selection thresholds), diagonal likelihood only
+ *   sort_band     : with tiles_coarse, the stars are fitted in the order of their flux in this
+ *                   band (the one that tells stars apart best: neighbours then rule out the same
+ *                   groups); -1 orders them by the group of their coarse minimum instead
  *   pair_bin / pair_off / pair_len : 2D PDF tables (bf_pdf2d_accumulate), pair_len = pair_off[n_pairs]
  *   force_legacy  : 1 = do not use the class-split kernels even if `params` carries the split
  *   max_range_entries : the sparse pass works on ranges of stars whose lists fit the scratch;
@@ -413,6 +416,7 @@ typedef struct {
   int force_legacy;
   int64_t max_range_entries; /* 0, or a cap on the listed groups the sparse pass takes at a time */
   const float* boxes;        /* group boxes for bf_dense_chi2_pruned, or NULL: sweep everything */
+  int sort_band;             /* order the stars by their flux in this band; -1: by coarse arg-min group */
 } bf_fit_plan;
 
 typedef struct {

@@ -105,3 +105,25 @@ report("total log flux", by_flux0, 64, cmin)
 report("coarse arg-min model", by_model, 32, cmin)
 if tmin is not None:
     report("coarse arg-min model, true minimum", by_model, 64, tmin)
+
+if os.environ.get("KEYS"):
+    med = f.median(dim=0).values
+    sl = torch.asinh(f / med)          # symmetric log of the flux in units of the band's median
+    bright = sl.sum(1)
+    report("asinh brightness", torch.argsort(bright, stable=True), 64, cmin)
+    for b in range(nb):
+        report("asinh flux band %d" % b, torch.argsort(sl[:, b], stable=True), 64, cmin)
+    colour = sl[:, 0] - sl[:, nb - 1]
+
+    def quant(x, n):
+        r = torch.argsort(torch.argsort(x))
+        return (r * n // len(x)).to(torch.int64)
+
+    for nlev in (8, 32, 128):
+        key = quant(bright, nlev) * (1 << 20) + quant(colour, 1 << 20)
+        report("brightness in %d levels, then colour" % nlev, torch.argsort(key, stable=True), 64, cmin)
+    for nlev in (8, 32):
+        key = quant(colour, nlev) * (1 << 20) + quant(bright, 1 << 20)
+        report("colour in %d levels, then brightness" % nlev, torch.argsort(key, stable=True), 64, cmin)
+    key = (carg // 64) * (1 << 20) + quant(bright, 1 << 20)
+    report("coarse group, then brightness", torch.argsort(key, stable=True), 64, cmin)
