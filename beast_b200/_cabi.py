@@ -142,6 +142,7 @@ class FitState(C.Structure):
         ("launches", i64),
         ("split", C.c_int),
         ("n_ranges", C.c_int),
+        ("dense_evaluated", i64),
         ("want_timing", C.c_int),
         ("stage_ms", C.c_float * 12),
     ]
@@ -158,7 +159,7 @@ PROTOTYPES = {
     "bf_dense_chi2": (C.c_int, [C.c_int, i64, c_void_p, i64, i64, c_void_p, c_void_p, c_void_p,
                                 C.c_int, c_void_p]),
     "bf_dense_chi2_pruned": (C.c_int, [C.c_int, i64, c_void_p, c_void_p, i64, i64, c_void_p, c_void_p, c_void_p,
-                                       c_void_p, C.c_int, c_void_p]),
+                                       c_void_p, C.c_int, c_void_p, c_void_p]),
     "bf_dense_chi2_cov": (C.c_int, [C.c_int, i64, c_void_p, i64, i64, c_void_p, c_void_p, c_void_p,
                                     C.c_int, c_void_p]),
     "bf_dense_tiles_per_item": (C.c_int, [i64, i64, C.c_int]),

@@ -61,7 +61,7 @@ __global__ void __launch_bounds__(kDenseThreads, COV ? 2 : 3)
 dense_chi2_kernel(const float* __restrict__ tiles, int64_t n_tiles, int tiles_per_item,
                   const float* __restrict__ flux, int64_t ld_star, float* __restrict__ gmin,
                   unsigned long long* __restrict__ starmin, const float* __restrict__ boxes,
-                  const float* __restrict__ cut) {
+                  const float* __restrict__ cut, unsigned long long* __restrict__ evaluated) {
   constexpr int TM = BF_TILE_MODELS;
   using Smem = DenseSmem<NB, COV, PRUNE>;
   constexpr int ROWS = Smem::kRows;
@@ -139,6 +139,7 @@ dense_chi2_kernel(const float* __restrict__ tiles, int64_t n_tiles, int tiles_pe
     sgrp[q] = 0xffffffffu;
   }
 
+  unsigned n_eval = 0;
   for (int i = 0; i < nt; ++i) {
     const int stage = i % kDenseStages;
     // producer side (one thread): refill the stage that was consumed two iterations ago
@@ -160,6 +161,7 @@ dense_chi2_kernel(const float* __restrict__ tiles, int64_t n_tiles, int tiles_pe
       float* gp = gmin + gidx * ld_star + star0 + wbase;
       unsigned need_mask = (1u << kNPair) - 1;
       if constexpr (PRUNE) {
+        // (n_eval: star pairs x groups this warp evaluates, for the caller's statistics)
         // can any star of this warp select a model of the group?  lower bound of acc per star
         const float* bx = box_buf + stage * (GROUPS_PER_TILE * BOXF) + g * BOXF;
         need_mask = 0;
@@ -186,6 +188,7 @@ dense_chi2_kernel(const float* __restrict__ tiles, int64_t n_tiles, int tiles_pe
           for (int q = 0; q < 2 * kNPair; ++q) gp[q * 32] = kInf;
           continue;
         }
+        n_eval += __popc(need_mask);
       }
       if constexpr (!COV) {
 #pragma unroll 2
@@ -270,6 +273,10 @@ dense_chi2_kernel(const float* __restrict__ tiles, int64_t n_tiles, int tiles_pe
     if ((tid & 31) == 0) mbar_arrive(&empty_bar[stage]);
   }
 
+  if constexpr (PRUNE) {
+    if (evaluated != nullptr && lane == 0 && n_eval > 0)  // (star, model) pairs: 64 stars x BF_GROUP models each
+      atomicAdd(evaluated, static_cast<unsigned long long>(n_eval) * (64 * BF_GROUP));
+  }
   // acc >= 0 always (chi2 >= 0, c2 >= 0), so the IEEE bit pattern orders like the value;
   // packed as (value bits << 32 | group) one 64-bit atomicMin keeps the arg-min group too
 #pragma unroll
@@ -285,7 +292,8 @@ dense_chi2_kernel(const float* __restrict__ tiles, int64_t n_tiles, int tiles_pe
 template <int NB, bool COV, bool PRUNE = false>
 static int launch_dense(int64_t n_tiles, const float* tiles, int64_t ld_star, const float* flux,
                         float* gmin, unsigned long long* starmin, int tiles_per_item,
-                        cudaStream_t st, const float* boxes = nullptr, const float* cut = nullptr) {
+                        cudaStream_t st, const float* boxes = nullptr, const float* cut = nullptr,
+                        unsigned long long* evaluated = nullptr) {
   auto kern = dense_chi2_kernel<NB, COV, PRUNE>;
   static bool configured[64] = {};
   int dev = 0;
@@ -298,7 +306,7 @@ static int launch_dense(int64_t n_tiles, const float* tiles, int64_t ld_star, co
   const int64_t n_items = (n_tiles + tiles_per_item - 1) / tiles_per_item;
   dim3 grid(static_cast<unsigned>(n_items), static_cast<unsigned>(ld_star / BF_STAR_BLOCK));
   kern<<<grid, kDenseThreads, DenseSmem<NB, COV, PRUNE>::kBytes, st>>>(
-      tiles, n_tiles, tiles_per_item, flux, ld_star, gmin, starmin, boxes, cut);
+      tiles, n_tiles, tiles_per_item, flux, ld_star, gmin, starmin, boxes, cut, evaluated);
   BF_CHECK_LAUNCH("dense_chi2_kernel");
   return BF_OK;
 }
@@ -373,7 +381,7 @@ extern "C" int bf_dense_chi2_cov(int nb, int64_t n_tiles, const float* tiles, in
 extern "C" int bf_dense_chi2_pruned(int nb, int64_t n_tiles, const float* tiles, const float* boxes,
                                     int64_t n_stars, int64_t ld_star, const float* flux,
                                     const float* cut, float* gmin, uint64_t* starmin,
-                                    int tiles_per_item, void* stream) {
+                                    int tiles_per_item, uint64_t* evaluated, void* stream) {
   using namespace bf;
   BF_REQUIRE(nb >= 1 && nb <= 12, "bf_dense_chi2_pruned: nb=%d not instantiated (1..12)", nb);
   BF_REQUIRE(n_tiles > 0 && n_stars > 0, "bf_dense_chi2_pruned: empty problem");
@@ -388,7 +396,8 @@ extern "C" int bf_dense_chi2_pruned(int nb, int64_t n_tiles, const float* tiles,
   switch (nb) {
 #define BF_CASE(N) \
   case N:          \
-    return launch_dense<N, false, true>(n_tiles, tiles, ld_star, flux, gmin, sm, tiles_per_item, st, boxes, cut);
+    return launch_dense<N, false, true>(n_tiles, tiles, ld_star, flux, gmin, sm, tiles_per_item, st, boxes, cut, \
+                                        reinterpret_cast<unsigned long long*>(evaluated));
     BF_CASE(1) BF_CASE(2) BF_CASE(3) BF_CASE(4) BF_CASE(5) BF_CASE(6) BF_CASE(7) BF_CASE(8)
     BF_CASE(9) BF_CASE(10) BF_CASE(11) BF_CASE(12)
 #undef BF_CASE

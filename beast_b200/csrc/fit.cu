@@ -223,7 +223,7 @@ extern "C" int64_t bf_fit_workspace_bytes(const bf_fit_plan* plan, int64_t n_sta
   b += 2 * static_cast<size_t>(n_stars) * p.nb * 8;            // flux copies
   b += static_cast<size_t>(p.nb) * ld * 4;                      // flux32
   b += static_cast<size_t>(p.n_tiles) * (BF_TILE_MODELS / BF_GROUP) * ld * 4;  // group minima
-  b += static_cast<size_t>(ld) * 12;                            // starmin, selection ceilings
+  b += static_cast<size_t>(ld) * 12 + 256;                      // starmin, selection ceilings, counter
   b += (2 * static_cast<size_t>(n_stars) * BF_SELECT_SPLIT + 2) * 4 + bf_scan_scratch_elems(n_stars * BF_SELECT_SPLIT) * 4;
   b += static_cast<size_t>(n_stars) * (4 * 4 + 4 + 8 + 4) + 2 * sort_temp_bytes(n_stars);
   // results in sorted order
@@ -299,13 +299,14 @@ extern "C" int bf_fit_batch(const bf_fit_plan* plan, int64_t n_stars, const doub
   const bool cov = p.full_cov != 0;
   const float tau = static_cast<float>(-2.0 * threshold);
   const float* cut = nullptr;  // set by the presort when the dense sweep may skip groups
+  uint64_t* evaluated = nullptr;
   auto dense = [&](int64_t n_tiles, const float* tiles, float* gmin, bool prune) -> int {
     starmin_init_kernel<<<blocks_for(ld), kT, 0, st>>>(ld, starmin);
     const int tpi = bf_dense_tiles_per_item(n_tiles, n, sm_count);
     launches += 2;
     if (prune)
       return bf_dense_chi2_pruned(nb, n_tiles, tiles, p.boxes, n, ld, flux32, cut, gmin,
-                                  reinterpret_cast<uint64_t*>(starmin), tpi, stream);
+                                  reinterpret_cast<uint64_t*>(starmin), tpi, evaluated, stream);
     return cov ? bf_dense_chi2_cov(nb, n_tiles, tiles, n, ld, flux32, gmin, reinterpret_cast<uint64_t*>(starmin), tpi, stream)
                : bf_dense_chi2(nb, n_tiles, tiles, n, ld, flux32, gmin, reinterpret_cast<uint64_t*>(starmin), tpi, stream);
   };
@@ -338,7 +339,9 @@ extern "C" int bf_fit_batch(const bf_fit_plan* plan, int64_t n_stars, const doub
     static const bool no_prune = std::getenv("BF_NO_PRUNE") != nullptr;
     if (p.boxes && !cov && nb <= 12 && !no_prune) {
       float* c = ar.take<float>(ld);
-      BF_WS(c);
+      evaluated = ar.take<uint64_t>(1);
+      BF_WS(evaluated);
+      BF_CUDA_TRY(cudaMemsetAsync(evaluated, 0, sizeof(uint64_t), st));
       prune_cut_kernel<<<blocks_for(ld), kT, 0, st>>>(n, ld, perm, starmin, tau, p.err_a, p.err_b, c);
       cut = c;
       ++launches;
@@ -371,6 +374,9 @@ extern "C" int bf_fit_batch(const bf_fit_plan* plan, int64_t n_stars, const doub
   launches += 5;
   std::vector<uint32_t> off_host(n + 1);
   BF_CUDA_TRY(cudaMemcpyAsync(off_host.data(), off_star, (n + 1) * sizeof(uint32_t), cudaMemcpyDeviceToHost, st));
+  uint64_t evaluated_host = static_cast<uint64_t>(ld) * static_cast<uint64_t>(p.n_groups) * BF_GROUP;
+  if (evaluated)
+    BF_CUDA_TRY(cudaMemcpyAsync(&evaluated_host, evaluated, sizeof(uint64_t), cudaMemcpyDeviceToHost, st));
   BF_CUDA_TRY(cudaStreamSynchronize(st));  // the list sizes decide the layout of everything below
   const int64_t total = off_host[n];
   const int64_t tot1 = total > 0 ? total : 1;
@@ -558,6 +564,7 @@ extern "C" int bf_fit_batch(const bf_fit_plan* plan, int64_t n_stars, const doub
     state->launches = launches;
     state->split = split ? 1 : 0;
     state->n_ranges = n_ranges;
+    state->dense_evaluated = static_cast<int64_t>(evaluated_host);
   }
 #undef BF_WS
   return BF_OK;

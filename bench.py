@@ -332,9 +332,11 @@ def run_ours(args, rank, world, local_rank):
     stage_tot, stage_cnt = eng.stage_ms()
     eng.profile = False
     n_list = 0
+    dense_evaluated = 0
     for (a, b), df in zip(batches, d_flux):  # listed groups of the catalog (for the rooflines)
         eng.fit_batch(df, THRESHOLD)
         n_list += int(eng.last_state[1].n_list)
+        dense_evaluated += int(eng.last_state[1].dense_evaluated)
 
     # ---- end to end through the reference-facing call: Q_all_memory with host objects in and
     # the reference's result arrays back on the host, every step ------------------------------
@@ -408,16 +410,23 @@ def run_ours(args, rank, world, local_rank):
         return stage_tot.get(name, 0.0) / max(nbat, 1)
 
     dense_ms = per_launch("dense")
-    evals_per_launch = stars * setup.ld_model / nbat
-    dense_tf = flop_per_eval * evals_per_launch / (dense_ms * 1e-3) / 1e12 if dense_ms else None
     ld = -(-int(stars / nbat) // 1024) * 1024
+    # the pruned sweep reports the (star, model) pairs it evaluated (padding included); the
+    # roofline counts those, not the pairs it could rule out
+    evals_all = float(nbat) * ld * setup.ld_model
+    evals_per_launch = dense_evaluated / nbat
+    dense_tf = flop_per_eval * evals_per_launch / (dense_ms * 1e-3) / 1e12 if dense_ms else None
     dense_traffic = (ld // 1024) * setup.tiles.nbytes + setup.n_groups * ld * 4
     peak_note = "%d SMs x 128 FP32 lanes x 2 x sm_max_mhz (%s); MEASURED_PEAKS.json has no FP32 entry" % (
         eng.sm_count, peak_src)
     r_dense = {"bound": "fp32", "kernel": "dense_chi2_kernel", "achieved": dense_tf, "peak": peak_tf,
                "unit": "TFLOP/s", "frac": (dense_tf / peak_tf) if dense_tf else None,
                "traffic": int(dense_traffic), "ms_per_step": stage_tot.get("dense", 0.0),
-               "work": "%d flop per star x model (2 nb + 1 FMA)" % flop_per_eval, "peak_source": peak_note,
+               "work": "%d flop per evaluated star x model (2 nb + 1 FMA); the sweep evaluated %.3g of %.3g "
+                       "pairs (the others ruled out per group by a lower bound, 5 nb + 2 flop per star x group, "
+                       "not counted)" % (flop_per_eval, dense_evaluated, evals_all),
+               "evaluated_fraction": dense_evaluated / evals_all if evals_all else None,
+               "peak_source": peak_note,
                "traffic_note": "bytes per launch = star blocks x tile bytes + group-minimum map; equals ncu "
                                "dram__bytes of the kernel (profiles/r01_dense_chi2_ncu.md)"}
     # exact weights: every listed model's FP64 rows (2 nb + 2 doubles) are needed once, every
@@ -453,7 +462,9 @@ def run_ours(args, rank, world, local_rank):
     roofline["stage_share_of_step"] = {k: v / stage_sum for k, v in stage_tot.items()}
     roofline["stage_note"] = ("stage times from one extra step in which bf_fit_batch synchronises after every "
                               "stage; their sum is %.1f ms against %.1f ms for the timed step" % (stage_sum, ms_step))
-    # the metric BASELINE.json states: fraction of the FP32 pipe peak for the whole fit
+    # the metric BASELINE.json states: fraction of the FP32 pipe peak for the whole fit, i.e. the
+    # reference's work (every star against every model) per second over the peak -- with the pruned
+    # sweep this is a rate of results, not a pipe utilisation (that is r_dense["frac"])
     roofline["frac_of_fp32_peak"] = flop_per_eval * stars * nm / (ms_step * 1e-3) / 1e12 / peak_tf
 
     # ---- the step before the fit: trim_models flags pass, HBM-bound (fitting/trim_grid.py) -----

@@ -90,10 +90,13 @@ int bf_dense_chi2(int nb, int64_t n_tiles, const float* tiles, int64_t n_stars,
  * Groups that bf_select_* would list get the same minimum as from bf_dense_chi2, the others
  * +inf or their true minimum (both above the threshold), and starmin is the same, so the lists
  * are identical.  Pays off when neighbouring stars are alike (bf_fit_batch orders them).
+ *   evaluated : optional device counter (may be NULL), raised by the number of (star, model)
+ *           pairs the sweep did evaluate (padding stars and models included)
  * No counterpart in the reference, which evaluates every model for every star. */
 int bf_dense_chi2_pruned(int nb, int64_t n_tiles, const float* tiles, const float* boxes,
                          int64_t n_stars, int64_t ld_star, const float* flux, const float* cut,
-                         float* gmin, uint64_t* starmin, int tiles_per_item, void* stream);
+                         float* gmin, uint64_t* starmin, int tiles_per_item, uint64_t* evaluated,
+                         void* stream);
 
 /* Same sweep for the full-covariance likelihood (N_covar_logLikelihood / N_covar_chi2,
  * fitting/fit_metrics/likelihood.py:58-106, 170-218; selected at fit.py:432-444).
@@ -451,6 +454,8 @@ typedef struct {
   int64_t launches;               /* kernels launched by the call */
   int split;                      /* 1: the class-split kernels ran */
   int n_ranges;                   /* ranges of stars the sparse pass was cut into */
+  int64_t dense_evaluated;        /* (star, model) pairs the dense sweep evaluated; n_stars padded to
+                                     BF_STAR_BLOCK times the padded model count when nothing was skipped */
   int want_timing;                /* in: 1 = fill stage_ms (the call then synchronises the stream
                                      after every stage; for measurements) */
   float stage_ms[12];             /* device time per stage: presort, dense, select, exact_max,

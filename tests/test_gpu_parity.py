@@ -247,7 +247,10 @@ def test_pruned_dense_entry_point():
     boxes = torch.from_numpy(setup.boxes).to(dev)
     ng = setup.n_groups
 
+    count = torch.zeros(1, dtype=torch.int64, device=dev)
+
     def sweep(cut):
+        count.zero_()
         gmin = torch.empty((ng, ld), dtype=torch.float32, device=dev)
         smin = torch.full((ld,), 0x7f800000ffffffff, dtype=torch.int64, device=dev)
         st = torch.cuda.current_stream().cuda_stream
@@ -256,7 +259,7 @@ def test_pruned_dense_entry_point():
                        gmin.data_ptr(), smin.data_ptr(), 4, st)
         else:
             _cabi.call("bf_dense_chi2_pruned", nb, setup.n_tiles, tiles.data_ptr(), boxes.data_ptr(), n, ld,
-                       flux.data_ptr(), cut.data_ptr(), gmin.data_ptr(), smin.data_ptr(), 4, st)
+                       flux.data_ptr(), cut.data_ptr(), gmin.data_ptr(), smin.data_ptr(), 4, count.data_ptr(), st)
         torch.cuda.synchronize()
         return gmin.cpu().numpy(), smin.cpu().numpy()
 
@@ -268,10 +271,14 @@ def test_pruned_dense_entry_point():
     skipped = np.isinf(pruned) & ~np.isinf(full)
     assert skipped.mean() > 0.3            # the sweep does leave things out
     np.testing.assert_array_equal(pruned[~skipped], full[~skipped])
+    # the counter: whole pairs of 32 + 32 stars are evaluated, so it lies between the groups
+    # reported and everything
+    assert (~np.isinf(pruned)).sum() * 64 <= int(count.item()) < 0.7 * ng * 64 * ld
     assert np.all(full[skipped] >= np.broadcast_to(cut.cpu().numpy()[None, :], full.shape)[skipped])
     # a ceiling of +inf keeps everything, -1 (padding stars) skips everything
     same, _ = sweep(torch.full((ld,), float("inf"), device=dev))
     np.testing.assert_array_equal(same, full)
+    assert int(count.item()) == ng * 64 * ld
     none, _ = sweep(torch.full((ld,), -1.0, device=dev))
     assert np.all(np.isinf(none))
 
