@@ -360,11 +360,26 @@ class FitEngine:
                 res.sparse_off = np.zeros(res.ns + 1, dtype=np.int64)
             if "_sp_j" in t:  # records land in the preallocated arrays as the batches finish
                 res.sparse_j, res.sparse_lnp, res.sparse_chi2 = res._sp_j, res._sp_lnp, res._sp_chi2
+        n_batches = -(-ns // bs)
+        # record offsets of every batch, staged in page-locked memory: they are small and go first
+        # on the copy stream, so that nothing on the host waits behind a batch's 1D PDFs
+        off_stage = torch.empty((n_batches, bs + 1), dtype=torch.int64, pin_memory=True) if sparse is not None else None
+        settled = [0]
+        spans = []
+
+        def settle(upto):  # offsets of the batches [settled, upto), whose copies have arrived
+            off = res.sparse_off
+            for i in range(settled[0], upto):
+                lo, hi = spans[i]
+                off[lo + 1:hi + 1] = off[lo] + off_stage[i, 1:hi - lo + 1].numpy()
+                off[hi + 1:] = off[hi]
+            settled[0] = max(settled[0], upto)
+
         with torch.cuda.device(self.device):
             main = torch.cuda.current_stream(self.device)
             copy_stream = self._copy_stream
             pending = None
-            for a in range(0, ns, bs):
+            for i, a in enumerate(range(0, ns, bs)):
                 b = min(ns, a + bs)
                 o = self.fit_batch(fluxes[a:b], threshold, percentiles, want_pdf2d, sparse, rng,
                                    lnp_rng, seed, row_offset + a)
@@ -372,7 +387,11 @@ class FitEngine:
                 done.record(main)
                 copy_stream.wait_event(done)
                 lo, hi = row_offset + a, row_offset + b
+                spans.append((lo, hi))
                 with torch.cuda.stream(copy_stream):
+                    if sparse is not None:
+                        o["sparse_off"].record_stream(copy_stream)
+                        off_stage[i, :hi - lo + 1].copy_(o["sparse_off"], non_blocking=True)
                     names = ["Pmax", "Pmax_j", "total_log_norm", "chi2min", "chi2min_j", "n_sparse",
                              "n_groups_selected", "exp_vals", "per_vals", "pdf1d"]
                     if pair_len:
@@ -382,9 +401,6 @@ class FitEngine:
                         t[name][lo:hi].copy_(o[name], non_blocking=True)
                     if sparse is not None:
                         nrec = int(o["sparse_j"].shape[0])
-                        off = res.sparse_off
-                        off[lo + 1:hi + 1] = off[lo] + o["sparse_off"].cpu().numpy()[1:]
-                        off[hi + 1:] = off[hi]
                         if "_sp_j" in t and sp_pos + nrec <= t["_sp_j"].shape[0]:
                             for name, src in (("_sp_j", "sparse_j"), ("_sp_lnp", "sparse_lnp"),
                                               ("_sp_chi2", "sparse_chi2")):
@@ -400,10 +416,14 @@ class FitEngine:
                 if on_batch is not None:
                     if pending is not None:  # the previous batch has had a whole batch to arrive
                         pending[0].synchronize()
+                        if sparse is not None:
+                            settle(i)
                         on_batch(pending[1], pending[2])
                     pending = (arrived, lo, hi)
             copy_stream.synchronize()
             main.synchronize()
+            if sparse is not None:
+                settle(n_batches)
             if on_batch is not None and pending is not None:
                 on_batch(pending[1], pending[2])
         if sparse is not None:
