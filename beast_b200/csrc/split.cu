@@ -423,8 +423,9 @@ __device__ __align__(16) const double g_zero_weights[8] = {0, 0, 0, 0, 0, 0, 0, 
 // (Four at a time, as in hist_window_kernel, costs 44 instructions per four models -- most of
 // them for the six pairwise bin comparisons -- against 24 here; this kernel has few warps per
 // SM when the private copies are large and is bound by instruction issue, not by the chain.)
-__device__ __forceinline__ void add_two(uint32_t col_s, uint32_t b0, uint32_t b1, double w0, double w1) {
-  const uint32_t a0 = col_s + b0 * 128u, a1 = col_s + b1 * 128u;
+__device__ __forceinline__ void add_two(uint32_t col_s, uint32_t b0, uint32_t b1, double w0, double w1,
+                                        uint32_t bin_stride = 128u) {
+  const uint32_t a0 = col_s + b0 * bin_stride, a1 = col_s + b1 * bin_stride;
   double h0, h1;
   asm volatile("ld.shared.f64 %0, [%1];" : "=d"(h0) : "r"(a0));
   asm volatile("ld.shared.f64 %0, [%1];" : "=d"(h1) : "r"(a1));
@@ -437,12 +438,15 @@ __device__ __forceinline__ void add_two(uint32_t col_s, uint32_t b0, uint32_t b1
   asm volatile("st.shared.f64 [%0], %1;" ::"r"(a1), "d"(h1));
 }
 
-__device__ __forceinline__ void add_chunk(uint32_t col_s, const FastRows& r) {
-  const uint32_t bx = r.bins.x, by = r.bins.y;
-  add_two(col_s, bx & 0xffu, (bx >> 8) & 0xffu, r.w[0], r.w[1]);
-  add_two(col_s, (bx >> 16) & 0xffu, bx >> 24, r.w[2], r.w[3]);
-  add_two(col_s, by & 0xffu, (by >> 8) & 0xffu, r.w[4], r.w[5]);
-  add_two(col_s, (by >> 16) & 0xffu, by >> 24, r.w[6], r.w[7]);
+// (a lane without a parameter has bin_mask = 0 and adds into the one bin of its column: applied
+// here as a bin stride of 0, not where the bins are loaded -- an operation on a freshly loaded
+// register makes the warp wait for the load on the spot, which is what the pipeline must avoid)
+__device__ __forceinline__ void add_chunk(uint32_t col_s, const FastRows& r, uint32_t bin_mask) {
+  const uint32_t bx = r.bins.x, by = r.bins.y, st = bin_mask & 128u;
+  add_two(col_s, bx & 0xffu, (bx >> 8) & 0xffu, r.w[0], r.w[1], st);
+  add_two(col_s, (bx >> 16) & 0xffu, bx >> 24, r.w[2], r.w[3], st);
+  add_two(col_s, by & 0xffu, (by >> 8) & 0xffu, r.w[4], r.w[5], st);
+  add_two(col_s, (by >> 16) & 0xffu, by >> 24, r.w[6], r.w[7], st);
 }
 
 // A fast warp: chunks first*SLOTS + h, then every nfw*SLOTS-th, of the star's member chunks.
@@ -456,7 +460,7 @@ __device__ __forceinline__ void fast_accumulate(const uint8_t* __restrict__ bins
                                                 uint32_t bin_mask, const double* __restrict__ weights,
                                                 const uint2* refs, uint32_t n_mc, uint32_t first,
                                                 uint32_t nfw, int lane, double* col,
-                                                volatile uint32_t* progress) {
+                                                volatile uint32_t* progress, bool far_on) {
   const uint32_t h = SLOTS == 2 ? static_cast<uint32_t>(lane >> 4) : 0u;
   const uint32_t step = nfw * SLOTS;
   const uint32_t col_s = static_cast<uint32_t>(__cvta_generic_to_shared(col));
@@ -465,18 +469,22 @@ __device__ __forceinline__ void fast_accumulate(const uint8_t* __restrict__ bins
   const uint32_t n_steps = (n_mc - start + step - 1) / step;
   const uint32_t last = n_mc - 1;
   uint32_t i = start + h;  // this lane's position of the step whose reference is read next
-  auto next_ref = [&](bool& valid) {
-    valid = i <= last;
-    const uint2 r = refs[valid ? i : last];
+  // (a position past the end of the list: the last chunk's bins with the marker y = ~0, which the
+  //  row load turns into zero weights -- no separate flag to keep in a register)
+  auto next_ref = [&]() {
+    const bool valid = i <= last;
+    uint2 r = refs[valid ? i : last];
+    if (!valid) r.y = 0xffffffffu;
     i += step;
     return r;
   };
-  auto load = [&](uint2 ref, bool valid, FastRows& r) {
-    const double2* wp = valid ? reinterpret_cast<const double2*>(weights + static_cast<size_t>(ref.y) * BF_CHUNK)
-                              : reinterpret_cast<const double2*>(g_zero_weights);
+  auto load = [&](uint2 ref, FastRows& r) {
+    const double2* wp = ref.y != 0xffffffffu
+                            ? reinterpret_cast<const double2*>(weights + static_cast<size_t>(ref.y) * BF_CHUNK)
+                            : reinterpret_cast<const double2*>(g_zero_weights);
     const double2 a = __ldg(wp), b = __ldg(wp + 1), c = __ldg(wp + 2), d = __ldg(wp + 3);
     const uint2 bb = __ldg(reinterpret_cast<const uint2*>(bins_lane + static_cast<size_t>(ref.x) * row_bytes));
-    r.bins = make_uint2(bb.x & bin_mask, bb.y & bin_mask);
+    r.bins = bb;
     r.w[0] = a.x; r.w[1] = a.y; r.w[2] = b.x; r.w[3] = b.y;
     r.w[4] = c.x; r.w[5] = c.y; r.w[6] = d.x; r.w[7] = d.y;
   };
@@ -484,52 +492,66 @@ __device__ __forceinline__ void fast_accumulate(const uint8_t* __restrict__ bins
   // consumed, and two sets of three chunk references in turn, requested a whole round before
   // they are needed as addresses: no register copy and no address ever waits for a load that
   // was issued less than three steps earlier.
+  // Further ahead still (kFarAhead steps) the rows are only pulled into L2, so that the loads
+  // above meet L2 latency instead of DRAM latency: the reference of step t + kFarAhead + 1 is
+  // requested while the rows of step t + kFarAhead are prefetched, one register pair in all.
+  constexpr uint32_t kFarAhead = 12;
+  uint32_t ifar = start + h + kFarAhead * step;
+  uint2 far = refs[ifar <= last ? ifar : last];
+  auto prefetch_far = [&]() {
+    if (ifar <= last) {
+      asm volatile("prefetch.global.L2 [%0];" ::"l"(weights + static_cast<size_t>(far.y) * BF_CHUNK));
+      asm volatile("prefetch.global.L2 [%0];" ::"l"(bins_lane + static_cast<size_t>(far.x) * row_bytes));
+    }
+    ifar += step;
+    far = refs[ifar <= last ? ifar : last];
+  };
   FastRows r0, r1, r2;
   uint2 qa0, qa1, qa2, qb0, qb1, qb2;
-  bool va0, va1, va2, vb0, vb1, vb2;
-  {
-    bool v;
-    uint2 ref = next_ref(v);
-    load(ref, v, r0);
-    ref = next_ref(v);
-    load(ref, v, r1);
-    ref = next_ref(v);
-    load(ref, v, r2);
-  }
-  qa0 = next_ref(va0);
-  qa1 = next_ref(va1);
-  qa2 = next_ref(va2);
+  load(next_ref(), r0);
+  load(next_ref(), r1);
+  load(next_ref(), r2);
+  qa0 = next_ref();
+  qa1 = next_ref();
+  qa2 = next_ref();
   for (uint32_t t = 0; t < n_steps; t += 6) {
     if (progress && lane == 0) *progress = start + t * step;  // (the prefetching warps follow it)
-    qb0 = next_ref(vb0);
-    qb1 = next_ref(vb1);
-    qb2 = next_ref(vb2);
-    add_chunk(col_s, r0);
-    load(qa0, va0, r0);
+    qb0 = next_ref();
+    qb1 = next_ref();
+    qb2 = next_ref();
+    add_chunk(col_s, r0, bin_mask);
+    load(qa0, r0);
+    if (far_on) prefetch_far();
     if (t + 1 < n_steps) {
-      add_chunk(col_s, r1);
-      load(qa1, va1, r1);
+      add_chunk(col_s, r1, bin_mask);
+      load(qa1, r1);
+      if (far_on) prefetch_far();
     }
     if (t + 2 < n_steps) {
-      add_chunk(col_s, r2);
-      load(qa2, va2, r2);
+      add_chunk(col_s, r2, bin_mask);
+      load(qa2, r2);
+      if (far_on) prefetch_far();
     }
     if (t + 3 >= n_steps) break;
-    qa0 = next_ref(va0);
-    qa1 = next_ref(va1);
-    qa2 = next_ref(va2);
-    add_chunk(col_s, r0);
-    load(qb0, vb0, r0);
+    qa0 = next_ref();
+    qa1 = next_ref();
+    qa2 = next_ref();
+    add_chunk(col_s, r0, bin_mask);
+    load(qb0, r0);
+    if (far_on) prefetch_far();
     if (t + 4 < n_steps) {
-      add_chunk(col_s, r1);
-      load(qb1, vb1, r1);
+      add_chunk(col_s, r1, bin_mask);
+      load(qb1, r1);
+      if (far_on) prefetch_far();
     }
     if (t + 5 < n_steps) {
-      add_chunk(col_s, r2);
-      load(qb2, vb2, r2);
+      add_chunk(col_s, r2, bin_mask);
+      load(qb2, r2);
+      if (far_on) prefetch_far();
     }
   }
 }
+
 
 constexpr int kSlowBatch = 4;  // runs per lane and step of a slow warp
 struct SlowRefs {
@@ -696,7 +718,7 @@ __device__ __forceinline__ void class_ranges(const bf_param_tables& prm, const u
 
 template <int FS, int SS>  // chunk slots per instruction of the fast / slow class (1 or 2)
 __global__ void __launch_bounds__(kSplitWarpsMax * 32, 1)
-split_hist_kernel(bf_param_tables prm, int hist_doubles, uint32_t seg_chunks, const double* __restrict__ pmax,
+split_hist_kernel(bf_param_tables prm, int hist_doubles, uint32_t seg_chunks_far, const double* __restrict__ pmax,
                   const uint32_t* __restrict__ offsets, const uint32_t* __restrict__ list,
                   const int32_t* __restrict__ star_order, int64_t star_begin, int64_t entry_base,
                   bf_accum_scratch sc, double p0, double p1, double p2, bf_star_outputs out) {
@@ -795,6 +817,10 @@ split_hist_kernel(bf_param_tables prm, int hist_doubles, uint32_t seg_chunks, co
   // narrower than the whole star's, the private copies smaller, and more warps get one -- a
   // broad star as a whole leaves room for 8 fast warps of 20.  Every segment adds its merged
   // copies to the star's pdf rows (in global memory, not normalised yet).
+  // (top two bits: who prefetches into L2 -- 0 the fast warps unless four idle warps do it,
+  //  1 nobody but idle warps, 2 the fast warps always; measurements)
+  const uint32_t seg_chunks = seg_chunks_far & 0x3fffffffu;
+  const uint32_t far_mode = seg_chunks_far >> 30;
   const uint32_t n_seg = n_mc > seg_chunks + seg_chunks / 2 ? (n_mc + seg_chunks / 2) / seg_chunks : 1u;
   const uint32_t seg_len = (n_mc + n_seg - 1) / n_seg;
   for (uint32_t seg = 0; seg < n_seg; ++seg) {
@@ -880,7 +906,8 @@ split_hist_kernel(bf_param_tables prm, int hist_doubles, uint32_t seg_chunks, co
       fast_accumulate<FS>(prm.fast_bin + (kf >= 0 ? kf : 0) * BF_CHUNK,
                           static_cast<uint32_t>(prm.fast_pad) * BF_CHUNK, kf >= 0 ? 0xffffffffu : 0u,
                           sc.weights, frefs, nf_seg, warp, F, lane, hist + warp * cf + lcol[lane],
-                          warp == 0 ? progress : nullptr);
+                          warp == 0 ? progress : nullptr,
+                          far_mode == 2 || (far_mode == 0 && !(NW - F - S >= 4)));
       if (warp == 0 && lane == 0) *progress = 0xffffffffu - kPrefetchAhead;  // release the followers
     } else if (warp < F + S) {
       const int ks = lparam[32 + lane];
@@ -1030,6 +1057,8 @@ int launch_split_hist(const bf_param_tables& prm, const double* pmax, const uint
   uint32_t seg_chunks = kSegmentChunks;  // BF_SEG=<chunks>: measurements
   if (const char* env = getenv("BF_SEG")) seg_chunks = static_cast<uint32_t>(strtoul(env, nullptr, 10));
   if (seg_chunks < 256) seg_chunks = 256;
+  if (seg_chunks > 0x3fffffffu) seg_chunks = 0x3fffffffu;
+  if (const char* env = getenv("BF_FAR")) seg_chunks |= static_cast<uint32_t>(atoi(env) & 3) << 30;
   const size_t smem = SplitSmem::bytes(hd);
   const int fs = prm.fast_pad == 16 ? 2 : 1, ss = prm.slow_pad == 16 ? 2 : 1;
   static bool configured[64][4] = {};
