@@ -817,8 +817,8 @@ split_hist_kernel(bf_param_tables prm, int hist_doubles, uint32_t seg_chunks_far
   // narrower than the whole star's, the private copies smaller, and more warps get one -- a
   // broad star as a whole leaves room for 8 fast warps of 20.  Every segment adds its merged
   // copies to the star's pdf rows (in global memory, not normalised yet).
-  // (top two bits: who prefetches into L2 -- 0 the fast warps unless four idle warps do it,
-  //  1 nobody but idle warps, 2 the fast warps always; measurements)
+  // (top two bits: who prefetches into L2 -- 0 idle warps only (when there are four), 1 the fast
+  //  warps themselves when there are not, 2 the fast warps always; 1 and 2 measured no faster)
   const uint32_t seg_chunks = seg_chunks_far & 0x3fffffffu;
   const uint32_t far_mode = seg_chunks_far >> 30;
   const uint32_t n_seg = n_mc > seg_chunks + seg_chunks / 2 ? (n_mc + seg_chunks / 2) / seg_chunks : 1u;
@@ -907,7 +907,7 @@ split_hist_kernel(bf_param_tables prm, int hist_doubles, uint32_t seg_chunks_far
                           static_cast<uint32_t>(prm.fast_pad) * BF_CHUNK, kf >= 0 ? 0xffffffffu : 0u,
                           sc.weights, frefs, nf_seg, warp, F, lane, hist + warp * cf + lcol[lane],
                           warp == 0 ? progress : nullptr,
-                          far_mode == 2 || (far_mode == 0 && !(NW - F - S >= 4)));
+                          far_mode == 2 || (far_mode == 1 && !(NW - F - S >= 4)));
       if (warp == 0 && lane == 0) *progress = 0xffffffffu - kPrefetchAhead;  // release the followers
     } else if (warp < F + S) {
       const int ks = lparam[32 + lane];
