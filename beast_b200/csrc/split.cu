@@ -450,6 +450,8 @@ __device__ __forceinline__ void add_chunk(uint32_t col_s, const FastRows& r, uin
 }
 
 // A fast warp: chunks first*SLOTS + h, then every nfw*SLOTS-th, of the star's member chunks.
+// (Pulling the rows into L2 twelve steps ahead from the fast warps themselves, with
+// prefetch.global.L2, was measured: no faster for narrow stars, slower for broad ones.)
 // Software pipeline in registers: the chunk reference is read four steps ahead, the rows (8 bin
 // bytes + 8 weights) three steps ahead of their use, so that three steps' rows are in flight
 // per warp.  bins_lane = fast_bin + this lane's parameter, bin_mask = 0 for a lane without a
@@ -460,7 +462,7 @@ __device__ __forceinline__ void fast_accumulate(const uint8_t* __restrict__ bins
                                                 uint32_t bin_mask, const double* __restrict__ weights,
                                                 const uint2* refs, uint32_t n_mc, uint32_t first,
                                                 uint32_t nfw, int lane, double* col,
-                                                volatile uint32_t* progress, bool far_on) {
+                                                volatile uint32_t* progress) {
   const uint32_t h = SLOTS == 2 ? static_cast<uint32_t>(lane >> 4) : 0u;
   const uint32_t step = nfw * SLOTS;
   const uint32_t col_s = static_cast<uint32_t>(__cvta_generic_to_shared(col));
@@ -469,19 +471,20 @@ __device__ __forceinline__ void fast_accumulate(const uint8_t* __restrict__ bins
   const uint32_t n_steps = (n_mc - start + step - 1) / step;
   const uint32_t last = n_mc - 1;
   uint32_t i = start + h;  // this lane's position of the step whose reference is read next
-  // (a position past the end of the list: the last chunk's bins with the marker y = ~0, which the
-  //  row load turns into zero weights -- no separate flag to keep in a register)
+  // (a position past the end of the list reads the last chunk's reference, and the row load,
+  //  which keeps its own running position, turns it into zero weights: no flag travels with the
+  //  reference, and nothing operates on a reference before it is used as an address)
   auto next_ref = [&]() {
-    const bool valid = i <= last;
-    uint2 r = refs[valid ? i : last];
-    if (!valid) r.y = 0xffffffffu;
+    const uint2 r = refs[i <= last ? i : last];
     i += step;
     return r;
   };
+  uint32_t il = start + h;  // position of the step whose rows are loaded next
   auto load = [&](uint2 ref, FastRows& r) {
-    const double2* wp = ref.y != 0xffffffffu
+    const double2* wp = il <= last
                             ? reinterpret_cast<const double2*>(weights + static_cast<size_t>(ref.y) * BF_CHUNK)
                             : reinterpret_cast<const double2*>(g_zero_weights);
+    il += step;
     const double2 a = __ldg(wp), b = __ldg(wp + 1), c = __ldg(wp + 2), d = __ldg(wp + 3);
     const uint2 bb = __ldg(reinterpret_cast<const uint2*>(bins_lane + static_cast<size_t>(ref.x) * row_bytes));
     r.bins = bb;
@@ -492,20 +495,6 @@ __device__ __forceinline__ void fast_accumulate(const uint8_t* __restrict__ bins
   // consumed, and two sets of three chunk references in turn, requested a whole round before
   // they are needed as addresses: no register copy and no address ever waits for a load that
   // was issued less than three steps earlier.
-  // Further ahead still (kFarAhead steps) the rows are only pulled into L2, so that the loads
-  // above meet L2 latency instead of DRAM latency: the reference of step t + kFarAhead + 1 is
-  // requested while the rows of step t + kFarAhead are prefetched, one register pair in all.
-  constexpr uint32_t kFarAhead = 12;
-  uint32_t ifar = start + h + kFarAhead * step;
-  uint2 far = refs[ifar <= last ? ifar : last];
-  auto prefetch_far = [&]() {
-    if (ifar <= last) {
-      asm volatile("prefetch.global.L2 [%0];" ::"l"(weights + static_cast<size_t>(far.y) * BF_CHUNK));
-      asm volatile("prefetch.global.L2 [%0];" ::"l"(bins_lane + static_cast<size_t>(far.x) * row_bytes));
-    }
-    ifar += step;
-    far = refs[ifar <= last ? ifar : last];
-  };
   FastRows r0, r1, r2;
   uint2 qa0, qa1, qa2, qb0, qb1, qb2;
   load(next_ref(), r0);
@@ -521,16 +510,13 @@ __device__ __forceinline__ void fast_accumulate(const uint8_t* __restrict__ bins
     qb2 = next_ref();
     add_chunk(col_s, r0, bin_mask);
     load(qa0, r0);
-    if (far_on) prefetch_far();
     if (t + 1 < n_steps) {
       add_chunk(col_s, r1, bin_mask);
       load(qa1, r1);
-      if (far_on) prefetch_far();
     }
     if (t + 2 < n_steps) {
       add_chunk(col_s, r2, bin_mask);
       load(qa2, r2);
-      if (far_on) prefetch_far();
     }
     if (t + 3 >= n_steps) break;
     qa0 = next_ref();
@@ -538,16 +524,13 @@ __device__ __forceinline__ void fast_accumulate(const uint8_t* __restrict__ bins
     qa2 = next_ref();
     add_chunk(col_s, r0, bin_mask);
     load(qb0, r0);
-    if (far_on) prefetch_far();
     if (t + 4 < n_steps) {
       add_chunk(col_s, r1, bin_mask);
       load(qb1, r1);
-      if (far_on) prefetch_far();
     }
     if (t + 5 < n_steps) {
       add_chunk(col_s, r2, bin_mask);
       load(qb2, r2);
-      if (far_on) prefetch_far();
     }
   }
 }
@@ -718,7 +701,7 @@ __device__ __forceinline__ void class_ranges(const bf_param_tables& prm, const u
 
 template <int FS, int SS>  // chunk slots per instruction of the fast / slow class (1 or 2)
 __global__ void __launch_bounds__(kSplitWarpsMax * 32, 1)
-split_hist_kernel(bf_param_tables prm, int hist_doubles, uint32_t seg_chunks_far, const double* __restrict__ pmax,
+split_hist_kernel(bf_param_tables prm, int hist_doubles, uint32_t seg_chunks, const double* __restrict__ pmax,
                   const uint32_t* __restrict__ offsets, const uint32_t* __restrict__ list,
                   const int32_t* __restrict__ star_order, int64_t star_begin, int64_t entry_base,
                   bf_accum_scratch sc, double p0, double p1, double p2, bf_star_outputs out) {
@@ -817,10 +800,6 @@ split_hist_kernel(bf_param_tables prm, int hist_doubles, uint32_t seg_chunks_far
   // narrower than the whole star's, the private copies smaller, and more warps get one -- a
   // broad star as a whole leaves room for 8 fast warps of 20.  Every segment adds its merged
   // copies to the star's pdf rows (in global memory, not normalised yet).
-  // (top two bits: who prefetches into L2 -- 0 idle warps only (when there are four), 1 the fast
-  //  warps themselves when there are not, 2 the fast warps always; 1 and 2 measured no faster)
-  const uint32_t seg_chunks = seg_chunks_far & 0x3fffffffu;
-  const uint32_t far_mode = seg_chunks_far >> 30;
   const uint32_t n_seg = n_mc > seg_chunks + seg_chunks / 2 ? (n_mc + seg_chunks / 2) / seg_chunks : 1u;
   const uint32_t seg_len = (n_mc + n_seg - 1) / n_seg;
   for (uint32_t seg = 0; seg < n_seg; ++seg) {
@@ -906,8 +885,7 @@ split_hist_kernel(bf_param_tables prm, int hist_doubles, uint32_t seg_chunks_far
       fast_accumulate<FS>(prm.fast_bin + (kf >= 0 ? kf : 0) * BF_CHUNK,
                           static_cast<uint32_t>(prm.fast_pad) * BF_CHUNK, kf >= 0 ? 0xffffffffu : 0u,
                           sc.weights, frefs, nf_seg, warp, F, lane, hist + warp * cf + lcol[lane],
-                          warp == 0 ? progress : nullptr,
-                          far_mode == 2 || (far_mode == 1 && !(NW - F - S >= 4)));
+                          warp == 0 ? progress : nullptr);
       if (warp == 0 && lane == 0) *progress = 0xffffffffu - kPrefetchAhead;  // release the followers
     } else if (warp < F + S) {
       const int ks = lparam[32 + lane];
@@ -1057,8 +1035,6 @@ int launch_split_hist(const bf_param_tables& prm, const double* pmax, const uint
   uint32_t seg_chunks = kSegmentChunks;  // BF_SEG=<chunks>: measurements
   if (const char* env = getenv("BF_SEG")) seg_chunks = static_cast<uint32_t>(strtoul(env, nullptr, 10));
   if (seg_chunks < 256) seg_chunks = 256;
-  if (seg_chunks > 0x3fffffffu) seg_chunks = 0x3fffffffu;
-  if (const char* env = getenv("BF_FAR")) seg_chunks |= static_cast<uint32_t>(atoi(env) & 3) << 30;
   const size_t smem = SplitSmem::bytes(hd);
   const int fs = prm.fast_pad == 16 ? 2 : 1, ss = prm.slow_pad == 16 ? 2 : 1;
   static bool configured[64][4] = {};
