@@ -324,7 +324,7 @@ class FitEngine:
     # ------------------------------------------------------------------------------
     def fit(self, fluxes, threshold=-10.0, percentiles=(16.0, 50.0, 84.0), want_pdf2d=False,
             sparse=None, batch=None, rng=None, lnp_rng="device", seed=0, reuse_buffers=False,
-            result=None, row_offset=0, on_batch=None):
+            result=None, row_offset=0, on_batch=None, tail_batch=0):
         """Fit all stars of ``fluxes`` (ns, nb) in batches; returns a host ``FitResult``.
 
         Results are copied device->host asynchronously into page-locked arrays while the next
@@ -332,7 +332,9 @@ class FitEngine:
         the same ones back on the next call of the same shape (they are overwritten then).
         ``result`` / ``row_offset``: write into rows ``row_offset ...`` of an existing
         ``FitResult`` (a resumed run); ``on_batch(lo, hi)`` is called after the rows [lo, hi) of
-        a batch have arrived on the host (checkpoints)."""
+        a batch have arrived on the host (checkpoints).  ``tail_batch``: when there are several
+        batches, end with one of at most this many stars -- the copy of the last batch's results
+        is the only one no computation hides, so a short last batch shortens the call."""
         torch = _torch()
         s = self.setup
         fluxes = np.ascontiguousarray(fluxes, dtype=np.float64)
@@ -360,7 +362,11 @@ class FitEngine:
                 res.sparse_off = np.zeros(res.ns + 1, dtype=np.int64)
             if "_sp_j" in t:  # records land in the preallocated arrays as the batches finish
                 res.sparse_j, res.sparse_lnp, res.sparse_chi2 = res._sp_j, res._sp_lnp, res._sp_chi2
-        n_batches = -(-ns // bs)
+        starts = list(range(0, ns, bs))
+        if tail_batch and len(starts) > 1 and ns - starts[-1] > 2 * int(tail_batch):
+            starts.append(ns - int(tail_batch))
+        ends = starts[1:] + [ns]
+        n_batches = len(starts)
         # record offsets of every batch, staged in page-locked memory: they are small and go first
         # on the copy stream, so that nothing on the host waits behind a batch's 1D PDFs
         off_stage = torch.empty((n_batches, bs + 1), dtype=torch.int64, pin_memory=True) if sparse is not None else None
@@ -379,8 +385,7 @@ class FitEngine:
             main = torch.cuda.current_stream(self.device)
             copy_stream = self._copy_stream
             pending = None
-            for i, a in enumerate(range(0, ns, bs)):
-                b = min(ns, a + bs)
+            for i, (a, b) in enumerate(zip(starts, ends)):
                 o = self.fit_batch(fluxes[a:b], threshold, percentiles, want_pdf2d, sparse, rng,
                                    lnp_rng, seed, row_offset + a)
                 done = torch.cuda.Event()

@@ -490,7 +490,8 @@ def Q_all_memory(prev_result, obs, sedgrid, obsmodel, qnames_in, p=[16.0, 50.0, 
     if len(fluxes):
         engine.fit(fluxes, threshold=float(threshold), percentiles=tuple(trios[0]),
                    want_pdf2d=make_pdf2d, sparse=sparse, lnp_rng=lnp_rng, seed=start_pos, batch=bs,
-                   result=res, row_offset=start_pos, on_batch=checkpoint)
+                   result=res, row_offset=start_pos, on_batch=checkpoint,
+                   tail_batch=8192 if save_every_npts is None else 0)
     if len(pvals) != 3:  # any list of percentiles (fit.py:749-753): three per pass on the device
         from .subgrid import CudaMergeMath
 
