@@ -210,10 +210,13 @@ class FitEngine:
         return tot, cnt
 
     def fit_batch(self, flux, threshold=-10.0, percentiles=(16.0, 50.0, 84.0), want_pdf2d=False,
-                  sparse=None, rng=None, lnp_rng="device", seed=0, star_base=0):
+                  sparse=None, rng=None, lnp_rng="device", seed=0, star_base=0, while_running=None):
         """Fit one batch (<= max_batch stars) with one call of ``bf_fit_batch``.  ``flux``:
         (n, nb) float64 NumPy array (host: copied inside the call) or CUDA tensor.  Returns a
         dict of device tensors, one row per star in input order.
+
+        ``while_running``: called once after the C call has returned and before the host waits
+        for the batch (the sparse pass is then still running on the device): host work to hide.
 
         ``sparse``: None, "all" or lnp_npts (fit.py:693-709).  ``lnp_rng="device"``: the subsample
         is drawn inside the call by a keyed permutation (same distribution as the reference,
@@ -282,6 +285,8 @@ class FitEngine:
                 for name, v in zip(_cabi.STAGES, state.stage_ms):
                     self._stage_tot[name] = self._stage_tot.get(name, 0.0) + float(v)
                     self._stage_cnt[name] = self._stage_cnt.get(name, 0) + 1
+            if while_running is not None:
+                while_running()
             if mode == 2:
                 nrec = int(o["sparse_off"][-1].item())
                 for name in ("sparse_j", "sparse_lnp", "sparse_chi2"):
@@ -385,9 +390,20 @@ class FitEngine:
             main = torch.cuda.current_stream(self.device)
             copy_stream = self._copy_stream
             pending = None
+            def previous_batch_done():
+                # the previous batch's rows have had a C call's worth of time to arrive; the host
+                # work on them runs while this batch's sparse pass does
+                nonlocal pending
+                if on_batch is not None and pending is not None:
+                    pending[0].synchronize()
+                    if sparse is not None:
+                        settle(pending[3] + 1)
+                    on_batch(pending[1], pending[2])
+                    pending = None
+
             for i, (a, b) in enumerate(zip(starts, ends)):
                 o = self.fit_batch(fluxes[a:b], threshold, percentiles, want_pdf2d, sparse, rng,
-                                   lnp_rng, seed, row_offset + a)
+                                   lnp_rng, seed, row_offset + a, while_running=previous_batch_done)
                 done = torch.cuda.Event()
                 done.record(main)
                 copy_stream.wait_event(done)
@@ -419,12 +435,8 @@ class FitEngine:
                     arrived.record(copy_stream)
                 del o  # (record_stream keeps the device buffers alive until their copies are done)
                 if on_batch is not None:
-                    if pending is not None:  # the previous batch has had a whole batch to arrive
-                        pending[0].synchronize()
-                        if sparse is not None:
-                            settle(i)
-                        on_batch(pending[1], pending[2])
-                    pending = (arrived, lo, hi)
+                    previous_batch_done()  # (normally done already, inside fit_batch)
+                    pending = (arrived, lo, hi, i)
             copy_stream.synchronize()
             main.synchronize()
             if sparse is not None:
