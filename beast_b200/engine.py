@@ -72,6 +72,34 @@ class FitResult:
             alloc("_sp_chi2", (sparse_cap,), torch.float32)
 
 
+def bind_host_to_gpu(device_index):
+    """Pin the calling process to the CPU cores next to GPU ``device_index`` (NVML's ideal CPU
+    affinity), so that the page-locked result arrays allocated afterwards sit in that socket's
+    memory and the device-to-host copies do not cross the socket link.  One process per GPU;
+    call before the first allocation.  Returns the cores chosen, or None when NVML or the
+    affinity calls are not available (nothing is changed then)."""
+    import os
+
+    try:
+        import pynvml
+
+        torch = _torch()
+        pr = torch.cuda.get_device_properties(device_index)
+        pynvml.nvmlInit()
+        bus = "%08x:%02x:%02x.0" % (pr.pci_domain_id, pr.pci_bus_id, pr.pci_device_id)
+        h = pynvml.nvmlDeviceGetHandleByPciBusId(bus.encode() if bytes is not str else bus)
+        words = (os.cpu_count() + 63) // 64
+        mask = pynvml.nvmlDeviceGetCpuAffinity(h, words)
+        cpus = {i * 64 + b for i, m in enumerate(mask) for b in range(64) if (int(m) >> b) & 1}
+        cpus &= set(os.sched_getaffinity(0))
+        if not cpus:
+            return None
+        os.sched_setaffinity(0, cpus)
+        return sorted(cpus)
+    except Exception:
+        return None
+
+
 class FitEngine:
     """Grid resident in HBM + the batched fit pipeline.
 

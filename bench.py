@@ -260,6 +260,10 @@ def run_ours(args, rank, world, local_rank):
 
     torch.cuda.set_device(local_rank)
     dev = torch.device("cuda", local_rank)
+    from beast_b200.engine import bind_host_to_gpu
+
+    # one process per GPU, on the cores (and memory) of the socket that GPU hangs on
+    host_cores = bind_host_to_gpu(local_rank) if os.environ.get("BF_NO_BIND") is None else None
     dist = None
     if world > 1:
         import torch.distributed as dist_mod
@@ -523,7 +527,9 @@ def run_ours(args, rank, world, local_rank):
                         "max_nbins=%d, lnp_npts=%d, threshold=%g, engine=<resident grid>, keep_lnp=True): host "
                         "objects in, the reference's result arrays (stats, pdf1d, sparse lnP) back on the host, "
                         "no files" % (args.max_nbins, LNP_NPTS, THRESHOLD),
-                "with_files_on_tmpfs_seconds": files_s},
+                "with_files_on_tmpfs_seconds": files_s,
+                "host_cores_rank0": ("%d cores next to the GPU (NVML affinity)" % len(host_cores)) if host_cores
+                else "unbound"},
         "gpu_launches": int(launches),
         "roofline": roofline,
         "cpu_baseline": cpu,
