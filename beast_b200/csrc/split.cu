@@ -60,16 +60,11 @@ constexpr int kOrderStretch = 128;  // positions of the group order one warp wal
 // the fast parameters: the weights of up to 8 list positions (A operand) and the group's
 // fixed-point parameter values (B operand) of the FP64 tensor-core products below.
 constexpr int kWtLd = BF_GROUP + 4;  // row pitch of the weight tile: conflict-free fragments
-// Plus, always: the fluxes of the stars of two blocks of 32 list positions (the block at work and
-// the next one, fetched by cp.async while this one is evaluated).
-constexpr int kFluxBands = 8;  // the grouped kernel is instantiated for up to 8 bands
 template <int NT>
 struct GroupedSmem {
   static constexpr int kLdq = NT * 8 + 4;
-  static constexpr size_t kFluxBytes = 2 * 32 * kFluxBands * sizeof(double);
-  static constexpr size_t kTileBytes =
+  static constexpr size_t kWarpBytes =
       NT == 0 ? 0 : 8 * kWtLd * sizeof(double) + BF_GROUP * kLdq * sizeof(int32_t) + 8 * sizeof(int32_t);
-  static constexpr size_t kWarpBytes = kTileBytes + kFluxBytes;
 };
 
 // D[8 list positions][8 parameters] += A[8][4 models] * B[4 models][8 parameters]  (FP64 tensor core)
@@ -129,9 +124,6 @@ exact_weights_grouped_kernel(bf_exact_grid grid, const double* __restrict__ flux
   double* wt = reinterpret_cast<double*>(mine);
   int32_t* qg = reinterpret_cast<int32_t*>(wt + 8 * kWtLd);
   int32_t* slots = qg + BF_GROUP * kLdq;
-  double* fx = reinterpret_cast<double*>(mine + GroupedSmem<NT>::kTileBytes);  // [2][32][NB]
-  const uint32_t fx_s = static_cast<uint32_t>(__cvta_generic_to_shared(fx));
-  static_assert(NB <= kFluxBands, "flux staging area");
   const int64_t n_stretch = (n_entries + kOrderStretch - 1) / kOrderStretch;
   for (int64_t st = static_cast<int64_t>(blockIdx.x) * kGroupedWarps + (threadIdx.x >> 5);
        st < n_stretch; st += static_cast<int64_t>(gridDim.x) * kGroupedWarps) {
@@ -144,58 +136,26 @@ exact_weights_grouped_kernel(bf_exact_grid grid, const double* __restrict__ flux
     int64_t j0 = 0;
     int pending = 0;  // list positions whose weights wait in wt for the expectation products
     uint32_t run_bits = 0xffu;  // chunks of the group that start a run of equal slow values
-    // A block of 32 list positions at a time: every lane holds the description of one of them
-    // (position, star, group, the star's maximum), and the stars' fluxes sit in shared memory.
-    // The next block's descriptions and fluxes are fetched while this block is evaluated -- the
-    // three dependent loads (order -> star -> maximum, fluxes) a quarter of a block apart, the
-    // fluxes by cp.async straight into the other half of the staging area -- so that no pair
-    // waits for a load of its own.
-    uint32_t my_e = 0, my_s = 0, my_g = 0, nx_e = 0, nx_s = 0, nx_g = 0;
-    double my_M = 0.0, nx_M = 0.0;
-    int buf = 0;
-    auto fetch_flux = [&](uint32_t star, int which) {  // this lane's star -> fx[which][lane][:]
-      const double* src = flux64 + static_cast<int64_t>(star) * NB;
-      const uint32_t dst = fx_s + static_cast<uint32_t>((which * 32 + lane) * NB * sizeof(double));
-#pragma unroll
-      for (int b = 0; b < NB; ++b)
-        asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(dst + b * 8), "l"(src + b) : "memory");
-    };
-    __syncwarp();  // (the previous stretch's reads of the staging area are over)
-    if (i0 + lane < i1) {
-      my_e = order[i0 + lane];
-      my_s = entry_star[my_e];
-      my_g = list[my_e];
-      my_M = pmax[my_s];
-      fetch_flux(my_s, 0);
-    }
-    asm volatile("cp.async.commit_group;" ::: "memory");
     for (int64_t blk = i0; blk < i1; blk += 32) {
       const int cnt = static_cast<int>(i1 - blk < 32 ? i1 - blk : 32);
-      const bool more = blk + 32 + lane < i1;  // this lane has a position in the next block
-      asm volatile("cp.async.wait_group 0;" ::: "memory");
-      __syncwarp();  // this block's fluxes have landed, for all lanes
-      const double* fb = fx + buf * 32 * NB;
+      // every lane fetches the description of one list position of this block of 32
+      uint32_t my_e = 0, my_s = 0, my_g = 0;
+      double my_M = 0.0;
+      if (lane < cnt) {
+        my_e = order[blk + lane];
+        my_s = entry_star[my_e];
+        my_g = list[my_e];
+        my_M = pmax[my_s];
+      }
       for (int t = 0; t < cnt; ++t) {
-        if (t == 0) {
-          if (more) nx_e = order[blk + 32 + lane];
-        } else if (t == 8) {
-          if (more) {
-            nx_s = entry_star[nx_e];
-            nx_g = list[nx_e];
-          }
-        } else if (t == 16) {
-          if (more) {
-            nx_M = pmax[nx_s];
-            fetch_flux(nx_s, buf ^ 1);
-          }
-          asm volatile("cp.async.commit_group;" ::: "memory");
-        }
         const uint32_t e = __shfl_sync(0xffffffffu, my_e, t);
+        const uint32_t s = __shfl_sync(0xffffffffu, my_s, t);
         const uint32_t g = __shfl_sync(0xffffffffu, my_g, t);
         const double M = __shfl_sync(0xffffffffu, my_M, t);
         double f[NB];
+        const double* sflux = flux64 + static_cast<int64_t>(s) * NB;
 #pragma unroll
-        for (int b = 0; b < NB; ++b) f[b] = fb[t * NB + b];
+        for (int b = 0; b < NB; ++b) f[b] = __ldg(sflux + b);
         if (g != cur_g) {  // warp-uniform: the rows of the next group
           if constexpr (NT > 0) {
             if (pending) flush_expectations<NT>(wt, qg, slots, pending, sc.exp_part, lane);
@@ -335,12 +295,6 @@ exact_weights_grouped_kernel(bf_exact_grid grid, const double* __restrict__ flux
           }
         }
       }
-      // (a block shorter than 17 positions is the last of its stretch: nothing left to fetch)
-      my_e = nx_e;
-      my_s = nx_s;
-      my_g = nx_g;
-      my_M = nx_M;
-      buf ^= 1;
     }
     if constexpr (NT > 0) {
       if (pending) flush_expectations<NT>(wt, qg, slots, pending, sc.exp_part, lane);
