@@ -24,7 +24,8 @@
 // r; the smallest c2),
 //   acc(s, m) = sum_b r_mb^2 (f_sb - m_mb)^2 + c2_m >= sum_b rlo_b^2 dist(f_sb, [mlo_b, mhi_b])^2 + c2min
 // a warp skips a group that none of its 256 stars can select and reports +inf for it; within a
-// group it evaluates only those of its four star pairs (64 stars each) that hold such a star.  The
+// group it evaluates only those of its four star pairs (64 stars each) that hold such a star, and
+// for those only the halves of the group (32 models, with boxes of their own) that they meet.  The
 // group lists that follow are the same ones: a skipped group's minimum is above the star's
 // selection threshold, and the group of the star's minimum is never skipped.
 
@@ -45,7 +46,8 @@ struct DenseSmem {
   static constexpr int kStages = COV ? 3 : 4;
   static constexpr int kPrefetch = COV ? 1 : 2;  // tiles in flight ahead of the consumer
   static constexpr uint32_t kTileBytes = kRows * BF_TILE_MODELS * sizeof(float);
-  // group boxes of a tile: per group mlo[NB], mhi[NB], rlo[NB], c2min, padded to 16 bytes
+  // group boxes of a tile: per group 3 x (mlo[NB], mhi[NB], rlo[NB], c2min) -- the group and its
+  // two halves --, padded to 16 bytes
   static constexpr int kBoxFloats = BF_BOX_FLOATS(NB);
   static constexpr uint32_t kBoxBytes = PRUNE ? (BF_TILE_MODELS / BF_GROUP) * kBoxFloats * sizeof(float) : 0;
   static constexpr uint32_t kCutBytes = PRUNE ? BF_STAR_BLOCK * sizeof(float) : 0;
@@ -161,18 +163,17 @@ dense_chi2_kernel(const float* __restrict__ tiles, int64_t n_tiles, int tiles_pe
       float* gp = gmin + gidx * ld_star + star0 + wbase;
       unsigned need_mask = (1u << kNPair) - 1;
       if constexpr (PRUNE) {
-        // (n_eval: star pairs x groups this warp evaluates, for the caller's statistics)
+        // (n_eval: star pairs x half groups this warp evaluates, for the caller's statistics)
         // can any star of this warp select a model of the group?  lower bound of acc per star
+        // A group's record: the box of its 64 models, then the boxes of its two halves.
         const float* bx = box_buf + stage * (GROUPS_PER_TILE * BOXF) + g * BOXF;
-        need_mask = 0;
-#pragma unroll
-        for (int p = 0; p < kNPair; ++p) {
-          float lo = bx[3 * NB], hi = lo;
+        auto pair_needs = [&](const float* box, int p) {  // does a star of pair p get below its ceiling?
+          float lo = box[3 * NB], hi = lo;
 #pragma unroll
           for (int b = 0; b < NB; ++b) {
             float fl, fh;
             unpack2(f[p][b], fl, fh);
-            const float mlo = bx[b], mhi = bx[NB + b], rlo = bx[2 * NB + b];
+            const float mlo = box[b], mhi = box[NB + b], rlo = box[2 * NB + b];
             const float dl = fmaxf(fmaxf(mlo - fl, fl - mhi), 0.0f) * rlo;
             const float dh = fmaxf(fmaxf(mlo - fh, fh - mhi), 0.0f) * rlo;
             lo = fmaf(dl, dl, lo);
@@ -181,18 +182,35 @@ dense_chi2_kernel(const float* __restrict__ tiles, int64_t n_tiles, int tiles_pe
           // 1 - 2^-16 covers the FP32 rounding of both this bound and the accumulators below
           const bool need = lo * 0.99998474f < cut_s[wbase + (2 * p) * 32] ||
                             hi * 0.99998474f < cut_s[wbase + (2 * p + 1) * 32];
-          if (__any_sync(0xffffffffu, need)) need_mask |= 1u << p;  // the pair's 64 stars are evaluated
+          return __any_sync(0xffffffffu, need) != 0;
+        };
+        need_mask = 0;
+#pragma unroll
+        for (int p = 0; p < kNPair; ++p) {
+          if (pair_needs(bx, p)) need_mask |= 1u << p;  // the pair's 64 stars meet the group
         }
         if (need_mask == 0) {
 #pragma unroll
           for (int q = 0; q < 2 * kNPair; ++q) gp[q * 32] = kInf;
           continue;
         }
+        // the pairs that do: which half of the group (bits p: first 32 models, kNPair + p: second)
+        unsigned halves = 0;
+#pragma unroll
+        for (int p = 0; p < kNPair; ++p) {
+          if ((need_mask >> p) & 1) {  // warp-uniform
+            if (pair_needs(bx + (3 * NB + 1), p)) halves |= 1u << p;
+            if (pair_needs(bx + 2 * (3 * NB + 1), p)) halves |= 1u << (kNPair + p);
+          }
+        }
+        need_mask = halves;
         n_eval += __popc(need_mask);
       }
       if constexpr (!COV) {
 #pragma unroll 2
         for (int m = g * BF_GROUP; m < (g + 1) * BF_GROUP; m += 2) {
+          // (pruned: the pairs of this half of the group)
+          const unsigned live = PRUNE ? need_mask >> (((m / (BF_GROUP / 2)) & 1) * kNPair) : need_mask;
           float2 r[NB], na[NB];
 #pragma unroll
           for (int b = 0; b < NB; ++b) {
@@ -202,7 +220,7 @@ dense_chi2_kernel(const float* __restrict__ tiles, int64_t n_tiles, int tiles_pe
           const float2 c2 = *reinterpret_cast<const float2*>(sb + 2 * NB * TM + m);
 #pragma unroll
           for (int p = 0; p < kNPair; ++p) {
-            if (PRUNE && !((need_mask >> p) & 1)) continue;  // warp-uniform
+            if (PRUNE && !((live >> p) & 1)) continue;  // warp-uniform
             f32x2 acc0 = pack2(c2.x, c2.x);
             f32x2 acc1 = pack2(c2.y, c2.y);
 #pragma unroll
@@ -274,8 +292,8 @@ dense_chi2_kernel(const float* __restrict__ tiles, int64_t n_tiles, int tiles_pe
   }
 
   if constexpr (PRUNE) {
-    if (evaluated != nullptr && lane == 0 && n_eval > 0)  // (star, model) pairs: 64 stars x BF_GROUP models each
-      atomicAdd(evaluated, static_cast<unsigned long long>(n_eval) * (64 * BF_GROUP));
+    if (evaluated != nullptr && lane == 0 && n_eval > 0)  // (star, model) pairs: 64 stars x half a group each
+      atomicAdd(evaluated, static_cast<unsigned long long>(n_eval) * (64 * (BF_GROUP / 2)));
   }
   // acc >= 0 always (chi2 >= 0, c2 >= 0), so the IEEE bit pattern orders like the value;
   // packed as (value bits << 32 | group) one 64-bit atomicMin keeps the arg-min group too

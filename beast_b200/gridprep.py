@@ -128,16 +128,13 @@ def _pad_to(n, mult):
 
 def box_floats(nb):
     """BF_BOX_FLOATS(nb) of include/beast_b200.h"""
-    return (3 * nb + 1 + 3) // 4 * 4
+    return (3 * (3 * nb + 1) + 3) // 4 * 4
 
 
-def _group_boxes(rows, nm, nb):
-    """Per group of GROUP models a box around what the dense pass reads for them (the FP32 tile
-    rows r_b, -a_b, c2): the range of m_b = a_b / r_b, the smallest r_b and the smallest c2, each
-    rounded outwards, so that  acc >= sum_b rlo_b^2 dist(f_b, [mlo_b, mhi_b])^2 + c2min  for every
-    model of the group (bf_dense_chi2_pruned).  Padding models (c2 = 3e38) stay out of the box."""
+def _boxes_of(rows, nm, nb, size):
+    """one box (3 nb + 1 floats: mlo, mhi, rlo, c2min) per run of ``size`` consecutive models"""
     nmp = rows.shape[1]
-    ng = nmp // GROUP
+    ng = nmp // size
     r = rows[:nb].astype(np.float64)
     a = -rows[nb:2 * nb].astype(np.float64)
     with np.errstate(divide="ignore", invalid="ignore"):
@@ -145,10 +142,10 @@ def _group_boxes(rows, nm, nb):
     valid = np.arange(nmp) < nm
     usable = valid[None, :] & np.isfinite(m)   # r = 0: the band does not constrain, rlo = 0 covers it
     big = np.finfo(np.float32).max
-    mlo = np.where(usable, m, np.inf).reshape(nb, ng, GROUP).min(axis=2)
-    mhi = np.where(usable, m, -np.inf).reshape(nb, ng, GROUP).max(axis=2)
-    rlo = np.where(valid[None, :], r, np.inf).reshape(nb, ng, GROUP).min(axis=2)
-    c2min = rows[2 * nb].reshape(ng, GROUP).min(axis=1)
+    mlo = np.where(usable, m, np.inf).reshape(nb, ng, size).min(axis=2)
+    mhi = np.where(usable, m, -np.inf).reshape(nb, ng, size).max(axis=2)
+    rlo = np.where(valid[None, :], r, np.inf).reshape(nb, ng, size).min(axis=2)
+    c2min = rows[2 * nb].reshape(ng, size).min(axis=1)
     empty = ~np.isfinite(mlo) | ~np.isfinite(mhi)
     mlo = np.where(empty, -big, mlo)
     mhi = np.where(empty, big, mhi)
@@ -161,11 +158,27 @@ def _group_boxes(rows, nm, nb):
         # one more step outwards: the kernel's r and a are the FP32 values, but a / r above is rounded
         lo32 = np.maximum(np.nextafter(lo32, np.float32(-np.inf)), -big).astype(np.float32)
         hi32 = np.minimum(np.nextafter(hi32, np.float32(np.inf)), big).astype(np.float32)
-    out = np.zeros((ng, box_floats(nb)), dtype=np.float32)
+    out = np.zeros((ng, 3 * nb + 1), dtype=np.float32)
     out[:, :nb] = lo32.T
     out[:, nb:2 * nb] = hi32.T
     out[:, 2 * nb:3 * nb] = rlo.astype(np.float32).T   # r is FP32 already: exact
     out[:, 3 * nb] = c2min
+    return out
+
+
+def _group_boxes(rows, nm, nb):
+    """Per group of GROUP models three boxes around what the dense pass reads for them (the FP32
+    tile rows r_b, -a_b, c2) -- the whole group, its first and its second half --: the range of
+    m_b = a_b / r_b, the smallest r_b and the smallest c2, each rounded outwards, so that
+    acc >= sum_b rlo_b^2 dist(f_b, [mlo_b, mhi_b])^2 + c2min  for every model of the box
+    (bf_dense_chi2_pruned).  Padding models (c2 = 3e38) stay out of the boxes."""
+    ng = rows.shape[1] // GROUP
+    one = 3 * nb + 1
+    out = np.zeros((ng, box_floats(nb)), dtype=np.float32)
+    out[:, :one] = _boxes_of(rows, nm, nb, GROUP)
+    halves = _boxes_of(rows, nm, nb, GROUP // 2)
+    out[:, one:2 * one] = halves[0::2]
+    out[:, 2 * one:3 * one] = halves[1::2]
     return out
 
 

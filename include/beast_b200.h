@@ -33,8 +33,9 @@ extern "C" {
 #define BF_GROUP 64        /* models per group minimum                            */
 #define BF_CHUNK 8         /* models per parameter-table chunk                    */
 #define BF_STAR_BLOCK 1024 /* stars per thread block of the dense pass            */
-/* floats per group box of the pruned dense pass: mlo[nb], mhi[nb], rlo[nb], c2min, padded to 16 B */
-#define BF_BOX_FLOATS(nb) ((3 * (nb) + 1 + 3) / 4 * 4)
+/* floats per group record of the pruned dense pass: three boxes (the group's 64 models, its first
+ * and its second 32), each mlo[nb], mhi[nb], rlo[nb], c2min; the record padded to 16 B */
+#define BF_BOX_FLOATS(nb) ((3 * (3 * (nb) + 1) + 3) / 4 * 4)
 #define BF_MAX_BANDS 16   /* array bound; the diagonal likelihood is built for 1..12 bands,
                              the full-covariance one for 2..8, trimming for 1..15 */
 #define BF_MAX_PARAMS 128
@@ -77,10 +78,12 @@ int bf_dense_chi2(int nb, int64_t n_tiles, const float* tiles, int64_t n_stars,
 
 /* The same sweep, leaving out what cannot matter.  A warp of the kernel owns 256 neighbouring
  * stars; it skips a group when a lower bound of acc over the group's models is above the
- * selection threshold of every one of them, and reports +inf for that group.  The bound comes
- * from a box per group,
- *   boxes : [n_tiles*BF_TILE_MODELS/BF_GROUP][BF_BOX_FLOATS(nb)] float, 16-byte aligned:
- *           mlo_b <= a_b / r_b <= mhi_b and rlo_b <= r_b for every model of the group and band b,
+ * selection threshold of every one of them, and reports +inf for that group; otherwise it
+ * evaluates, for each 64 of its stars, the halves of the group their bounds do not rule out.
+ * The bounds come from boxes per group,
+ *   boxes : [n_tiles*BF_TILE_MODELS/BF_GROUP][BF_BOX_FLOATS(nb)] float, 16-byte aligned; per group
+ *           three boxes of 3 nb + 1 floats (all 64 models, the first 32, the last 32):
+ *           mlo_b <= a_b / r_b <= mhi_b and rlo_b <= r_b for every model of the box and band b,
  *           c2min <= c2  (rounded outwards), so that
  *           acc >= sum_b rlo_b^2 dist(f_b, [mlo_b, mhi_b])^2 + c2min;
  *   cut   : [ld_star] float, per star a ceiling of its selection threshold on the acc scale
@@ -88,8 +91,8 @@ int bf_dense_chi2(int nb, int64_t n_tiles, const float* tiles, int64_t n_stars,
  *           minimum, e.g. the minimum over the coarse tiles); -1 for padding stars, +inf to
  *           keep everything.
  * Groups that bf_select_* would list get the same minimum as from bf_dense_chi2, the others
- * +inf or their true minimum (both above the threshold), and starmin is the same, so the lists
- * are identical.  Pays off when neighbouring stars are alike (bf_fit_batch orders them).
+ * +inf, their true minimum or the minimum over the half evaluated (all at or above the star's
+ * ceiling), and starmin is the same, so the lists are identical.  Pays off when neighbouring stars are alike (bf_fit_batch orders them).
  *   evaluated : optional device counter (may be NULL), raised by the number of (star, model)
  *           pairs the sweep did evaluate (padding stars and models included)
  * No counterpart in the reference, which evaluates every model for every star. */

@@ -86,14 +86,18 @@ def test_group_boxes_bound_the_accumulator(small):
         acc = rows[2 * nb].astype(np.float64).copy()
         for b in range(nb):
             acc += (fs[b].astype(np.float64) * rows[b] + rows[nb + b]) ** 2
-        gmin = acc.reshape(ng, gridprep.GROUP).min(axis=1)
-        bx = st.boxes
-        lb = bx[:, 3 * nb].copy()
-        for b in range(nb):
-            u = np.maximum(np.maximum(bx[:, b] - fs[b], fs[b] - bx[:, nb + b]), f32(0))
-            d = (u * bx[:, 2 * nb + b]).astype(f32)
-            lb = (d.astype(np.float64) * d + lb).astype(f32)   # fmaf
-        assert np.all(lb.astype(np.float64) * 0.99998474 <= gmin * (1 + 1e-6) + 1e-30)
+        one = 3 * nb + 1
+        # the group's box, then the boxes of its two halves
+        for which, size in ((0, gridprep.GROUP), (1, gridprep.GROUP // 2), (2, gridprep.GROUP // 2)):
+            per = acc.reshape(ng, gridprep.GROUP)
+            gmin = (per if which == 0 else per[:, (which - 1) * size:which * size]).min(axis=1)
+            bx = st.boxes[:, which * one:(which + 1) * one]
+            lb = bx[:, 3 * nb].copy()
+            for b in range(nb):
+                u = np.maximum(np.maximum(bx[:, b] - fs[b], fs[b] - bx[:, nb + b]), f32(0))
+                d = (u * bx[:, 2 * nb + b]).astype(f32)
+                lb = (d.astype(np.float64) * d + lb).astype(f32)   # fmaf
+            assert np.all(lb.astype(np.float64) * 0.99998474 <= gmin * (1 + 1e-6) + 1e-30)
     # the boxes are not vacuous: a star far from a group is bounded away from it
     assert np.median(lb) > 10.0
 

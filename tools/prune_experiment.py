@@ -127,3 +127,21 @@ if os.environ.get("KEYS"):
         report("colour in %d levels, then brightness" % nlev, torch.argsort(key, stable=True), 64, cmin)
     key = (carg // 64) * (1 << 20) + quant(bright, 1 << 20)
     report("coarse group, then brightness", torch.argsort(key, stable=True), 64, cmin)
+
+if os.environ.get("KEYS2"):
+    med = f.median(dim=0).values
+    sl = torch.asinh(f / med)
+
+    def nested(primary, secondary, block):
+        o = torch.argsort(sl[:, primary], stable=True)
+        o = o.clone()
+        for a in range(0, nstars, block):
+            seg = o[a:a + block]
+            o[a:a + block] = seg[torch.argsort(sl[seg, secondary], stable=True)]
+        return o
+
+    report("band 4", torch.argsort(sl[:, 4], stable=True), 64, cmin)
+    report("band 3", torch.argsort(sl[:, 3], stable=True), 64, cmin)
+    for blk in (64, 128, 256, 512):   # (a quarter of the real batch: 256 here = 1024 stars there)
+        for sec in (2, 5, 3):
+            report("band 4, blocks of %d by band %d" % (blk * scale, sec), nested(4, sec, blk), 64, cmin)
