@@ -125,13 +125,57 @@ dense_chi2_kernel(const float* __restrict__ tiles, int64_t n_tiles, int tiles_pe
       f[p][b] = pack2(fb[(2 * p) * 32], fb[(2 * p + 1) * 32]);
     }
   }
+  const float kInf = __int_as_float(0x7f800000);
+  // Pruned: a first test per (warp, group) in one band only -- the band in which this warp's 256
+  // stars lie closest together (the one the caller ordered them by, found here from the fluxes):
+  // the interval [wlo, whi] of their fluxes in band pb against the group's box in that band and
+  // the largest of their ceilings.  Six instructions rule out most groups before any star is
+  // looked at.
+  float wlo = kInf, whi = -kInf, cutmax = -kInf;
+  int pb = 0;
   if constexpr (PRUNE) {
+    float cq[2 * kNPair];
 #pragma unroll
-    for (int q = 0; q < 2 * kNPair; ++q) cut_s[wbase + q * 32] = cut[star0 + wbase + q * 32];
+    for (int q = 0; q < 2 * kNPair; ++q) {
+      cq[q] = cut[star0 + wbase + q * 32];
+      cut_s[wbase + q * 32] = cq[q];
+      cutmax = fmaxf(cutmax, cq[q]);
+    }
+    float best = kInf;
+#pragma unroll
+    for (int b = 0; b < NB; ++b) {
+      float lo = kInf, hi = -kInf;
+#pragma unroll
+      for (int p = 0; p < kNPair; ++p) {
+        float fl, fh;
+        unpack2(f[p][b], fl, fh);
+        if (cq[2 * p] >= 0.0f) {  // (padding stars carry -1 and take no part)
+          lo = fminf(lo, fl);
+          hi = fmaxf(hi, fl);
+        }
+        if (cq[2 * p + 1] >= 0.0f) {
+          lo = fminf(lo, fh);
+          hi = fmaxf(hi, fh);
+        }
+      }
+#pragma unroll
+      for (int d = 16; d > 0; d >>= 1) {
+        lo = fminf(lo, __shfl_xor_sync(0xffffffffu, lo, d));
+        hi = fmaxf(hi, __shfl_xor_sync(0xffffffffu, hi, d));
+      }
+      const float spread = (hi - lo) / fmaxf(fabsf(hi) + fabsf(lo), 1e-30f);
+      if (spread < best) {  // (a NaN spread -- no star, or infinite fluxes -- never wins)
+        best = spread;
+        pb = b;
+        wlo = lo;
+        whi = hi;
+      }
+    }
+#pragma unroll
+    for (int d = 16; d > 0; d >>= 1) cutmax = fmaxf(cutmax, __shfl_xor_sync(0xffffffffu, cutmax, d));
     __syncwarp();  // a thread reads back only what it wrote; the fence keeps the order explicit
   }
 
-  const float kInf = __int_as_float(0x7f800000);
   float rmin[2 * kNPair], smin[2 * kNPair];
   unsigned int sgrp[2 * kNPair];  // group that holds the running minimum
 #pragma unroll
@@ -185,9 +229,12 @@ dense_chi2_kernel(const float* __restrict__ tiles, int64_t n_tiles, int tiles_pe
           return __any_sync(0xffffffffu, need) != 0;
         };
         need_mask = 0;
+        const float dw = fmaxf(fmaxf(bx[pb] - whi, wlo - bx[NB + pb]), 0.0f) * bx[2 * NB + pb];
+        if (fmaf(dw, dw, bx[3 * NB]) * 0.99998474f < cutmax) {  // warp-uniform
 #pragma unroll
-        for (int p = 0; p < kNPair; ++p) {
-          if (pair_needs(bx, p)) need_mask |= 1u << p;  // the pair's 64 stars meet the group
+          for (int p = 0; p < kNPair; ++p) {
+            if (pair_needs(bx, p)) need_mask |= 1u << p;  // the pair's 64 stars meet the group
+          }
         }
         if (need_mask == 0) {
 #pragma unroll
