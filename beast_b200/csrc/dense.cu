@@ -132,7 +132,6 @@ dense_chi2_kernel(const float* __restrict__ tiles, int64_t n_tiles, int tiles_pe
   // the largest of their ceilings.  Six instructions rule out most groups before any star is
   // looked at.
   float wlo = kInf, whi = -kInf, cutmax = -kInf;
-  float plo[kNPair], phi[kNPair], pcut[kNPair];  // the same per pair of 64 stars, in band pb
   int pb = 0;
   if constexpr (PRUNE) {
     float cq[2 * kNPair];
@@ -140,6 +139,7 @@ dense_chi2_kernel(const float* __restrict__ tiles, int64_t n_tiles, int tiles_pe
     for (int q = 0; q < 2 * kNPair; ++q) {
       cq[q] = cut[star0 + wbase + q * 32];
       cut_s[wbase + q * 32] = cq[q];
+      cutmax = fmaxf(cutmax, cq[q]);
     }
     float best = kInf;
 #pragma unroll
@@ -172,29 +172,7 @@ dense_chi2_kernel(const float* __restrict__ tiles, int64_t n_tiles, int tiles_pe
       }
     }
 #pragma unroll
-    for (int p = 0; p < kNPair; ++p) {
-      float lo = kInf, hi = -kInf;
-#pragma unroll
-      for (int b = 0; b < NB; ++b) {
-        if (b == pb) {
-          float fl, fh;
-          unpack2(f[p][b], fl, fh);
-          if (cq[2 * p] >= 0.0f) lo = fminf(lo, fl), hi = fmaxf(hi, fl);
-          if (cq[2 * p + 1] >= 0.0f) lo = fminf(lo, fh), hi = fmaxf(hi, fh);
-        }
-      }
-      float c = fmaxf(cq[2 * p], cq[2 * p + 1]);
-#pragma unroll
-      for (int d = 16; d > 0; d >>= 1) {
-        lo = fminf(lo, __shfl_xor_sync(0xffffffffu, lo, d));
-        hi = fmaxf(hi, __shfl_xor_sync(0xffffffffu, hi, d));
-        c = fmaxf(c, __shfl_xor_sync(0xffffffffu, c, d));
-      }
-      plo[p] = lo;
-      phi[p] = hi;
-      pcut[p] = c;
-      cutmax = fmaxf(cutmax, c);
-    }
+    for (int d = 16; d > 0; d >>= 1) cutmax = fmaxf(cutmax, __shfl_xor_sync(0xffffffffu, cutmax, d));
     __syncwarp();  // a thread reads back only what it wrote; the fence keeps the order explicit
   }
 
@@ -234,8 +212,6 @@ dense_chi2_kernel(const float* __restrict__ tiles, int64_t n_tiles, int tiles_pe
         // A group's record: the box of its 64 models, then the boxes of its two halves.
         const float* bx = box_buf + stage * (GROUPS_PER_TILE * BOXF) + g * BOXF;
         auto pair_needs = [&](const float* box, int p) {  // does a star of pair p get below its ceiling?
-          const float dp = fmaxf(fmaxf(box[pb] - phi[p], plo[p] - box[NB + pb]), 0.0f) * box[2 * NB + pb];
-          if (!(fmaf(dp, dp, box[3 * NB]) * 0.99998474f < pcut[p])) return false;  // warp-uniform: band pb alone
           float lo = box[3 * NB], hi = lo;
 #pragma unroll
           for (int b = 0; b < NB; ++b) {
