@@ -64,6 +64,7 @@ class ParamTables(C.Structure):
         ("slow_bin", c_void_p),
         ("slow_q", c_void_p),
         ("slow_run", c_void_p),
+        ("fast_rng", c_void_p),
     ]
 
 

@@ -672,7 +672,15 @@ __device__ __forceinline__ void class_ranges(const bf_param_tables& prm, const u
       const uint32_t i = base + u * step;
       chunk[u] = refs[i < n_mc ? i : base].x;  // (a repeated chunk changes nothing)
     }
-    if (FAST) {
+    if (FAST && prm.fast_rng != nullptr) {  // the chunks' own bin ranges: 2 bytes instead of 8
+      uint32_t v[4];
+#pragma unroll
+      for (int u = 0; u < 4; ++u) v[u] = __ldg(prm.fast_rng + static_cast<size_t>(chunk[u]) * prm.fast_pad + p);
+      const uint32_t lo01 = (v[0] & 0xffu) | ((v[1] & 0xffu) << 16), lo23 = (v[2] & 0xffu) | ((v[3] & 0xffu) << 16);
+      const uint32_t hi01 = (v[0] >> 8) | ((v[1] >> 8) << 16), hi23 = (v[2] >> 8) | ((v[3] >> 8) << 16);
+      mn2 = __vimin3_u16x2(mn2, lo01, lo23);
+      mx2 = __vimax3_u16x2(mx2, hi01, hi23);
+    } else if (FAST) {
       uint2 bb[4];
 #pragma unroll
       for (int u = 0; u < 4; ++u)

@@ -156,6 +156,7 @@ class FitEngine:
                 self.d_fast_bin, self.d_fast_q = up(s.fast_bin), up(s.fast_q)
                 self.d_slow_bin, self.d_slow_q = up(s.slow_bin), up(s.slow_q)
                 self.d_slow_run = up(s.slow_run)
+                self.d_fast_rng = up(s.fast_rng.view(np.int16))
             self.d_inv_scale = up((1.0 / s.band_scale).astype(np.float64))
             if s.pair_bin is not None:
                 self.d_pair_bin, self.d_pair_off = up(s.pair_bin), up(s.pair_off)
@@ -177,6 +178,7 @@ class FitEngine:
             p.fast_bin, p.fast_q = self.d_fast_bin.data_ptr(), self.d_fast_q.data_ptr()
             p.slow_bin, p.slow_q = self.d_slow_bin.data_ptr(), self.d_slow_q.data_ptr()
             p.slow_run = self.d_slow_run.data_ptr()
+            p.fast_rng = self.d_fast_rng.data_ptr()
         per_star = s.n_groups * 4
         mb = max(STAR_BLOCK, (gmin_budget_bytes // per_star) // STAR_BLOCK * STAR_BLOCK)
         mb = min(mb, ((2**31 - 1) // max(s.n_groups, 1)) // STAR_BLOCK * STAR_BLOCK, 32768 * STAR_BLOCK)

@@ -410,6 +410,7 @@ class FitSetup:
         self.slow_pad = 16 if nsl <= 16 else 32
         if not self.split_ok:
             self.fast_bin = self.fast_q = self.slow_bin = self.slow_q = self.slow_run = None
+            self.fast_rng = None
             return
         fb = np.zeros((nch if nf else 1, self.fast_pad, CHUNK), dtype=np.uint8)
         fq = np.zeros((nch if nf else 1, 2, self.fast_pad, CHUNK // 2), dtype=np.int32)
@@ -422,6 +423,8 @@ class FitSetup:
             sb[:, i] = b3[k][:, 0]
             sq[:, i] = q3[k][:, 0]
         self.fast_bin, self.fast_q, self.slow_bin, self.slow_q = fb, fq, sb, sq
+        # bin range of every chunk's 8 models, per fast parameter: lo | hi << 8
+        self.fast_rng = (fb.min(axis=2).astype(np.uint16) | (fb.max(axis=2).astype(np.uint16) << 8))
         # runs of chunks with the same slow values inside a group of 8 chunks: bit c of
         # slow_run[g] = chunk c starts a run (bit 0 always).  The weights kernel sums the weights
         # per run, so the slow parameters take one update per run, not per chunk.

@@ -238,7 +238,10 @@ typedef struct {
    *                                         0..3 of all parameters, then models 4..7
    *   slow_bin [ld_model/8][slow_pad] u8,  slow_q [ld_model/8][slow_pad] int32
    *   slow_run [ld_model/64] u8             bit c: chunk c of the group starts a run of chunks
-   *                                         with equal slow values (bit 0 always set) */
+   *                                         with equal slow values (bit 0 always set)
+   *   fast_rng [ld_model/8][fast_pad] u16   optional (may be NULL): smallest bin | largest bin << 8
+   *                                         of the chunk's 8 models, what the histogram kernel
+   *                                         sizes its private copies from */
   int n_fast, n_slow, fast_pad, slow_pad;
   const int32_t* fast_k;
   const int32_t* slow_k;
@@ -247,6 +250,7 @@ typedef struct {
   const uint8_t* slow_bin;
   const int32_t* slow_q;
   const uint8_t* slow_run;
+  const uint16_t* fast_rng;
 } bf_param_tables;
 
 typedef struct {
