@@ -254,10 +254,14 @@ dense_chi2_kernel(const float* __restrict__ tiles, int64_t n_tiles, int tiles_pe
         n_eval += __popc(need_mask);
       }
       if constexpr (!COV) {
+#pragma unroll 1
+        for (int hf = 0; hf < 2; ++hf) {
+        // (pruned: the pairs that meet this half of the group; a half nobody meets is not walked)
+        const unsigned live = PRUNE ? (need_mask >> (hf * kNPair)) & ((1u << kNPair) - 1) : need_mask;
+        if (PRUNE && live == 0) continue;
+        const int m0 = g * BF_GROUP + hf * (BF_GROUP / 2);
 #pragma unroll 2
-        for (int m = g * BF_GROUP; m < (g + 1) * BF_GROUP; m += 2) {
-          // (pruned: the pairs of this half of the group)
-          const unsigned live = PRUNE ? need_mask >> (((m / (BF_GROUP / 2)) & 1) * kNPair) : need_mask;
+        for (int m = m0; m < m0 + BF_GROUP / 2; m += 2) {
           float2 r[NB], na[NB];
 #pragma unroll
           for (int b = 0; b < NB; ++b) {
@@ -283,6 +287,7 @@ dense_chi2_kernel(const float* __restrict__ tiles, int64_t n_tiles, int tiles_pe
             rmin[2 * p] = min3(rmin[2 * p], a0l, a1l);
             rmin[2 * p + 1] = min3(rmin[2 * p + 1], a0h, a1h);
           }
+        }
         }
       } else {
         constexpr int NP = NB * (NB - 1) / 2;
