@@ -43,15 +43,14 @@ constexpr int kNPair = BF_STAR_BLOCK / kDenseThreads / 2;  // star pairs per thr
 template <int NB, bool COV, bool PRUNE = false>
 struct DenseSmem {
   static constexpr int kRows = COV ? 2 * NB + NB * (NB - 1) / 2 + 1 : 2 * NB + 1;
-  // (the pruned sweep passes over most tiles quickly: one more stage and tile in flight)
-  static constexpr int kStages = COV ? 3 : (PRUNE ? 5 : 4);
-  static constexpr int kPrefetch = COV ? 1 : (PRUNE ? 3 : 2);  // tiles in flight ahead of the consumer
+  static constexpr int kStages = COV ? 3 : 4;
+  static constexpr int kPrefetch = COV ? 1 : 2;  // tiles in flight ahead of the consumer
   static constexpr uint32_t kTileBytes = kRows * BF_TILE_MODELS * sizeof(float);
   // group boxes of a tile: per group 3 x (mlo[NB], mhi[NB], rlo[NB], c2min) -- the group and its
   // two halves --, padded to 16 bytes
   static constexpr int kBoxFloats = BF_BOX_FLOATS(NB);
   static constexpr uint32_t kBoxBytes = PRUNE ? (BF_TILE_MODELS / BF_GROUP) * kBoxFloats * sizeof(float) : 0;
-  static constexpr uint32_t kCutBytes = 0;  // (the stars' ceilings live in registers)
+  static constexpr uint32_t kCutBytes = PRUNE ? BF_STAR_BLOCK * sizeof(float) : 0;
   static constexpr uint32_t kBytes =
       kStages * (kTileBytes + kBoxBytes) + kCutBytes + 2 * kStages * sizeof(uint64_t);
 };
@@ -78,6 +77,7 @@ dense_chi2_kernel(const float* __restrict__ tiles, int64_t n_tiles, int tiles_pe
   extern __shared__ __align__(128) unsigned char smem_raw[];
   float* stage_buf = reinterpret_cast<float*>(smem_raw);
   float* box_buf = reinterpret_cast<float*>(smem_raw + kDenseStages * TILE_BYTES);
+  float* cut_s = reinterpret_cast<float*>(smem_raw + kDenseStages * (TILE_BYTES + BOX_BYTES));
   uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem_raw + kDenseStages * (TILE_BYTES + BOX_BYTES) +
                                                    Smem::kCutBytes);
   uint64_t* empty_bar = full_bar + kDenseStages;
@@ -133,11 +133,12 @@ dense_chi2_kernel(const float* __restrict__ tiles, int64_t n_tiles, int tiles_pe
   // looked at.
   float wlo = kInf, whi = -kInf, cutmax = -kInf;
   int pb = 0;
-  float cq[2 * kNPair];  // this thread's stars' ceilings
   if constexpr (PRUNE) {
+    float cq[2 * kNPair];
 #pragma unroll
     for (int q = 0; q < 2 * kNPair; ++q) {
       cq[q] = cut[star0 + wbase + q * 32];
+      cut_s[wbase + q * 32] = cq[q];
       cutmax = fmaxf(cutmax, cq[q]);
     }
     float best = kInf;
@@ -172,6 +173,7 @@ dense_chi2_kernel(const float* __restrict__ tiles, int64_t n_tiles, int tiles_pe
     }
 #pragma unroll
     for (int d = 16; d > 0; d >>= 1) cutmax = fmaxf(cutmax, __shfl_xor_sync(0xffffffffu, cutmax, d));
+    __syncwarp();  // a thread reads back only what it wrote; the fence keeps the order explicit
   }
 
   float rmin[2 * kNPair], smin[2 * kNPair];
@@ -222,7 +224,8 @@ dense_chi2_kernel(const float* __restrict__ tiles, int64_t n_tiles, int tiles_pe
             hi = fmaf(dh, dh, hi);
           }
           // 1 - 2^-16 covers the FP32 rounding of both this bound and the accumulators below
-          const bool need = lo * 0.99998474f < cq[2 * p] || hi * 0.99998474f < cq[2 * p + 1];
+          const bool need = lo * 0.99998474f < cut_s[wbase + (2 * p) * 32] ||
+                            hi * 0.99998474f < cut_s[wbase + (2 * p + 1) * 32];
           return __any_sync(0xffffffffu, need) != 0;
         };
         need_mask = 0;
