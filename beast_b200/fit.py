@@ -324,6 +324,10 @@ def _load_grid(sedgrid, gridbackend):
     return sedgrid
 
 
+# stars in the last batch of a multi-batch call (its result copy is the only one not hidden)
+TAIL_BATCH = int(os.environ.get("BF_TAIL_BATCH", "8192"))
+
+
 def _collect_fluxes(obs, start):
     """(n - start, nb) float64 fluxes of stars start.. in catalog order (fit.py:633-639)"""
     arr = getattr(obs, "fluxes", None)
@@ -491,7 +495,7 @@ def Q_all_memory(prev_result, obs, sedgrid, obsmodel, qnames_in, p=[16.0, 50.0, 
         engine.fit(fluxes, threshold=float(threshold), percentiles=tuple(trios[0]),
                    want_pdf2d=make_pdf2d, sparse=sparse, lnp_rng=lnp_rng, seed=start_pos, batch=bs,
                    result=res, row_offset=start_pos, on_batch=checkpoint,
-                   tail_batch=8192 if save_every_npts is None else 0)
+                   tail_batch=TAIL_BATCH if save_every_npts is None else 0)
     if len(pvals) != 3:  # any list of percentiles (fit.py:749-753): three per pass on the device
         from .subgrid import CudaMergeMath
 
