@@ -136,8 +136,8 @@ int launch_weights_grouped(const bf_exact_grid& grid, const double* flux64, cons
 bool split_hist_supported(const bf_param_tables& prm, size_t smem_budget);
 int launch_split_hist(const bf_param_tables& prm, const double* pmax, const uint32_t* offsets,
                       const uint32_t* list, const int32_t* star_order, int64_t star_begin,
-                      int64_t n_stars, int64_t entry_base, const bf_accum_scratch& sc, double p0,
-                      double p1, double p2, const bf_star_outputs& out, size_t smem_budget,
-                      cudaStream_t st);
+                      int64_t n_stars, int64_t entry_base, int64_t n_entries,
+                      const bf_accum_scratch& sc, double p0, double p1, double p2,
+                      const bf_star_outputs& out, size_t smem_budget, cudaStream_t st);
 
 }  // namespace bf

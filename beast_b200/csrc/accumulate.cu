@@ -922,7 +922,7 @@ extern "C" int bf_exact_accumulate(const bf_exact_grid* grid, const bf_param_tab
   // windowed kernel, one worst-case private copy per class; it does every expectation itself
   if (want_split) {
     const int rc = launch_split_hist(*params, pmax, offsets, list, star_order, star_begin, n_stars,
-                                     entry_base, *scratch, percentiles_host[0], percentiles_host[1],
+                                     entry_base, n_entries, *scratch, percentiles_host[0], percentiles_host[1],
                                      percentiles_host[2], *out, budget, st);
     if (rc != BF_OK) return rc;
     if (timing) {

@@ -364,6 +364,7 @@ constexpr int kSplitWarpsMax = 20;
 // chunks of a star's list worked through at a time (C2: 54 ms per 33,792 stars with or without
 // segments of this size; C5, whose subgrid posteriors are broad: 2.0 s -> 1.6 s per 16,384 stars)
 constexpr uint32_t kSegmentChunks = 16384;
+constexpr int64_t kNarrowListedGroups = 2000;  // mean listed groups per star below which two blocks share an SM
 
 // shared memory: hist [hist_doubles] | red [2 NW] | redj [NW] | sscan (NW u32, as NW/2 doubles)
 //   | epart [NW][32] | int tables (see kernel); sized for the largest block
@@ -1029,16 +1030,21 @@ bool split_hist_supported(const bf_param_tables& prm, size_t smem_budget) {
 
 int launch_split_hist(const bf_param_tables& prm, const double* pmax, const uint32_t* offsets,
                       const uint32_t* list, const int32_t* star_order, int64_t star_begin,
-                      int64_t n_stars, int64_t entry_base, const bf_accum_scratch& sc, double p0,
-                      double p1, double p2, const bf_star_outputs& out, size_t smem_budget,
-                      cudaStream_t st) {
-  // One block of 20 warps per SM.  BF_SPLIT_WARPS=10: two blocks of 10 warps when a worst-case
-  // star fits half the shared memory (measured slower at C2: 90 vs 67 ms per 33,792 stars -- a
-  // broad star then has half the private copies).
+                      int64_t n_stars, int64_t entry_base, int64_t n_entries,
+                      const bf_accum_scratch& sc, double p0, double p1, double p2,
+                      const bf_star_outputs& out, size_t smem_budget, cudaStream_t st) {
+  // One block of 20 warps per SM, or two of 10 warps (when a worst-case star fits half the shared
+  // memory) for a range of stars with short lists: a narrow star cannot use 20 warps' worth of
+  // private copies, and with two blocks one star's serial phases (lists, ranges, merge,
+  // percentiles) overlap the other's accumulation.  Measured per range of one C2 batch (listed
+  // groups per star: 12,800 / 3,000 / 610): 27.9 / 13.8 / 11.5 ms with one block, 35.3 / 13.6 / 9.5
+  // with two -- a broad star then has half the copies.  BF_SPLIT_WARPS=20 | 1x forces either.
   const size_t half = (smem_budget + 1024) / 2 - 1024;
   int warps = kSplitWarpsMax;
-  if (const char* env = getenv("BF_SPLIT_WARPS"))
-    if (env[0] == '1' && split_fits(prm, half, kSplitWarpsMax / 2)) warps = kSplitWarpsMax / 2;
+  const bool narrow = n_stars > 0 && n_entries / n_stars < kNarrowListedGroups;
+  const char* env = getenv("BF_SPLIT_WARPS");
+  const bool want_half = env ? env[0] == '1' : narrow;
+  if (want_half && split_fits(prm, half, kSplitWarpsMax / 2)) warps = kSplitWarpsMax / 2;
   const int hd = split_hist_doubles(warps == kSplitWarpsMax ? smem_budget : half);
   uint32_t seg_chunks = kSegmentChunks;  // BF_SEG=<chunks>: measurements
   if (const char* env = getenv("BF_SEG")) seg_chunks = static_cast<uint32_t>(strtoul(env, nullptr, 10));
