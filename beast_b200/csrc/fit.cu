@@ -341,11 +341,8 @@ extern "C" int bf_fit_batch(const bf_fit_plan* plan, int64_t n_stars, const doub
     if (p.boxes && !cov && nb <= 12 && !no_prune) {
       float* c = ar.take<float>(ld);
       evaluated = ar.take<uint64_t>(1);
-      // (the selection stages a sixteenth of the flags of a run of stars in shared memory)
-      if ((p.n_groups + BF_SELECT_SPLIT - 1) / BF_SELECT_SPLIT <= 48 * 1024) {
-        skipmap = ar.take<uint8_t>(static_cast<size_t>(ld / 256) * p.n_groups);
-        BF_WS(skipmap);
-      }
+      skipmap = ar.take<uint8_t>(static_cast<size_t>(ld / 256) * p.n_groups);
+      BF_WS(skipmap);
       BF_CUDA_TRY(cudaMemsetAsync(evaluated, 0, sizeof(uint64_t), st));
       prune_cut_kernel<<<blocks_for(ld), kT, 0, st>>>(n, ld, perm, starmin, tau, p.err_a, p.err_b, c);
       cut = c;

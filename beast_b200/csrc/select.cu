@@ -25,24 +25,15 @@ select_kernel(int64_t n_groups, int64_t n_stars, int64_t ld_star, const float* _
               const uint32_t* __restrict__ offsets, uint32_t* __restrict__ list,
               uint32_t* __restrict__ entry_star, const uint8_t* __restrict__ skipmap) {
   const int64_t s = static_cast<int64_t>(blockIdx.x) * kSelThreads + threadIdx.x;
+  if (s >= n_stars) return;
+  // skipmap[star / 256][group] != 0: the pruned dense sweep left the group out for these 256
+  // stars and wrote nothing -- not selected, and gmin is not read (the same byte for the whole
+  // thread block, whose 128 stars lie in one run of 256)
+  const uint8_t* skip = skipmap ? skipmap + (s >> 8) * n_groups : nullptr;
   const int c = blockIdx.y;
   const int64_t per = (n_groups + BF_SELECT_SPLIT - 1) / BF_SELECT_SPLIT;
   const int64_t g0 = c * per;
   const int64_t g1 = min(n_groups, g0 + per);
-  // skipmap[star / 256][group] != 0: the pruned dense sweep left the group out for these 256
-  // stars and wrote nothing -- not selected, and gmin is not read.  The flags of this block's
-  // groups (the same for its 128 stars, which lie in one run of 256) are staged in shared memory
-  // first, so that the loop below decides from shared memory which values to request and keeps
-  // eight of them in flight.
-  extern __shared__ uint8_t skip_s[];
-  const uint8_t* skip = nullptr;
-  if (skipmap != nullptr) {
-    const uint8_t* src = skipmap + ((static_cast<int64_t>(blockIdx.x) * kSelThreads) >> 8) * n_groups + g0;
-    for (int64_t i = threadIdx.x; i < g1 - g0; i += kSelThreads) skip_s[i] = __ldg(src + i);
-    __syncthreads();
-    skip = skip_s - g0;  // indexed by group
-  }
-  if (s >= n_stars) return;
   const float thr = select_threshold(starmin_value(starmin[s]), tau, err_a, err_b);
   const float* p = gmin + s;
   uint32_t n = 0;
@@ -53,7 +44,7 @@ select_kernel(int64_t n_groups, int64_t n_stars, int64_t ld_star, const float* _
     if (skip) {
       uint8_t k[8];
 #pragma unroll
-      for (int u = 0; u < 8; ++u) k[u] = skip[g + u];
+      for (int u = 0; u < 8; ++u) k[u] = __ldg(skip + g + u);
 #pragma unroll
       for (int u = 0; u < 8; ++u) v[u] = k[u] ? __int_as_float(0x7f800000) : __ldg(p + (g + u) * ld_star);
     } else {
@@ -73,7 +64,7 @@ select_kernel(int64_t n_groups, int64_t n_stars, int64_t ld_star, const float* _
     }
   }
   for (; g < g1; ++g) {
-    if (skip && skip[g]) continue;
+    if (skip && __ldg(skip + g)) continue;
     if (__ldg(p + g * ld_star) < thr) {
       if (FILL) {
         list[pos] = static_cast<uint32_t>(g);
@@ -198,9 +189,7 @@ extern "C" int bf_select_count_skip(int64_t n_groups, int64_t n_stars, int64_t l
   BF_REQUIRE(n_groups > 0 && n_stars > 0 && ld_star >= n_stars, "bf_select_count: bad sizes");
   BF_REQUIRE(gmin && starmin && counts, "bf_select_count: null pointer");
   dim3 grid(static_cast<unsigned>((n_stars + kSelThreads - 1) / kSelThreads), BF_SELECT_SPLIT);
-  const size_t flags = skipmap ? static_cast<size_t>((n_groups + BF_SELECT_SPLIT - 1) / BF_SELECT_SPLIT) : 0;
-  BF_REQUIRE(flags <= 48 * 1024, "bf_select_count_skip: more than %d groups with a skip map", 48 * 1024 * BF_SELECT_SPLIT);
-  select_kernel<false><<<grid, kSelThreads, flags, static_cast<cudaStream_t>(stream)>>>(
+  select_kernel<false><<<grid, kSelThreads, 0, static_cast<cudaStream_t>(stream)>>>(
       n_groups, n_stars, ld_star, gmin, reinterpret_cast<const unsigned long long*>(starmin), tau,
       err_a, err_b, counts, nullptr, nullptr, nullptr, skipmap);
   BF_CHECK_LAUNCH("select_kernel<count>");
@@ -223,9 +212,7 @@ extern "C" int bf_select_fill_skip(int64_t n_groups, int64_t n_stars, int64_t ld
   BF_REQUIRE(n_groups > 0 && n_stars > 0 && ld_star >= n_stars, "bf_select_fill: bad sizes");
   BF_REQUIRE(gmin && starmin && offsets && list, "bf_select_fill: null pointer");
   dim3 grid(static_cast<unsigned>((n_stars + kSelThreads - 1) / kSelThreads), BF_SELECT_SPLIT);
-  const size_t flags = skipmap ? static_cast<size_t>((n_groups + BF_SELECT_SPLIT - 1) / BF_SELECT_SPLIT) : 0;
-  BF_REQUIRE(flags <= 48 * 1024, "bf_select_fill_skip: more than %d groups with a skip map", 48 * 1024 * BF_SELECT_SPLIT);
-  select_kernel<true><<<grid, kSelThreads, flags, static_cast<cudaStream_t>(stream)>>>(
+  select_kernel<true><<<grid, kSelThreads, 0, static_cast<cudaStream_t>(stream)>>>(
       n_groups, n_stars, ld_star, gmin, reinterpret_cast<const unsigned long long*>(starmin), tau,
       err_a, err_b, nullptr, offsets, list, entry_star, skipmap);
   BF_CHECK_LAUNCH("select_kernel<fill>");
