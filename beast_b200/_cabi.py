@@ -160,16 +160,12 @@ PROTOTYPES = {
     "bf_dense_chi2": (C.c_int, [C.c_int, i64, c_void_p, i64, i64, c_void_p, c_void_p, c_void_p,
                                 C.c_int, c_void_p]),
     "bf_dense_chi2_pruned": (C.c_int, [C.c_int, i64, c_void_p, c_void_p, i64, i64, c_void_p, c_void_p, c_void_p,
-                                       c_void_p, C.c_int, c_void_p, c_void_p, c_void_p]),
+                                       c_void_p, C.c_int, c_void_p, c_void_p]),
     "bf_dense_chi2_cov": (C.c_int, [C.c_int, i64, c_void_p, i64, i64, c_void_p, c_void_p, c_void_p,
                                     C.c_int, c_void_p]),
     "bf_dense_tiles_per_item": (C.c_int, [i64, i64, C.c_int]),
     "bf_select_count": (C.c_int, [i64, i64, i64, c_void_p, c_void_p, C.c_float, C.c_float,
                                   C.c_float, c_void_p, c_void_p]),
-    "bf_select_count_skip": (C.c_int, [i64, i64, i64, c_void_p, c_void_p, C.c_float, C.c_float,
-                                       C.c_float, c_void_p, c_void_p, c_void_p]),
-    "bf_select_fill_skip": (C.c_int, [i64, i64, i64, c_void_p, c_void_p, C.c_float, C.c_float,
-                                      C.c_float, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]),
     "bf_select_fill": (C.c_int, [i64, i64, i64, c_void_p, c_void_p, C.c_float, C.c_float,
                                  C.c_float, c_void_p, c_void_p, c_void_p, c_void_p]),
     "bf_scan_scratch_elems": (i64, [i64]),

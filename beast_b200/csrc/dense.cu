@@ -63,8 +63,7 @@ __global__ void __launch_bounds__(kDenseThreads, COV ? 2 : 3)
 dense_chi2_kernel(const float* __restrict__ tiles, int64_t n_tiles, int tiles_per_item,
                   const float* __restrict__ flux, int64_t ld_star, float* __restrict__ gmin,
                   unsigned long long* __restrict__ starmin, const float* __restrict__ boxes,
-                  const float* __restrict__ cut, unsigned long long* __restrict__ evaluated,
-                  uint8_t* __restrict__ skipmap, int64_t n_groups) {
+                  const float* __restrict__ cut, unsigned long long* __restrict__ evaluated) {
   constexpr int TM = BF_TILE_MODELS;
   using Smem = DenseSmem<NB, COV, PRUNE>;
   constexpr int ROWS = Smem::kRows;
@@ -237,13 +236,9 @@ dense_chi2_kernel(const float* __restrict__ tiles, int64_t n_tiles, int tiles_pe
             if (pair_needs(bx, p)) need_mask |= 1u << p;  // the pair's 64 stars meet the group
           }
         }
-        if (skipmap != nullptr && lane == 0)  // [star / 256][group]: 1 = left out, gmin not written
-          skipmap[((star0 + wbase) >> 8) * n_groups + gidx] = need_mask == 0 ? 1 : 0;
         if (need_mask == 0) {
-          if (skipmap == nullptr) {
 #pragma unroll
-            for (int q = 0; q < 2 * kNPair; ++q) gp[q * 32] = kInf;
-          }
+          for (int q = 0; q < 2 * kNPair; ++q) gp[q * 32] = kInf;
           continue;
         }
         // the pairs that do: which half of the group (bits p: first 32 models, kNPair + p: second)
@@ -368,7 +363,7 @@ template <int NB, bool COV, bool PRUNE = false>
 static int launch_dense(int64_t n_tiles, const float* tiles, int64_t ld_star, const float* flux,
                         float* gmin, unsigned long long* starmin, int tiles_per_item,
                         cudaStream_t st, const float* boxes = nullptr, const float* cut = nullptr,
-                        unsigned long long* evaluated = nullptr, uint8_t* skipmap = nullptr) {
+                        unsigned long long* evaluated = nullptr) {
   auto kern = dense_chi2_kernel<NB, COV, PRUNE>;
   static bool configured[64] = {};
   int dev = 0;
@@ -381,8 +376,7 @@ static int launch_dense(int64_t n_tiles, const float* tiles, int64_t ld_star, co
   const int64_t n_items = (n_tiles + tiles_per_item - 1) / tiles_per_item;
   dim3 grid(static_cast<unsigned>(n_items), static_cast<unsigned>(ld_star / BF_STAR_BLOCK));
   kern<<<grid, kDenseThreads, DenseSmem<NB, COV, PRUNE>::kBytes, st>>>(
-      tiles, n_tiles, tiles_per_item, flux, ld_star, gmin, starmin, boxes, cut, evaluated, skipmap,
-      n_tiles * (BF_TILE_MODELS / BF_GROUP));
+      tiles, n_tiles, tiles_per_item, flux, ld_star, gmin, starmin, boxes, cut, evaluated);
   BF_CHECK_LAUNCH("dense_chi2_kernel");
   return BF_OK;
 }
@@ -457,8 +451,7 @@ extern "C" int bf_dense_chi2_cov(int nb, int64_t n_tiles, const float* tiles, in
 extern "C" int bf_dense_chi2_pruned(int nb, int64_t n_tiles, const float* tiles, const float* boxes,
                                     int64_t n_stars, int64_t ld_star, const float* flux,
                                     const float* cut, float* gmin, uint64_t* starmin,
-                                    int tiles_per_item, uint64_t* evaluated, uint8_t* skipmap,
-                                    void* stream) {
+                                    int tiles_per_item, uint64_t* evaluated, void* stream) {
   using namespace bf;
   BF_REQUIRE(nb >= 1 && nb <= 12, "bf_dense_chi2_pruned: nb=%d not instantiated (1..12)", nb);
   BF_REQUIRE(n_tiles > 0 && n_stars > 0, "bf_dense_chi2_pruned: empty problem");
@@ -474,7 +467,7 @@ extern "C" int bf_dense_chi2_pruned(int nb, int64_t n_tiles, const float* tiles,
 #define BF_CASE(N) \
   case N:          \
     return launch_dense<N, false, true>(n_tiles, tiles, ld_star, flux, gmin, sm, tiles_per_item, st, boxes, cut, \
-                                        reinterpret_cast<unsigned long long*>(evaluated), skipmap);
+                                        reinterpret_cast<unsigned long long*>(evaluated));
     BF_CASE(1) BF_CASE(2) BF_CASE(3) BF_CASE(4) BF_CASE(5) BF_CASE(6) BF_CASE(7) BF_CASE(8)
     BF_CASE(9) BF_CASE(10) BF_CASE(11) BF_CASE(12)
 #undef BF_CASE

@@ -223,7 +223,7 @@ extern "C" int64_t bf_fit_workspace_bytes(const bf_fit_plan* plan, int64_t n_sta
   b += 2 * static_cast<size_t>(n_stars) * p.nb * 8;            // flux copies
   b += static_cast<size_t>(p.nb) * ld * 4;                      // flux32
   b += static_cast<size_t>(p.n_tiles) * (BF_TILE_MODELS / BF_GROUP) * ld * 4;  // group minima
-  b += static_cast<size_t>(ld) * 12 + 256 + static_cast<size_t>(ld / 256) * p.n_groups + 256;  // starmin, selection ceilings, counter, skip map
+  b += static_cast<size_t>(ld) * 12 + 256;                      // starmin, selection ceilings, counter
   b += (2 * static_cast<size_t>(n_stars) * BF_SELECT_SPLIT + 2) * 4 + bf_scan_scratch_elems(n_stars * BF_SELECT_SPLIT) * 4;
   b += static_cast<size_t>(n_stars) * (4 * 4 + 4 + 8 + 4) + 2 * sort_temp_bytes(n_stars);
   // results in sorted order
@@ -300,14 +300,13 @@ extern "C" int bf_fit_batch(const bf_fit_plan* plan, int64_t n_stars, const doub
   const float tau = static_cast<float>(-2.0 * threshold);
   const float* cut = nullptr;  // set by the presort when the dense sweep may skip groups
   uint64_t* evaluated = nullptr;
-  uint8_t* skipmap = nullptr;  // groups the pruned sweep leaves out, per run of 256 stars
   auto dense = [&](int64_t n_tiles, const float* tiles, float* gmin, bool prune) -> int {
     starmin_init_kernel<<<blocks_for(ld), kT, 0, st>>>(ld, starmin);
     const int tpi = bf_dense_tiles_per_item(n_tiles, n, sm_count);
     launches += 2;
     if (prune)
       return bf_dense_chi2_pruned(nb, n_tiles, tiles, p.boxes, n, ld, flux32, cut, gmin,
-                                  reinterpret_cast<uint64_t*>(starmin), tpi, evaluated, skipmap, stream);
+                                  reinterpret_cast<uint64_t*>(starmin), tpi, evaluated, stream);
     return cov ? bf_dense_chi2_cov(nb, n_tiles, tiles, n, ld, flux32, gmin, reinterpret_cast<uint64_t*>(starmin), tpi, stream)
                : bf_dense_chi2(nb, n_tiles, tiles, n, ld, flux32, gmin, reinterpret_cast<uint64_t*>(starmin), tpi, stream);
   };
@@ -341,8 +340,7 @@ extern "C" int bf_fit_batch(const bf_fit_plan* plan, int64_t n_stars, const doub
     if (p.boxes && !cov && nb <= 12 && !no_prune) {
       float* c = ar.take<float>(ld);
       evaluated = ar.take<uint64_t>(1);
-      skipmap = ar.take<uint8_t>(static_cast<size_t>(ld / 256) * p.n_groups);
-      BF_WS(skipmap);
+      BF_WS(evaluated);
       BF_CUDA_TRY(cudaMemsetAsync(evaluated, 0, sizeof(uint64_t), st));
       prune_cut_kernel<<<blocks_for(ld), kT, 0, st>>>(n, ld, perm, starmin, tau, p.err_a, p.err_b, c);
       cut = c;
@@ -368,7 +366,7 @@ extern "C" int bf_fit_batch(const bf_fit_plan* plan, int64_t n_stars, const doub
   uint32_t* off_star = ar.take<uint32_t>(n + 1);
   int64_t* n_listed = ar.take<int64_t>(n);
   BF_WS(n_listed);
-  rc = bf_select_count_skip(p.n_groups, n, ld, gmin, reinterpret_cast<uint64_t*>(starmin), tau, p.err_a, p.err_b, skipmap, counts, stream);
+  rc = bf_select_count(p.n_groups, n, ld, gmin, reinterpret_cast<uint64_t*>(starmin), tau, p.err_a, p.err_b, counts, stream);
   if (rc != BF_OK) return rc;
   rc = bf_exclusive_scan_u32(nc, counts, offsets, scan_tmp, stream);
   if (rc != BF_OK) return rc;
@@ -387,7 +385,7 @@ extern "C" int bf_fit_batch(const bf_fit_plan* plan, int64_t n_stars, const doub
   uint32_t* mask = ar.take<uint32_t>(tot1 * (BF_GROUP / 32));
   uint32_t* prefix = ar.take<uint32_t>(tot1);
   BF_WS(prefix);
-  rc = bf_select_fill_skip(p.n_groups, n, ld, gmin, reinterpret_cast<uint64_t*>(starmin), tau, p.err_a, p.err_b, skipmap, offsets, list, entry_star, stream);
+  rc = bf_select_fill(p.n_groups, n, ld, gmin, reinterpret_cast<uint64_t*>(starmin), tau, p.err_a, p.err_b, offsets, list, entry_star, stream);
   if (rc != BF_OK) return rc;
 
   // ---- results in sorted order (scattered back at the end) --------------------------------

@@ -23,13 +23,9 @@ select_kernel(int64_t n_groups, int64_t n_stars, int64_t ld_star, const float* _
               float err_b,
               uint32_t* __restrict__ counts,
               const uint32_t* __restrict__ offsets, uint32_t* __restrict__ list,
-              uint32_t* __restrict__ entry_star, const uint8_t* __restrict__ skipmap) {
+              uint32_t* __restrict__ entry_star) {
   const int64_t s = static_cast<int64_t>(blockIdx.x) * kSelThreads + threadIdx.x;
   if (s >= n_stars) return;
-  // skipmap[star / 256][group] != 0: the pruned dense sweep left the group out for these 256
-  // stars and wrote nothing -- not selected, and gmin is not read (the same byte for the whole
-  // thread block, whose 128 stars lie in one run of 256)
-  const uint8_t* skip = skipmap ? skipmap + (s >> 8) * n_groups : nullptr;
   const int c = blockIdx.y;
   const int64_t per = (n_groups + BF_SELECT_SPLIT - 1) / BF_SELECT_SPLIT;
   const int64_t g0 = c * per;
@@ -41,16 +37,8 @@ select_kernel(int64_t n_groups, int64_t n_stars, int64_t ld_star, const float* _
   int64_t g = g0;
   for (; g + 8 <= g1; g += 8) {
     float v[8];
-    if (skip) {
-      uint8_t k[8];
 #pragma unroll
-      for (int u = 0; u < 8; ++u) k[u] = __ldg(skip + g + u);
-#pragma unroll
-      for (int u = 0; u < 8; ++u) v[u] = k[u] ? __int_as_float(0x7f800000) : __ldg(p + (g + u) * ld_star);
-    } else {
-#pragma unroll
-      for (int u = 0; u < 8; ++u) v[u] = __ldg(p + (g + u) * ld_star);
-    }
+    for (int u = 0; u < 8; ++u) v[u] = __ldg(p + (g + u) * ld_star);
 #pragma unroll
     for (int u = 0; u < 8; ++u) {
       if (v[u] < thr) {
@@ -64,7 +52,6 @@ select_kernel(int64_t n_groups, int64_t n_stars, int64_t ld_star, const float* _
     }
   }
   for (; g < g1; ++g) {
-    if (skip && __ldg(skip + g)) continue;
     if (__ldg(p + g * ld_star) < thr) {
       if (FILL) {
         list[pos] = static_cast<uint32_t>(g);
@@ -181,41 +168,17 @@ static int run_scan(int64_t n, const uint32_t* in, uint32_t* out, uint32_t* scra
 
 }  // namespace bf
 
-extern "C" int bf_select_count_skip(int64_t n_groups, int64_t n_stars, int64_t ld_star,
-                                    const float* gmin, const uint64_t* starmin, float tau,
-                                    float err_a, float err_b, const uint8_t* skipmap,
-                                    uint32_t* counts, void* stream) {
+extern "C" int bf_select_count(int64_t n_groups, int64_t n_stars, int64_t ld_star,
+                               const float* gmin, const uint64_t* starmin, float tau,
+                               float err_a, float err_b, uint32_t* counts, void* stream) {
   using namespace bf;
   BF_REQUIRE(n_groups > 0 && n_stars > 0 && ld_star >= n_stars, "bf_select_count: bad sizes");
   BF_REQUIRE(gmin && starmin && counts, "bf_select_count: null pointer");
   dim3 grid(static_cast<unsigned>((n_stars + kSelThreads - 1) / kSelThreads), BF_SELECT_SPLIT);
   select_kernel<false><<<grid, kSelThreads, 0, static_cast<cudaStream_t>(stream)>>>(
       n_groups, n_stars, ld_star, gmin, reinterpret_cast<const unsigned long long*>(starmin), tau,
-      err_a, err_b, counts, nullptr, nullptr, nullptr, skipmap);
+      err_a, err_b, counts, nullptr, nullptr, nullptr);
   BF_CHECK_LAUNCH("select_kernel<count>");
-  return BF_OK;
-}
-
-extern "C" int bf_select_count(int64_t n_groups, int64_t n_stars, int64_t ld_star,
-                               const float* gmin, const uint64_t* starmin, float tau,
-                               float err_a, float err_b, uint32_t* counts, void* stream) {
-  return bf_select_count_skip(n_groups, n_stars, ld_star, gmin, starmin, tau, err_a, err_b, nullptr,
-                              counts, stream);
-}
-
-extern "C" int bf_select_fill_skip(int64_t n_groups, int64_t n_stars, int64_t ld_star,
-                                   const float* gmin, const uint64_t* starmin, float tau,
-                                   float err_a, float err_b, const uint8_t* skipmap,
-                                   const uint32_t* offsets, uint32_t* list, uint32_t* entry_star,
-                                   void* stream) {
-  using namespace bf;
-  BF_REQUIRE(n_groups > 0 && n_stars > 0 && ld_star >= n_stars, "bf_select_fill: bad sizes");
-  BF_REQUIRE(gmin && starmin && offsets && list, "bf_select_fill: null pointer");
-  dim3 grid(static_cast<unsigned>((n_stars + kSelThreads - 1) / kSelThreads), BF_SELECT_SPLIT);
-  select_kernel<true><<<grid, kSelThreads, 0, static_cast<cudaStream_t>(stream)>>>(
-      n_groups, n_stars, ld_star, gmin, reinterpret_cast<const unsigned long long*>(starmin), tau,
-      err_a, err_b, nullptr, offsets, list, entry_star, skipmap);
-  BF_CHECK_LAUNCH("select_kernel<fill>");
   return BF_OK;
 }
 
@@ -223,8 +186,15 @@ extern "C" int bf_select_fill(int64_t n_groups, int64_t n_stars, int64_t ld_star
                               const float* gmin, const uint64_t* starmin, float tau,
                               float err_a, float err_b, const uint32_t* offsets,
                               uint32_t* list, uint32_t* entry_star, void* stream) {
-  return bf_select_fill_skip(n_groups, n_stars, ld_star, gmin, starmin, tau, err_a, err_b, nullptr,
-                             offsets, list, entry_star, stream);
+  using namespace bf;
+  BF_REQUIRE(n_groups > 0 && n_stars > 0 && ld_star >= n_stars, "bf_select_fill: bad sizes");
+  BF_REQUIRE(gmin && starmin && offsets && list, "bf_select_fill: null pointer");
+  dim3 grid(static_cast<unsigned>((n_stars + kSelThreads - 1) / kSelThreads), BF_SELECT_SPLIT);
+  select_kernel<true><<<grid, kSelThreads, 0, static_cast<cudaStream_t>(stream)>>>(
+      n_groups, n_stars, ld_star, gmin, reinterpret_cast<const unsigned long long*>(starmin), tau,
+      err_a, err_b, nullptr, offsets, list, entry_star);
+  BF_CHECK_LAUNCH("select_kernel<fill>");
+  return BF_OK;
 }
 
 extern "C" int64_t bf_scan_scratch_elems(int64_t n) {

@@ -95,15 +95,11 @@ int bf_dense_chi2(int nb, int64_t n_tiles, const float* tiles, int64_t n_stars,
  * ceiling), and starmin is the same, so the lists are identical.  Pays off when neighbouring stars are alike (bf_fit_batch orders them).
  *   evaluated : optional device counter (may be NULL), raised by the number of (star, model)
  *           pairs the sweep did evaluate (padding stars and models included)
- *   skipmap : optional out (may be NULL) [ld_star/256][n_groups] bytes: 1 where the group was
- *           left out for that run of 256 stars, else 0.  With a skipmap the sweep writes nothing
- *           to gmin for those (group, stars) -- not even +inf --, so the selection must be the
- *           bf_select_*_skip kind with the same map
  * No counterpart in the reference, which evaluates every model for every star. */
 int bf_dense_chi2_pruned(int nb, int64_t n_tiles, const float* tiles, const float* boxes,
                          int64_t n_stars, int64_t ld_star, const float* flux, const float* cut,
                          float* gmin, uint64_t* starmin, int tiles_per_item, uint64_t* evaluated,
-                         uint8_t* skipmap, void* stream);
+                         void* stream);
 
 /* Same sweep for the full-covariance likelihood (N_covar_logLikelihood / N_covar_chi2,
  * fitting/fit_metrics/likelihood.py:58-106, 170-218; selected at fit.py:432-444).
@@ -137,16 +133,6 @@ int bf_select_count(int64_t n_groups, int64_t n_stars, int64_t ld_star, const fl
 int bf_select_fill(int64_t n_groups, int64_t n_stars, int64_t ld_star, const float* gmin,
                    const uint64_t* starmin, float tau, float err_a, float err_b,
                    const uint32_t* offsets, uint32_t* list, uint32_t* entry_star, void* stream);
-/* The same two passes after bf_dense_chi2_pruned with a skipmap ([ld_star/256][n_groups] bytes,
- * NULL = none): a group marked there for a star's run of 256 is not selected and its gmin entry,
- * which the sweep did not write, is not read. */
-int bf_select_count_skip(int64_t n_groups, int64_t n_stars, int64_t ld_star, const float* gmin,
-                         const uint64_t* starmin, float tau, float err_a, float err_b,
-                         const uint8_t* skipmap, uint32_t* counts, void* stream);
-int bf_select_fill_skip(int64_t n_groups, int64_t n_stars, int64_t ld_star, const float* gmin,
-                        const uint64_t* starmin, float tau, float err_a, float err_b,
-                        const uint8_t* skipmap, const uint32_t* offsets, uint32_t* list,
-                        uint32_t* entry_star, void* stream);
 
 /* Exclusive prefix sum of n uint32 (out[n] = total).  scratch: >= bf_scan_scratch_elems(n)
  * uint32.  Plumbing for the variable-length per-star lists. */

@@ -249,7 +249,7 @@ def test_pruned_dense_entry_point():
 
     count = torch.zeros(1, dtype=torch.int64, device=dev)
 
-    def sweep(cut, skipmap=None):
+    def sweep(cut):
         count.zero_()
         gmin = torch.empty((ng, ld), dtype=torch.float32, device=dev)
         smin = torch.full((ld,), 0x7f800000ffffffff, dtype=torch.int64, device=dev)
@@ -259,8 +259,7 @@ def test_pruned_dense_entry_point():
                        gmin.data_ptr(), smin.data_ptr(), 4, st)
         else:
             _cabi.call("bf_dense_chi2_pruned", nb, setup.n_tiles, tiles.data_ptr(), boxes.data_ptr(), n, ld,
-                       flux.data_ptr(), cut.data_ptr(), gmin.data_ptr(), smin.data_ptr(), 4, count.data_ptr(),
-                       skipmap.data_ptr() if skipmap is not None else None, st)
+                       flux.data_ptr(), cut.data_ptr(), gmin.data_ptr(), smin.data_ptr(), 4, count.data_ptr(), st)
         torch.cuda.synchronize()
         return gmin.cpu().numpy(), smin.cpu().numpy()
 
@@ -282,32 +281,6 @@ def test_pruned_dense_entry_point():
     # below the ceilings and everything
     assert below.sum() * 32 <= int(count.item()) < 0.7 * ng * 64 * ld
     assert np.all(full[skipped] >= cutb[skipped])
-    # with a skip map: marked (group, 256 stars) are those left out as a whole, nothing is written
-    # for them, and the selection that honours the map counts what the plain one counts
-    smap = torch.full((ld // 256, ng), 7, dtype=torch.uint8, device=dev)
-    gm = torch.full((ng, ld), -5.0, dtype=torch.float32, device=dev)
-    smin2 = torch.full((ld,), 0x7f800000ffffffff, dtype=torch.int64, device=dev)
-    st = torch.cuda.current_stream().cuda_stream
-    _cabi.call("bf_dense_chi2_pruned", nb, setup.n_tiles, tiles.data_ptr(), boxes.data_ptr(), n, ld,
-               flux.data_ptr(), cut.data_ptr(), gm.data_ptr(), smin2.data_ptr(), 4, None, smap.data_ptr(), st)
-    torch.cuda.synchronize()
-    m = smap.cpu().numpy()
-    assert set(np.unique(m)) <= {0, 1} and 0.3 < m.mean() < 1.0
-    gmh = gm.cpu().numpy().reshape(ng, ld // 256, 256)
-    marked = m.T.astype(bool)                                   # [group][run of 256 stars]
-    assert np.all(gmh[marked] == -5.0)                          # untouched
-    np.testing.assert_array_equal(gmh[~marked], pruned.reshape(ng, ld // 256, 256)[~marked])
-    assert np.all(np.isinf(pruned.reshape(ng, ld // 256, 256)[marked]))
-    split = 16
-    c_plain = torch.zeros((n, split), dtype=torch.int32, device=dev)
-    c_skip = torch.zeros((n, split), dtype=torch.int32, device=dev)
-    d_full = torch.from_numpy(full).to(dev)
-    _cabi.call("bf_select_count", ng, n, ld, d_full.data_ptr(), smin2.data_ptr(), 20.0, setup.err_a, setup.err_b,
-               c_plain.data_ptr(), st)
-    _cabi.call("bf_select_count_skip", ng, n, ld, gm.data_ptr(), smin2.data_ptr(), 20.0, setup.err_a, setup.err_b,
-               smap.data_ptr(), c_skip.data_ptr(), st)
-    torch.cuda.synchronize()
-    np.testing.assert_array_equal(c_skip.cpu().numpy(), c_plain.cpu().numpy())
     # a ceiling of +inf keeps everything, -1 (padding stars) skips everything
     same, _ = sweep(torch.full((ld,), float("inf"), device=dev))
     np.testing.assert_array_equal(same, full)
