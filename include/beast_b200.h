@@ -379,9 +379,10 @@ int bf_pdf2d_from_weights(int64_t ld_model, int n_pairs, const int32_t* pair_bin
  * list sizes decide the memory layout), twice with sparse_mode 1.
  *
  * plan    : the resident grid (device pointers; the struct itself is host memory)
- *   tiles / tiles_coarse : see bf_dense_chi2; tiles_coarse (a subset, e.g. every 64th model; may be NULL) is
- *                   swept first to order the stars by where their best models lie -- results
- *                   come back in the caller's order either way
+ *   tiles / tiles_coarse : see bf_dense_chi2; tiles_coarse (a subset of the models, e.g. every
+ *                   64th, in the same layout; may be NULL) is swept first: its minima are the
+ *                   ceilings of the pruned sweep, and the stars are put in an order in which
+ *                   neighbours are alike (sort_band) -- results come back in the caller's order
  *   inv_band_scale [nb] : 1 / s_b (device), turns flux64 into the FP32 fluxes of the dense pass
  *   boxes         : see bf_dense_chi2_pruned; used when tiles_coarse is given too (its minima
  *                   bound the selection thresholds), diagonal likelihood only
