@@ -223,3 +223,17 @@ def test_merging_stat_tables(tmp_path):
     assert list(hd[2][1]["filternames"]) == ["F1", "F2"]
     merge_stats_files(names, str(tmp_path / "tagged"), reorder_tag_list=["a", "b"])
     assert list(fitsio.read_fits(str(tmp_path / "tagged_stats.fits"))[1][1]["reorder_tag"]) == ["a"] * 3 + ["b"] * 2
+
+
+def test_host_binding_is_a_no_op_without_a_gpu():
+    """bind_host_to_gpu: without a CUDA device (or NVML) nothing is changed and None comes back"""
+    import os
+
+    from beast_b200.engine import bind_host_to_gpu
+
+    before = os.sched_getaffinity(0)
+    import torch
+
+    if not torch.cuda.is_available():
+        assert bind_host_to_gpu(0) is None
+    assert os.sched_getaffinity(0) == before or torch.cuda.is_available()
